@@ -1,0 +1,804 @@
+// engine.cu -- decoder engine: weights, paged KV cache, prefill / decode steps, CUDA-graph replay of
+// the decode step, Megatron tensor parallelism.  This is the body of the spec'd InferenceWorker
+// (.kiro/specs/distributed-inference-server/design.md:334-342); the reference's own worker file is
+// empty (crates/inference/src/worker.rs:1), so the step structure follows SURVEY.md §3.3.
+#include "engine.h"
+
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+
+namespace dis {
+
+// ------------------------------------------------------------------------------------ error state
+static thread_local std::string g_last_error;
+void set_last_error(const std::string &msg) { g_last_error = msg; }
+const char *get_last_error() { return g_last_error.c_str(); }
+
+int Engine::fail(int code, const std::string &msg) {
+  last_error = msg;
+  g_last_error = msg;
+  return code;
+}
+
+#define ENG_CUDA(expr)                                                                                   \
+  do {                                                                                                   \
+    cudaError_t _e = (expr);                                                                             \
+    if (_e != cudaSuccess) {                                                                             \
+      healthy = false;                                                                                   \
+      std::string _m = g_last_error.empty() ? std::string(cudaGetErrorString(_e)) : g_last_error;        \
+      return fail(_e == cudaErrorMemoryAllocation ? DIS_ERR_OUT_OF_MEMORY : DIS_ERR_INFERENCE_FAILED,    \
+                  std::string(#expr) + ": " + _m);                                                       \
+    }                                                                                                    \
+  } while (0)
+
+#define RET_CUDA(expr)                      \
+  do {                                      \
+    cudaError_t _e = (expr);                \
+    if (_e != cudaSuccess) return _e;       \
+  } while (0)
+
+template <class T_>
+static cudaError_t dev_alloc(T_ **p, size_t n, uint64_t *acct) {
+  *p = nullptr;
+  if (n == 0) return cudaSuccess;
+  cudaError_t e = cudaMalloc(reinterpret_cast<void **>(p), n * sizeof(T_));
+  if (e == cudaSuccess) *acct += n * sizeof(T_);
+  else set_last_error("cudaMalloc of " + std::to_string(n * sizeof(T_)) + " bytes failed");
+  return e;
+}
+
+static size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+// ------------------------------------------------------------------------------------ init
+int Engine::init(const dis_engine_config *c) {
+  cfg = *c;
+  m = c->model;
+  tp_rank = c->tp_rank;
+  tp_size = c->tp_size <= 0 ? 1 : c->tp_size;
+  if (m.vocab <= 0 || m.hidden <= 0 || m.layers <= 0 || m.n_heads <= 0 || m.n_kv_heads <= 0 || m.head_dim <= 0 ||
+      m.inter <= 0 || m.max_ctx <= 0)
+    return fail(DIS_ERR_INVALID_ARGUMENT, "model config: every dimension must be positive");
+  if (m.head_dim != 64 && m.head_dim != 128) return fail(DIS_ERR_INVALID_ARGUMENT, "head_dim must be 64 or 128");
+  if (m.n_heads % m.n_kv_heads != 0) return fail(DIS_ERR_INVALID_ARGUMENT, "n_heads must be a multiple of n_kv_heads");
+  if (tp_rank < 0 || tp_rank >= tp_size) return fail(DIS_ERR_INVALID_ARGUMENT, "tp_rank out of range");
+  if (m.n_kv_heads % tp_size || m.inter % tp_size || m.vocab % tp_size)
+    return fail(DIS_ERR_INVALID_ARGUMENT, "n_kv_heads, inter and vocab must be divisible by tp_size");
+  nh_l = m.n_heads / tp_size;
+  nkv_l = m.n_kv_heads / tp_size;
+  qd_l = nh_l * m.head_dim;
+  kvd_l = nkv_l * m.head_dim;
+  nqkv_l = qd_l + 2 * kvd_l;
+  inter_l = m.inter / tp_size;
+  vocab_l = m.vocab / tp_size;
+  vocab_off = tp_rank * vocab_l;
+  if (m.hidden % 8 || inter_l % 8 || qd_l % 8) return fail(DIS_ERR_INVALID_ARGUMENT, "hidden, inter/tp and n_heads*head_dim/tp must be multiples of 8");
+  max_batch = c->max_batch > 0 ? c->max_batch : 32;
+  cap_tokens = c->max_step_tokens > 0 ? c->max_step_tokens : 8192;
+  cap_tokens = std::max(cap_tokens, max_batch);
+  page_size = c->page_size > 0 ? c->page_size : 64;
+  if (page_size & (page_size - 1)) return fail(DIS_ERR_INVALID_ARGUMENT, "page_size must be a power of two");
+  max_pages = (m.max_ctx + page_size - 1) / page_size;
+
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
+    return fail(DIS_ERR_INFERENCE_FAILED, "no CUDA device: this engine has no CPU fallback");
+  if (c->device < 0 || c->device >= ndev) return fail(DIS_ERR_INVALID_ARGUMENT, "device ordinal out of range");
+  ENG_CUDA(cudaSetDevice(c->device));
+  cudaDeviceProp prop;
+  ENG_CUDA(cudaGetDeviceProperties(&prop, c->device));
+  if (prop.major != 10)
+    return fail(DIS_ERR_INFERENCE_FAILED, std::string("device is sm_") + std::to_string(prop.major * 10 + prop.minor) +
+                                              "; kernels are built for sm_100a only");
+  if (c->stream) stream = (cudaStream_t)c->stream;
+  else { ENG_CUDA(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking)); own_stream = true; }
+  ENG_CUDA(cudaEventCreate(&ev0));
+  ENG_CUDA(cudaEventCreate(&ev1));
+
+  const size_t L = m.layers, H = m.hidden;
+  // ---- weights
+  ENG_CUDA(dev_alloc(&embed, (size_t)m.vocab * H, &bytes_allocated));
+  ENG_CUDA(dev_alloc(&wqkv, L * nqkv_l * H, &bytes_allocated));
+  ENG_CUDA(dev_alloc(&wo, L * H * qd_l, &bytes_allocated));
+  ENG_CUDA(dev_alloc(&wgu, L * 2 * inter_l * H, &bytes_allocated));
+  ENG_CUDA(dev_alloc(&wdown, L * H * inter_l, &bytes_allocated));
+  ENG_CUDA(dev_alloc(&lm_head, (size_t)vocab_l * H, &bytes_allocated));
+  ENG_CUDA(dev_alloc(&attn_norm, L * H, &bytes_allocated));
+  ENG_CUDA(dev_alloc(&mlp_norm, L * H, &bytes_allocated));
+  ENG_CUDA(dev_alloc(&final_norm, H, &bytes_allocated));
+  ENG_CUDA(make_tma_map_2d(&wqkv_map, wqkv, L * nqkv_l, H, 128));
+  ENG_CUDA(make_tma_map_2d(&wo_map, wo, L * H, qd_l, 128));
+  ENG_CUDA(make_tma_map_2d(&wgu_map, wgu, L * 2 * inter_l, H, 128));
+  ENG_CUDA(make_tma_map_2d(&wdown_map, wdown, L * H, inter_l, 128));
+  ENG_CUDA(make_tma_map_2d(&lm_map, lm_head, vocab_l, H, 128));
+  // ---- activations
+  const size_t cap = cap_tokens;
+  const size_t widest = std::max<size_t>(nqkv_l, H);
+  partial_elems = std::max(cap * widest, (size_t)16 * 128 * widest);
+  ENG_CUDA(dev_alloc(&x, cap * H, &bytes_allocated));
+  ENG_CUDA(dev_alloc(&xn, cap * H, &bytes_allocated));
+  ENG_CUDA(dev_alloc(&q, cap * qd_l, &bytes_allocated));
+  ENG_CUDA(dev_alloc(&attn, cap * qd_l, &bytes_allocated));
+  ENG_CUDA(dev_alloc(&act, cap * inter_l, &bytes_allocated));
+  ENG_CUDA(dev_alloc(&partial, partial_elems, &bytes_allocated));
+  ENG_CUDA(dev_alloc(&logits, (size_t)max_batch * vocab_l, &bytes_allocated));
+  attn_scratch_elems = (size_t)(max_batch + 2 * kNumSMs + 64) * nh_l * (2 + m.head_dim);
+  ENG_CUDA(dev_alloc(&attn_scratch, attn_scratch_elems, &bytes_allocated));
+  ENG_CUDA(dev_alloc(&d_out_tokens, (size_t)max_batch, &bytes_allocated));
+  ENG_CUDA(cudaMallocHost(reinterpret_cast<void **>(&h_out_tokens), (size_t)max_batch * sizeof(uint32_t)));
+  if (tp_size > 1) {
+    ENG_CUDA(dev_alloc(&ar_buf, cap * H, &bytes_allocated));
+    ENG_CUDA(dev_alloc(&full_logits, (size_t)max_batch * m.vocab, &bytes_allocated));
+    ENG_CUDA(dev_alloc(&gather_buf, (size_t)max_batch * m.vocab, &bytes_allocated));
+    ENG_CUDA(dev_alloc(&cand_val, (size_t)max_batch, &bytes_allocated));
+    ENG_CUDA(dev_alloc(&cand_tok, (size_t)max_batch, &bytes_allocated));
+    ENG_CUDA(dev_alloc(&cand_val_all, (size_t)max_batch * tp_size, &bytes_allocated));
+    ENG_CUDA(dev_alloc(&cand_tok_all, (size_t)max_batch * tp_size, &bytes_allocated));
+  }
+  const uint32_t boxes[3] = {32, 64, 128};
+  for (int i = 0; i < 3; i++) {
+    ENG_CUDA(make_tma_map_2d(&xn_map[i], xn, cap, H, boxes[i]));
+    ENG_CUDA(make_tma_map_2d(&attn_map[i], attn, cap, qd_l, boxes[i]));
+    ENG_CUDA(make_tma_map_2d(&act_map[i], act, cap, inter_l, boxes[i]));
+  }
+  // ---- RoPE tables (computed in double on the host, like the oracle; values only depend on the math)
+  {
+    const int half = m.head_dim / 2;
+    std::vector<float> cs((size_t)m.max_ctx * half), sn((size_t)m.max_ctx * half);
+    for (int p = 0; p < m.max_ctx; p++)
+      for (int i = 0; i < half; i++) {
+        const double inv_freq = std::pow((double)m.rope_theta, -2.0 * (double)i / (double)m.head_dim);
+        const double a = (double)p * inv_freq;
+        cs[(size_t)p * half + i] = (float)std::cos(a);
+        sn[(size_t)p * half + i] = (float)std::sin(a);
+      }
+    ENG_CUDA(dev_alloc(&rope_cos, cs.size(), &bytes_allocated));
+    ENG_CUDA(dev_alloc(&rope_sin, sn.size(), &bytes_allocated));
+    ENG_CUDA(cudaMemcpy(rope_cos, cs.data(), cs.size() * 4, cudaMemcpyHostToDevice));
+    ENG_CUDA(cudaMemcpy(rope_sin, sn.data(), sn.size() * 4, cudaMemcpyHostToDevice));
+  }
+  // ---- step metadata
+  {
+    StepMeta &s = meta;
+    s.cap_tokens = cap_tokens;
+    s.cap_rows = max_batch;
+    size_t o = 0;
+    auto sec = [&](size_t bytes) { size_t at = o; o = align_up(o + bytes, 16); return at; };
+    s.o_tokens = sec(cap * 4); s.o_pos = sec(cap * 4); s.o_ptrow = sec(cap * 4); s.o_ctx = sec(cap * 4);
+    s.o_rowmap = sec((size_t)max_batch * 4); s.o_temp = sec((size_t)max_batch * 4); s.o_topp = sec((size_t)max_batch * 4);
+    s.o_seed = sec((size_t)max_batch * 8); s.o_step = sec((size_t)max_batch * 8);
+    s.bytes = o;
+    ENG_CUDA(cudaMallocHost(reinterpret_cast<void **>(&s.host), s.bytes));
+    ENG_CUDA(dev_alloc(&s.dev, s.bytes, &bytes_allocated));
+    memset(s.host, 0, s.bytes);
+  }
+  // ---- KV pages: [layer][page][2][nkv_l][page_size][d]
+  {
+    const size_t page_elems = (size_t)2 * nkv_l * page_size * m.head_dim;
+    const size_t page_bytes_all_layers = page_elems * 2 * L;
+    int64_t want = c->kv_pages;
+    const int64_t useful = (int64_t)max_batch * max_pages;
+    if (want <= 0) {
+      size_t free_b = 0, total_b = 0;
+      ENG_CUDA(cudaMemGetInfo(&free_b, &total_b));
+      const float frac = c->kv_mem_fraction > 0.f ? c->kv_mem_fraction : 0.85f;
+      want = (int64_t)((double)free_b * frac / (double)page_bytes_all_layers);
+      want = std::min(want, useful);
+    }
+    if (want < 1) return fail(DIS_ERR_OUT_OF_MEMORY, "no device memory left for KV pages");
+    n_pages = want;
+    kv_layer_stride = (size_t)n_pages * page_elems;
+    ENG_CUDA(dev_alloc(&kv_pool, kv_layer_stride * L, &bytes_allocated));
+    free_pages.resize((size_t)n_pages);
+    for (int64_t i = 0; i < n_pages; i++) free_pages[(size_t)i] = (int)(n_pages - 1 - i);
+    ENG_CUDA(dev_alloc(&d_page_table, (size_t)max_batch * max_pages, &bytes_allocated));
+    ENG_CUDA(cudaMallocHost(reinterpret_cast<void **>(&h_page_table), (size_t)max_batch * max_pages * sizeof(int)));
+    memset(h_page_table, 0, (size_t)max_batch * max_pages * sizeof(int));
+  }
+  seqs.resize((size_t)max_batch);
+  // ---- tensor parallel communicator
+  if (tp_size > 1) {
+    std::string err;
+    nccl = nccl_api(&err);
+    if (!nccl) return fail(DIS_ERR_INFERENCE_FAILED, "tensor parallel needs NCCL: " + err);
+    NcclId id;
+    memcpy(id.bytes, c->nccl_id, 128);
+    const int r = nccl->CommInitRank(&comm, tp_size, id, tp_rank);
+    if (r != 0) return fail(DIS_ERR_INFERENCE_FAILED, std::string("ncclCommInitRank: ") + nccl->GetErrorString(r));
+  }
+  ENG_CUDA(cudaDeviceSynchronize());
+  return DIS_OK;
+}
+
+Engine::~Engine() {
+  if (cfg.device >= 0) cudaSetDevice(cfg.device);
+  if (stream) cudaStreamSynchronize(stream);
+  for (auto &g : graphs) cudaGraphExecDestroy(g.second);
+  for (auto ev : prof_events) cudaEventDestroy(ev);
+  if (comm && nccl) nccl->CommDestroy(comm);
+  void *ptrs[] = {embed, wqkv, wo, wgu, wdown, lm_head, attn_norm, mlp_norm, final_norm, x, partial, logits, ar_buf,
+                  attn_scratch, full_logits, gather_buf, cand_val, cand_val_all, cand_tok, cand_tok_all, xn, q, attn,
+                  act, d_out_tokens, kv_pool, d_page_table, rope_cos, rope_sin, meta.dev};
+  for (void *p : ptrs) if (p) cudaFree(p);
+  if (h_out_tokens) cudaFreeHost(h_out_tokens);
+  if (h_page_table) cudaFreeHost(h_page_table);
+  if (meta.host) cudaFreeHost(meta.host);
+  if (ev0) cudaEventDestroy(ev0);
+  if (ev1) cudaEventDestroy(ev1);
+  if (own_stream && stream) cudaStreamDestroy(stream);
+}
+
+// ------------------------------------------------------------------------------------ weights
+bool Engine::tensor_slot(int kind, int layer, TensorSlot *o) {
+  const size_t H = m.hidden, d = m.head_dim, l = (size_t)layer;
+  const size_t qd = (size_t)m.n_heads * d, kd = (size_t)m.n_kv_heads * d;
+  const bool per_layer = !(kind == DIS_T_EMBED || kind == DIS_T_FINAL_NORM || kind == DIS_T_LM_HEAD);
+  if (per_layer && (layer < 0 || layer >= m.layers)) return false;
+  TensorSlot s{};
+  s.f32 = false;
+  switch (kind) {
+    case DIS_T_EMBED: s = {embed, (size_t)m.vocab, H, H, 0, 0, (size_t)m.vocab, H, false}; break;
+    case DIS_T_LM_HEAD: s = {lm_head, (size_t)vocab_l, H, H, (size_t)vocab_off, 0, (size_t)m.vocab, H, false}; break;
+    case DIS_T_FINAL_NORM: s = {final_norm, 1, H, H, 0, 0, 1, H, true}; break;
+    case DIS_T_ATTN_NORM: s = {attn_norm + l * H, 1, H, H, 0, 0, 1, H, true}; break;
+    case DIS_T_MLP_NORM: s = {mlp_norm + l * H, 1, H, H, 0, 0, 1, H, true}; break;
+    case DIS_T_WQ: s = {wqkv + l * nqkv_l * H, (size_t)qd_l, H, H, (size_t)tp_rank * qd_l, 0, qd, H, false}; break;
+    case DIS_T_WK: s = {wqkv + (l * nqkv_l + qd_l) * H, (size_t)kvd_l, H, H, (size_t)tp_rank * kvd_l, 0, kd, H, false}; break;
+    case DIS_T_WV: s = {wqkv + (l * nqkv_l + qd_l + kvd_l) * H, (size_t)kvd_l, H, H, (size_t)tp_rank * kvd_l, 0, kd, H, false}; break;
+    case DIS_T_WO: s = {wo + l * H * qd_l, H, (size_t)qd_l, (size_t)qd_l, 0, (size_t)tp_rank * qd_l, H, qd, false}; break;
+    case DIS_T_WGATE: s = {wgu + l * 2 * inter_l * H, (size_t)inter_l, H, H, (size_t)tp_rank * inter_l, 0, (size_t)m.inter, H, false}; break;
+    case DIS_T_WUP: s = {wgu + (l * 2 * inter_l + inter_l) * H, (size_t)inter_l, H, H, (size_t)tp_rank * inter_l, 0, (size_t)m.inter, H, false}; break;
+    case DIS_T_WDOWN: s = {wdown + l * H * inter_l, H, (size_t)inter_l, (size_t)inter_l, 0, (size_t)tp_rank * inter_l, H, (size_t)m.inter, false}; break;
+    default: return false;
+  }
+  *o = s;
+  return true;
+}
+
+int Engine::load_tensor(int kind, int layer, const void *host, int dtype) {
+  if (shut) return fail(DIS_ERR_SHUTDOWN, "engine is shut down");
+  if (!host) return fail(DIS_ERR_INVALID_ARGUMENT, "load_tensor: null host pointer");
+  if (dtype != DIS_F32 && dtype != DIS_BF16) return fail(DIS_ERR_INVALID_ARGUMENT, "load_tensor: dtype must be f32 or bf16");
+  TensorSlot s;
+  if (!tensor_slot(kind, layer, &s)) return fail(DIS_ERR_INVALID_ARGUMENT, "load_tensor: bad tensor kind or layer");
+  ENG_CUDA(cudaSetDevice(cfg.device));
+  const size_t n = s.rows * s.cols;
+  if (s.f32) {
+    std::vector<float> tmp(n);
+    for (size_t r = 0; r < s.rows; r++)
+      for (size_t c = 0; c < s.cols; c++) {
+        const size_t src = (s.row0 + r) * s.full_cols + s.col0 + c;
+        const float v = dtype == DIS_F32 ? static_cast<const float *>(host)[src]
+                                         : bf16_bits_to_float(static_cast<const uint16_t *>(host)[src]);
+        tmp[r * s.cols + c] = bf16_bits_to_float(float_to_bf16_bits(v));  // gains are bf16 values held in fp32
+      }
+    ENG_CUDA(cudaMemcpy(s.ptr, tmp.data(), n * 4, cudaMemcpyHostToDevice));
+  } else {
+    std::vector<uint16_t> tmp(n);
+    for (size_t r = 0; r < s.rows; r++) {
+      const size_t src0 = (s.row0 + r) * s.full_cols + s.col0;
+      if (dtype == DIS_BF16) memcpy(&tmp[r * s.cols], static_cast<const uint16_t *>(host) + src0, s.cols * 2);
+      else {
+        const float *f = static_cast<const float *>(host) + src0;
+        for (size_t c = 0; c < s.cols; c++) tmp[r * s.cols + c] = float_to_bf16_bits(f[c]);
+      }
+    }
+    ENG_CUDA(cudaMemcpy(s.ptr, tmp.data(), n * 2, cudaMemcpyHostToDevice));
+  }
+  return DIS_OK;
+}
+
+// amplitude / offset convention of the synthetic model (independently restated in the oracle)
+static void synth_params(const dis_model_config &m, int kind, float *amp, float *off) {
+  const float a = 0.034641016f;  // 0.02 * sqrt(3): uniform(-a, a) has std 0.02
+  *off = 0.f;
+  switch (kind) {
+    case DIS_T_ATTN_NORM: case DIS_T_MLP_NORM: case DIS_T_FINAL_NORM: *amp = 0.1f; *off = 1.0f; break;
+    case DIS_T_WO: case DIS_T_WDOWN: *amp = a / sqrtf(2.0f * (float)m.layers); break;
+    default: *amp = a; break;
+  }
+}
+
+int Engine::load_synthetic(uint64_t seed) {
+  if (shut) return fail(DIS_ERR_SHUTDOWN, "engine is shut down");
+  ENG_CUDA(cudaSetDevice(cfg.device));
+  uint16_t *tmp = nullptr;
+  uint64_t dummy = 0;
+  ENG_CUDA(dev_alloc(&tmp, (size_t)m.hidden, &dummy));
+  const int globals[3] = {DIS_T_EMBED, DIS_T_FINAL_NORM, DIS_T_LM_HEAD};
+  const int per_layer[9] = {DIS_T_ATTN_NORM, DIS_T_WQ, DIS_T_WK, DIS_T_WV, DIS_T_WO, DIS_T_MLP_NORM, DIS_T_WGATE, DIS_T_WUP, DIS_T_WDOWN};
+  auto gen = [&](int kind, int layer) -> cudaError_t {
+    TensorSlot s;
+    tensor_slot(kind, layer, &s);
+    float amp, off;
+    synth_params(m, kind, &amp, &off);
+    const bool pl = !(kind == DIS_T_EMBED || kind == DIS_T_FINAL_NORM || kind == DIS_T_LM_HEAD);
+    const size_t n = s.rows * s.cols;
+    const size_t idx0 = s.row0 * s.full_cols;
+    if (s.f32) {
+      RET_CUDA(launch_synth_bf16(tmp, n, seed, kind, pl ? layer : 0, amp, off, idx0, s.cols, s.full_cols, s.col0, stream));
+      return launch_bf16_to_f32(tmp, static_cast<float *>(s.ptr), n, stream);
+    }
+    return launch_synth_bf16(static_cast<uint16_t *>(s.ptr), n, seed, kind, pl ? layer : 0, amp, off, idx0, s.cols,
+                             s.full_cols, s.col0, stream);
+  };
+  for (int k : globals) ENG_CUDA(gen(k, 0));
+  for (int l = 0; l < m.layers; l++)
+    for (int k : per_layer) ENG_CUDA(gen(k, l));
+  ENG_CUDA(cudaStreamSynchronize(stream));
+  cudaFree(tmp);
+  return DIS_OK;
+}
+
+int Engine::read_tensor(int kind, int layer, uint16_t *host, size_t *n) {
+  TensorSlot s;
+  if (!n || !tensor_slot(kind, layer, &s)) return fail(DIS_ERR_INVALID_ARGUMENT, "read_tensor: bad argument");
+  const size_t need = s.rows * s.cols;
+  if (!host || *n < need) { *n = need; return fail(DIS_ERR_INVALID_ARGUMENT, "read_tensor: buffer too small"); }
+  *n = need;
+  ENG_CUDA(cudaSetDevice(cfg.device));
+  ENG_CUDA(cudaStreamSynchronize(stream));
+  if (s.f32) {
+    std::vector<float> tmp(need);
+    ENG_CUDA(cudaMemcpy(tmp.data(), s.ptr, need * 4, cudaMemcpyDeviceToHost));
+    for (size_t i = 0; i < need; i++) host[i] = float_to_bf16_bits(tmp[i]);
+  } else {
+    ENG_CUDA(cudaMemcpy(host, s.ptr, need * 2, cudaMemcpyDeviceToHost));
+  }
+  return DIS_OK;
+}
+
+int Engine::finalize() {
+  if (shut) return fail(DIS_ERR_SHUTDOWN, "engine is shut down");
+  loaded = true;
+  return DIS_OK;
+}
+
+// ------------------------------------------------------------------------------------ sequences
+bool Engine::ensure_pages(Sequence &s, int slot, int n_tokens) {
+  const int need = (n_tokens + page_size - 1) / page_size;
+  if (need > max_pages) return false;
+  while ((int)s.pages.size() < need) {
+    if (free_pages.empty()) return false;
+    const int p = free_pages.back();
+    free_pages.pop_back();
+    h_page_table[(size_t)slot * max_pages + s.pages.size()] = p;
+    s.pages.push_back(p);
+    pt_dirty = true;
+  }
+  return true;
+}
+
+void Engine::release_pages(Sequence &s) {
+  for (int p : s.pages) free_pages.push_back(p);
+  s.pages.clear();
+}
+
+int Engine::seq_add(const uint32_t *prompt, int n, const dis_sampling_params *p, int *slot_out) {
+  if (shut) return fail(DIS_ERR_SHUTDOWN, "engine is shut down");
+  if (!loaded) return fail(DIS_ERR_MODEL_NOT_LOADED, "model not loaded");
+  if (!prompt || n <= 0 || !p || !slot_out) return fail(DIS_ERR_INVALID_ARGUMENT, "seq_add: empty prompt or null argument");
+  if (n >= m.max_ctx) return fail(DIS_ERR_INVALID_ARGUMENT, "seq_add: prompt does not fit the context window");
+  for (int i = 0; i < n; i++)
+    if (prompt[i] >= (uint32_t)m.vocab) return fail(DIS_ERR_INVALID_ARGUMENT, "seq_add: token id out of vocabulary");
+  if (p->temperature < 0.f || p->top_p < 0.f || p->top_p > 1.f || p->max_tokens < 1)
+    return fail(DIS_ERR_INVALID_ARGUMENT, "seq_add: bad sampling parameters");
+  int slot = -1;
+  for (int i = 0; i < max_batch; i++) if (!seqs[(size_t)i].used) { slot = i; break; }
+  if (slot < 0) return fail(DIS_ERR_OUT_OF_MEMORY, "seq_add: all sequence slots are in use");
+  Sequence &s = seqs[(size_t)slot];
+  s = Sequence();
+  if (!ensure_pages(s, slot, n + 1)) { release_pages(s); return fail(DIS_ERR_OUT_OF_MEMORY, "seq_add: out of KV pages"); }
+  s.used = true;
+  s.prompt.assign(prompt, prompt + n);
+  s.max_tokens = p->max_tokens;
+  s.temperature = p->temperature;
+  s.top_p = p->top_p;
+  s.seed = p->seed;
+  size_t off = 0;
+  for (int i = 0; i < p->n_stop; i++) {
+    const int len = p->stop_lens ? p->stop_lens[i] : 0;
+    if (len > 0 && p->stop_tokens) s.stop.emplace_back(p->stop_tokens + off, p->stop_tokens + off + len);
+    off += (size_t)std::max(len, 0);
+  }
+  *slot_out = slot;
+  return DIS_OK;
+}
+
+int Engine::seq_remove(int slot) {
+  if (slot < 0 || slot >= max_batch || !seqs[(size_t)slot].used) return fail(DIS_ERR_INVALID_ARGUMENT, "seq_remove: no such sequence");
+  release_pages(seqs[(size_t)slot]);
+  seqs[(size_t)slot] = Sequence();
+  return DIS_OK;
+}
+
+void Engine::finish_check(Sequence &s, uint32_t tok) {
+  s.generated++;
+  tokens_generated++;
+  s.last_token = tok;
+  s.tail.push_back(tok);
+  size_t longest = 0;
+  for (auto &st : s.stop) longest = std::max(longest, st.size());
+  if (s.tail.size() > longest && longest > 0) s.tail.erase(s.tail.begin(), s.tail.end() - (long)longest);
+  if (longest == 0) s.tail.clear();
+  if (cfg.eos_token >= 0 && tok == (uint32_t)cfg.eos_token) { s.finish = DIS_FINISH_STOP; return; }
+  for (auto &st : s.stop)
+    if (st.size() <= s.tail.size() && std::equal(st.begin(), st.end(), s.tail.end() - (long)st.size())) { s.finish = DIS_FINISH_STOP_SEQUENCE; return; }
+  if (s.generated >= s.max_tokens) { s.finish = DIS_FINISH_LENGTH; return; }
+  if (s.len + 1 >= m.max_ctx) { s.finish = DIS_FINISH_LENGTH; return; }
+}
+
+// ------------------------------------------------------------------------------------ step plumbing
+cudaError_t Engine::upload_step(int T, int R) {
+  if (pt_dirty) {
+    RET_CUDA(cudaMemcpyAsync(d_page_table, h_page_table, (size_t)max_batch * max_pages * sizeof(int), cudaMemcpyHostToDevice, stream));
+    pt_dirty = false;
+  }
+  (void)T; (void)R;
+  return cudaMemcpyAsync(meta.dev, meta.host, meta.bytes, cudaMemcpyHostToDevice, stream);
+}
+
+int Engine::pick_attn_splits(int T, int max_ctx_in_batch) const {
+  const int hpk = nh_l / nkv_l;
+  const int gpk = hpk >= 4 ? hpk / 4 : 1;
+  const int ctas = T * nkv_l * gpk;
+  int want = (2 * kNumSMs + ctas - 1) / ctas;
+  const int cap = std::max(1, max_ctx_in_batch / 128);
+  want = std::min(std::min(want, cap), 32);
+  while ((size_t)T * nh_l * want * (2 + m.head_dim) > attn_scratch_elems && want > 1) want--;
+  return std::max(want, 1);
+}
+
+static int tile_index(int T) { const int t = gemm_token_tile(T); return t == 32 ? 0 : (t == 64 ? 1 : 2); }
+
+// out = partial[S][T][N] of  X[T][K] * W[w_row0 : w_row0+N][K]^T
+cudaError_t Engine::linear_partial(const TmaMap *xmaps, const uint16_t *xptr, const TmaMap &wmap, const uint16_t *wptr,
+                                   int w_row0, int T, int N, int K, int *split_out) {
+  const bool gemv = (cfg.flags & DIS_FLAG_FORCE_GEMV) || T <= 2;
+  if (gemv) {
+    *split_out = 1;
+    kernel_launches += (uint64_t)((T + kGemvMaxT - 1) / kGemvMaxT);
+    return launch_gemv(xptr, wptr + (size_t)w_row0 * K, partial, T, N, K, stream);
+  }
+  int s = gemm_pick_split_k(T, N, K);
+  if ((size_t)s * T * N > partial_elems) s = 1;
+  *split_out = s;
+  kernel_launches++;
+  return launch_gemm_partial(wmap, xmaps[tile_index(T)], partial, T, N, K, w_row0, s, stream);
+}
+
+// Tensor parallel: sum the split-K slices, all-reduce over ranks; afterwards the data is ar_buf[T][H].
+cudaError_t Engine::allreduce_partials(int split, int T) {
+  const long long n = (long long)T * m.hidden;
+  prof_mark(P_ALLREDUCE);
+  RET_CUDA(launch_reduce_partials(partial, split, n, ar_buf, n, stream));
+  kernel_launches += 2;
+  const int r = nccl->AllReduce(ar_buf, ar_buf, (size_t)n, /*ncclFloat32*/ 7, /*ncclSum*/ 0, comm, stream);
+  if (r != 0) { set_last_error(std::string("ncclAllReduce: ") + nccl->GetErrorString(r)); return cudaErrorUnknown; }
+  return cudaSuccess;
+}
+
+cudaError_t Engine::enqueue_layers(int T, int n_splits) {
+  const int H = m.hidden, d = m.head_dim;
+  const bool gemv = (cfg.flags & DIS_FLAG_FORCE_GEMV) || T <= 2;
+  const float *pend = nullptr;  // projection output waiting to be added to the residual
+  int pend_n = 0;
+  long long pend_stride = 0;
+  const uint32_t *tokens = meta.d<uint32_t>(meta.o_tokens);
+  const int *pos = meta.d<int>(meta.o_pos), *ptrow = meta.d<int>(meta.o_ptrow), *ctx = meta.d<int>(meta.o_ctx);
+  for (int l = 0; l < m.layers; l++) {
+    // x (+)= pending; xn = RMSNorm(x)
+    prof_mark(P_NORM);
+    RET_CUDA(launch_add_rmsnorm(x, l == 0 ? tokens : nullptr, embed, pend, pend_n, pend_stride, attn_norm + (size_t)l * H,
+                                xn, nullptr, T, H, m.rms_eps, stream));
+    kernel_launches++;
+    int s_qkv = 1;
+    prof_mark(P_QKV);
+    RET_CUDA(linear_partial(xn_map, xn, wqkv_map, wqkv, l * nqkv_l, T, nqkv_l, H, &s_qkv));
+    uint16_t *pool = kv_pool + (size_t)l * kv_layer_stride;
+    prof_mark(P_ROPE);
+    RET_CUDA(launch_rope_kv_write(partial, s_qkv, (long long)T * nqkv_l, q, pool, d_page_table, max_pages, ptrow, pos,
+                                  rope_cos, rope_sin, T, nh_l, nkv_l, d, page_size, stream));
+    prof_mark(P_ATTN);
+    RET_CUDA(launch_attn_paged(q, pool, d_page_table, max_pages, ptrow, ctx, attn, attn_scratch, n_splits, T, nh_l,
+                               nkv_l, d, page_size, stream));
+    kernel_launches += n_splits > 1 ? 3 : 2;
+    int s_o = 1;
+    prof_mark(P_OPROJ);
+    RET_CUDA(linear_partial(attn_map, attn, wo_map, wo, l * H, T, H, qd_l, &s_o));
+    if (tp_size > 1) { RET_CUDA(allreduce_partials(s_o, T)); pend = ar_buf; pend_n = 1; pend_stride = 0; }
+    else { pend = partial; pend_n = s_o; pend_stride = (long long)T * H; }
+    prof_mark(P_NORM);
+    RET_CUDA(launch_add_rmsnorm(x, nullptr, nullptr, pend, pend_n, pend_stride, mlp_norm + (size_t)l * H, xn, nullptr, T,
+                                H, m.rms_eps, stream));
+    kernel_launches++;
+    prof_mark(P_GATEUP);
+    if (gemv) {
+      RET_CUDA(launch_gemv_silu(xn, wgu + (size_t)l * 2 * inter_l * H, act, T, inter_l, H, stream));
+      kernel_launches += (uint64_t)((T + kGemvMaxT - 1) / kGemvMaxT);
+    } else {
+      RET_CUDA(launch_gemm_silu(wgu_map, xn_map[tile_index(T)], act, T, inter_l, H, l * 2 * inter_l, stream));
+      kernel_launches++;
+    }
+    int s_d = 1;
+    prof_mark(P_DOWN);
+    RET_CUDA(linear_partial(act_map, act, wdown_map, wdown, l * H, T, H, inter_l, &s_d));
+    if (tp_size > 1) { RET_CUDA(allreduce_partials(s_d, T)); pend = ar_buf; pend_n = 1; pend_stride = 0; }
+    else { pend = partial; pend_n = s_d; pend_stride = (long long)T * H; }
+  }
+  pend_ptr = pend; pend_count = pend_n; pend_str = pend_stride;
+  return cudaSuccess;
+}
+
+// final norm on the rows that need logits, lm_head, sampling
+cudaError_t Engine::enqueue_head(int R, bool all_greedy) {
+  const int H = m.hidden;
+  prof_mark(P_HEAD_NORM);
+  RET_CUDA(launch_add_rmsnorm(x, nullptr, nullptr, pend_ptr, pend_count, pend_str, final_norm, xn,
+                              meta.d<int>(meta.o_rowmap), R, H, m.rms_eps, stream));
+  kernel_launches++;
+  const bool gemv = (cfg.flags & DIS_FLAG_FORCE_GEMV) || R <= 2;
+  prof_mark(P_LM_HEAD);
+  if (gemv) { RET_CUDA(launch_gemv(xn, lm_head, logits, R, vocab_l, H, stream)); kernel_launches += (uint64_t)((R + kGemvMaxT - 1) / kGemvMaxT); }
+  else { RET_CUDA(launch_gemm_partial(lm_map, xn_map[tile_index(R)], logits, R, vocab_l, H, 0, 1, stream)); kernel_launches++; }
+  prof_mark(P_SAMPLE);
+  const float *temp = meta.d<float>(meta.o_temp), *topp = meta.d<float>(meta.o_topp);
+  const unsigned long long *seed = meta.d<unsigned long long>(meta.o_seed), *step = meta.d<unsigned long long>(meta.o_step);
+  if (tp_size == 1) {
+    kernel_launches++;
+    return launch_sample(logits, vocab_l, R, vocab_l, temp, topp, seed, step, d_out_tokens, 0, nullptr, stream);
+  }
+  if (all_greedy) {
+    // vocab-parallel argmax: local (value, id) -> all-gather -> merge
+    RET_CUDA(launch_sample(logits, vocab_l, R, vocab_l, nullptr, nullptr, nullptr, nullptr, cand_tok, vocab_off, cand_val, stream));
+    int r = nccl->AllGather(cand_val, cand_val_all, (size_t)R, /*ncclFloat32*/ 7, comm, stream);
+    if (r == 0) r = nccl->AllGather(cand_tok, cand_tok_all, (size_t)R, /*ncclUint32*/ 3, comm, stream);
+    if (r != 0) { set_last_error(std::string("ncclAllGather: ") + nccl->GetErrorString(r)); return cudaErrorUnknown; }
+    kernel_launches += 4;
+    return launch_argmax_merge(cand_val_all, cand_tok_all, tp_size, R, d_out_tokens, stream);
+  }
+  RET_CUDA(gather_full_logits(R));
+  kernel_launches++;
+  return launch_sample(full_logits, m.vocab, R, m.vocab, temp, topp, seed, step, d_out_tokens, 0, nullptr, stream);
+}
+
+__global__ void interleave_logits_kernel(const float *__restrict__ gathered, float *__restrict__ full, int tp, int R,
+                                         int vl) {
+  // gathered [tp][R][vl] -> full [R][tp*vl]
+  const size_t n = (size_t)tp * R * vl;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    const size_t c = i % vl, r = (i / vl) % R, k = i / ((size_t)vl * R);
+    full[r * (size_t)tp * vl + k * vl + c] = gathered[i];
+  }
+}
+
+cudaError_t Engine::gather_full_logits(int R) {
+  const int r = nccl->AllGather(logits, gather_buf, (size_t)R * vocab_l, /*ncclFloat32*/ 7, comm, stream);
+  if (r != 0) { set_last_error(std::string("ncclAllGather: ") + nccl->GetErrorString(r)); return cudaErrorUnknown; }
+  interleave_logits_kernel<<<kNumSMs * 4, 256, 0, stream>>>(gather_buf, full_logits, tp_size, R, vocab_l);
+  kernel_launches += 2;
+  return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------------------------ prefill
+int Engine::prefill(int n, const int *slots, uint32_t *out_tokens, int *out_finish) {
+  if (shut) return fail(DIS_ERR_SHUTDOWN, "engine is shut down");
+  if (!loaded) return fail(DIS_ERR_MODEL_NOT_LOADED, "model not loaded");
+  if (n <= 0 || n > max_batch || !slots || !out_tokens || !out_finish) return fail(DIS_ERR_INVALID_ARGUMENT, "prefill: bad argument");
+  for (int i = 0; i < n; i++) {
+    if (slots[i] < 0 || slots[i] >= max_batch || !seqs[(size_t)slots[i]].used || seqs[(size_t)slots[i]].prefilled)
+      return fail(DIS_ERR_INVALID_ARGUMENT, "prefill: sequence missing or already prefilled");
+    for (int k = 0; k < i; k++) if (slots[k] == slots[i]) return fail(DIS_ERR_INVALID_ARGUMENT, "prefill: duplicate slot");
+  }
+  ENG_CUDA(cudaSetDevice(cfg.device));
+  ENG_CUDA(cudaEventRecord(ev0, stream));
+  // flatten (sequence, position) pairs and cut them into chunks of at most cap_tokens
+  int si = 0, sp = 0;  // next sequence index / position inside it
+  bool all_greedy = true;
+  for (int i = 0; i < n; i++) all_greedy = all_greedy && seqs[(size_t)slots[i]].temperature <= 0.f;
+  while (si < n) {
+    int T = 0, R = 0;
+    std::vector<int> owners;
+    while (si < n && T < cap_tokens) {
+      Sequence &s = seqs[(size_t)slots[si]];
+      const int total = (int)s.prompt.size();
+      const int take = std::min(total - sp, cap_tokens - T);
+      for (int k = 0; k < take; k++) {
+        meta.h<uint32_t>(meta.o_tokens)[T + k] = s.prompt[(size_t)(sp + k)];
+        meta.h<int>(meta.o_pos)[T + k] = sp + k;
+        meta.h<int>(meta.o_ptrow)[T + k] = slots[si];
+        meta.h<int>(meta.o_ctx)[T + k] = sp + k + 1;
+      }
+      T += take;
+      sp += take;
+      if (sp == total) {
+        meta.h<int>(meta.o_rowmap)[R] = T - 1;
+        meta.h<float>(meta.o_temp)[R] = s.temperature;
+        meta.h<float>(meta.o_topp)[R] = s.top_p;
+        meta.h<unsigned long long>(meta.o_seed)[R] = s.seed;
+        meta.h<unsigned long long>(meta.o_step)[R] = 0;
+        owners.push_back(si);
+        R++;
+        si++;
+        sp = 0;
+      }
+    }
+    ENG_CUDA(upload_step(T, R));
+    ENG_CUDA(enqueue_layers(T, 1));
+    if (R > 0) {
+      ENG_CUDA(enqueue_head(R, all_greedy));
+      ENG_CUDA(cudaMemcpyAsync(h_out_tokens, d_out_tokens, (size_t)R * 4, cudaMemcpyDeviceToHost, stream));
+    }
+    ENG_CUDA(cudaStreamSynchronize(stream));  // the pinned metadata block is reused by the next chunk
+    for (int r = 0; r < R; r++) out_tokens[owners[(size_t)r]] = h_out_tokens[r];
+    last_rows = R;
+  }
+  ENG_CUDA(cudaEventRecord(ev1, stream));
+  ENG_CUDA(cudaEventSynchronize(ev1));
+  float ms = 0.f;
+  ENG_CUDA(cudaEventElapsedTime(&ms, ev0, ev1));
+  last_step_ms = ms;
+  for (int i = 0; i < n; i++) {
+    Sequence &s = seqs[(size_t)slots[i]];
+    s.len = (int)s.prompt.size();
+    s.prefilled = true;
+    finish_check(s, out_tokens[i]);
+    out_finish[i] = s.finish;
+  }
+  return DIS_OK;
+}
+
+// ------------------------------------------------------------------------------------ decode
+int Engine::decode(int n, const int *slots, uint32_t *out_tokens, int *out_finish) {
+  if (shut) return fail(DIS_ERR_SHUTDOWN, "engine is shut down");
+  if (!loaded) return fail(DIS_ERR_MODEL_NOT_LOADED, "model not loaded");
+  if (n <= 0 || n > max_batch || !slots || !out_tokens || !out_finish) return fail(DIS_ERR_INVALID_ARGUMENT, "decode: bad argument");
+  for (int i = 0; i < n; i++) {
+    if (slots[i] < 0 || slots[i] >= max_batch) return fail(DIS_ERR_INVALID_ARGUMENT, "decode: slot out of range");
+    const Sequence &s = seqs[(size_t)slots[i]];
+    if (!s.used || !s.prefilled) return fail(DIS_ERR_INVALID_ARGUMENT, "decode: sequence missing or not prefilled");
+    for (int k = 0; k < i; k++) if (slots[k] == slots[i]) return fail(DIS_ERR_INVALID_ARGUMENT, "decode: duplicate slot");
+  }
+  ENG_CUDA(cudaSetDevice(cfg.device));
+  // Sequences that cannot take another token (finished, out of context, out of pages) are left out
+  // of the batch and reported individually: one bad request must not fail the batch
+  // (design.md:812-816, Property 22).
+  std::vector<int> live;
+  int max_ctx_b = 1;
+  bool all_greedy = true;
+  for (int i = 0; i < n; i++) {
+    Sequence &s = seqs[(size_t)slots[i]];
+    out_tokens[i] = 0;
+    if (s.finish != DIS_FINISH_NONE) { out_finish[i] = s.finish; continue; }
+    if (s.len + 1 > m.max_ctx || !ensure_pages(s, slots[i], s.len + 1)) { s.finish = DIS_FINISH_FAILED; out_finish[i] = s.finish; continue; }
+    const int r = (int)live.size();
+    meta.h<uint32_t>(meta.o_tokens)[r] = s.last_token;
+    meta.h<int>(meta.o_pos)[r] = s.len;
+    meta.h<int>(meta.o_ptrow)[r] = slots[i];
+    meta.h<int>(meta.o_ctx)[r] = s.len + 1;
+    meta.h<int>(meta.o_rowmap)[r] = r;
+    meta.h<float>(meta.o_temp)[r] = s.temperature;
+    meta.h<float>(meta.o_topp)[r] = s.top_p;
+    meta.h<unsigned long long>(meta.o_seed)[r] = s.seed;
+    meta.h<unsigned long long>(meta.o_step)[r] = (unsigned long long)s.generated;
+    all_greedy = all_greedy && s.temperature <= 0.f;
+    max_ctx_b = std::max(max_ctx_b, s.len + 1);
+    live.push_back(i);
+  }
+  const int T = (int)live.size();
+  if (T == 0) { last_rows = 0; return DIS_OK; }
+  const int n_splits = pick_attn_splits(T, max_ctx_b);
+  ENG_CUDA(cudaEventRecord(ev0, stream));
+  ENG_CUDA(upload_step(T, T));
+  if ((cfg.flags & DIS_FLAG_NO_GRAPH) || profiling) {
+    ENG_CUDA(enqueue_layers(T, n_splits));
+    ENG_CUDA(enqueue_head(T, all_greedy));
+    prof_mark(P_COUNT);
+  } else {
+    const uint64_t key = ((uint64_t)T << 9) | ((uint64_t)n_splits << 1) | (all_greedy ? 1u : 0u);
+    auto it = graphs.find(key);
+    if (it == graphs.end()) {
+      const uint64_t before = kernel_launches;
+      cudaGraph_t g = nullptr;
+      ENG_CUDA(cudaStreamBeginCapture(stream, cudaStreamCaptureModeThreadLocal));
+      cudaError_t e1 = enqueue_layers(T, n_splits);
+      cudaError_t e2 = e1 == cudaSuccess ? enqueue_head(T, all_greedy) : e1;
+      cudaError_t e3 = cudaStreamEndCapture(stream, &g);
+      if (e2 != cudaSuccess || e3 != cudaSuccess) {
+        if (g) cudaGraphDestroy(g);
+        cudaGetLastError();
+        healthy = false;
+        return fail(DIS_ERR_INFERENCE_FAILED, std::string("decode graph capture failed: ") + (g_last_error.empty() ? cudaGetErrorString(e2 != cudaSuccess ? e2 : e3) : g_last_error));
+      }
+      cudaGraphExec_t ex = nullptr;
+      ENG_CUDA(cudaGraphInstantiate(&ex, g, 0));
+      cudaGraphDestroy(g);
+      graph_launches[key] = kernel_launches - before;
+      kernel_launches = before;
+      it = graphs.emplace(key, ex).first;
+    }
+    ENG_CUDA(cudaGraphLaunch(it->second, stream));
+    kernel_launches += graph_launches[key];
+  }
+  ENG_CUDA(cudaMemcpyAsync(h_out_tokens, d_out_tokens, (size_t)T * 4, cudaMemcpyDeviceToHost, stream));
+  ENG_CUDA(cudaEventRecord(ev1, stream));
+  ENG_CUDA(cudaEventSynchronize(ev1));
+  float ms = 0.f;
+  ENG_CUDA(cudaEventElapsedTime(&ms, ev0, ev1));
+  last_step_ms = ms;
+  last_rows = T;
+  for (int r = 0; r < T; r++) {
+    const int i = live[(size_t)r];
+    Sequence &s = seqs[(size_t)slots[i]];
+    s.len += 1;  // the consumed token is now in the cache
+    out_tokens[i] = h_out_tokens[r];
+    finish_check(s, h_out_tokens[r]);
+    out_finish[i] = s.finish;
+  }
+  return DIS_OK;
+}
+
+void Engine::prof_mark(int cls) {
+  if (!profiling) return;
+  const size_t i = prof_marks.size();
+  if (i >= prof_events.size()) {
+    cudaEvent_t ev;
+    if (cudaEventCreate(&ev) != cudaSuccess) return;
+    prof_events.push_back(ev);
+  }
+  cudaEventRecord(prof_events[i], stream);
+  prof_marks.emplace_back(cls, (int)i);
+}
+
+// One eager decode step with a CUDA event before every kernel class; class_ms[P_COUNT] receives the
+// summed device time per class (event to next event), class_launches how often each class ran.
+int Engine::profile_decode(int n, const int *slots, uint32_t *out_tokens, int *out_finish, float *class_ms,
+                           int *class_launches) {
+  if (!class_ms || !class_launches) return fail(DIS_ERR_INVALID_ARGUMENT, "profile_decode: null output");
+  profiling = true;
+  prof_marks.clear();
+  const int rc = decode(n, slots, out_tokens, out_finish);
+  profiling = false;
+  if (rc != DIS_OK) return rc;
+  for (int c = 0; c < P_COUNT; c++) { class_ms[c] = 0.f; class_launches[c] = 0; }
+  for (size_t i = 0; i + 1 < prof_marks.size(); i++) {
+    float ms = 0.f;
+    ENG_CUDA(cudaEventElapsedTime(&ms, prof_events[(size_t)prof_marks[i].second], prof_events[(size_t)prof_marks[i + 1].second]));
+    class_ms[prof_marks[i].first] += ms;
+    class_launches[prof_marks[i].first] += 1;
+  }
+  return DIS_OK;
+}
+
+int Engine::last_logits_host(float *host, int rows) {
+  if (!host || rows <= 0 || rows > last_rows) return fail(DIS_ERR_INVALID_ARGUMENT, "last_logits: no such rows");
+  ENG_CUDA(cudaSetDevice(cfg.device));
+  if (tp_size == 1) {
+    ENG_CUDA(cudaMemcpyAsync(host, logits, (size_t)rows * m.vocab * 4, cudaMemcpyDeviceToHost, stream));
+  } else {
+    ENG_CUDA(gather_full_logits(last_rows));
+    ENG_CUDA(cudaMemcpyAsync(host, full_logits, (size_t)rows * m.vocab * 4, cudaMemcpyDeviceToHost, stream));
+  }
+  ENG_CUDA(cudaStreamSynchronize(stream));
+  return DIS_OK;
+}
+
+int Engine::status(dis_worker_status *o) {
+  if (!o) return fail(DIS_ERR_INVALID_ARGUMENT, "status: null output");
+  memset(o, 0, sizeof(*o));
+  int active = 0;
+  for (auto &s : seqs) if (s.used) active++;
+  o->active_sequences = active;
+  o->is_healthy = healthy && !shut;
+  o->memory_used = bytes_allocated;
+  size_t free_b = 0, total_b = 0;
+  if (cudaSetDevice(cfg.device) == cudaSuccess && cudaMemGetInfo(&free_b, &total_b) == cudaSuccess) o->memory_available = free_b;
+  o->kv_pages_total = n_pages;
+  o->kv_pages_free = (int64_t)free_pages.size();
+  o->tokens_generated = tokens_generated;
+  o->last_step_ms = last_step_ms;
+  o->kernel_launches = kernel_launches;
+  return DIS_OK;
+}
+
+}  // namespace dis

@@ -1,0 +1,143 @@
+// engine.h -- the decoder engine behind include/dis_engine.h (internal C++).
+#pragma once
+
+#include <map>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "../../include/dis_engine.h"
+#include "kernels.h"
+
+namespace dis {
+
+// tp.cpp: NCCL entry points resolved with dlopen (no link-time dependency; reuses the copy a host
+// process such as PyTorch has already loaded).
+struct NcclId { char bytes[128]; };
+struct NcclApi {
+  void *lib = nullptr;
+  int (*GetUniqueId)(NcclId *) = nullptr;
+  int (*CommInitRank)(void **, int, NcclId, int) = nullptr;
+  int (*CommDestroy)(void *) = nullptr;
+  int (*AllReduce)(const void *, void *, size_t, int, int, void *, cudaStream_t) = nullptr;
+  int (*AllGather)(const void *, void *, size_t, int, void *, cudaStream_t) = nullptr;
+  const char *(*GetErrorString)(int) = nullptr;
+};
+NcclApi *nccl_api(std::string *err);
+
+struct Sequence {
+  bool used = false;
+  bool prefilled = false;
+  std::vector<uint32_t> prompt;
+  int len = 0;             // tokens whose K/V are in the cache
+  uint32_t last_token = 0;  // sampled, not yet in the cache
+  int generated = 0;
+  int finish = DIS_FINISH_NONE;
+  int32_t max_tokens = 0;
+  float temperature = 0.f, top_p = 1.f;
+  uint64_t seed = 0;
+  std::vector<std::vector<uint32_t>> stop;  // stop sequences
+  std::vector<uint32_t> tail;               // last generated tokens, for stop matching
+  std::vector<int> pages;
+};
+
+// Host-side image of the per-step device metadata (one pinned block, one H2D copy per step).
+struct StepMeta {
+  int cap_tokens = 0, cap_rows = 0;
+  size_t bytes = 0;
+  uint8_t *host = nullptr;  // pinned
+  uint8_t *dev = nullptr;
+  // sections (offsets in bytes)
+  size_t o_tokens, o_pos, o_ptrow, o_ctx, o_rowmap, o_temp, o_topp, o_seed, o_step;
+  template <class T_> T_ *h(size_t off) { return reinterpret_cast<T_ *>(host + off); }
+  template <class T_> T_ *d(size_t off) { return reinterpret_cast<T_ *>(dev + off); }
+};
+
+struct Engine {
+  dis_engine_config cfg{};
+  dis_model_config m{};
+  int tp_rank = 0, tp_size = 1;
+  // local (per tensor-parallel rank) dimensions
+  int nh_l = 0, nkv_l = 0, qd_l = 0, kvd_l = 0, nqkv_l = 0, inter_l = 0, vocab_l = 0, vocab_off = 0;
+  int max_batch = 0, cap_tokens = 0, page_size = 0, max_pages = 0;
+  int64_t n_pages = 0;
+  cudaStream_t stream = nullptr;
+  bool own_stream = false;
+  bool loaded = false, shut = false, healthy = true;
+  std::mutex mu;
+  std::string last_error;
+  uint64_t bytes_allocated = 0, tokens_generated = 0, kernel_launches = 0;
+  double last_step_ms = 0.0;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+
+  // weights
+  uint16_t *embed = nullptr, *wqkv = nullptr, *wo = nullptr, *wgu = nullptr, *wdown = nullptr, *lm_head = nullptr;
+  float *attn_norm = nullptr, *mlp_norm = nullptr, *final_norm = nullptr;
+  TmaMap wqkv_map, wo_map, wgu_map, wdown_map, lm_map;
+  // activations
+  float *x = nullptr, *partial = nullptr, *logits = nullptr, *ar_buf = nullptr, *attn_scratch = nullptr;
+  float *full_logits = nullptr, *gather_buf = nullptr, *cand_val = nullptr, *cand_val_all = nullptr;
+  uint32_t *cand_tok = nullptr, *cand_tok_all = nullptr;
+  uint16_t *xn = nullptr, *q = nullptr, *attn = nullptr, *act = nullptr;
+  size_t partial_elems = 0, attn_scratch_elems = 0;
+  TmaMap xn_map[3], attn_map[3], act_map[3];  // box rows 32 / 64 / 128
+  uint32_t *d_out_tokens = nullptr, *h_out_tokens = nullptr;
+  // KV
+  uint16_t *kv_pool = nullptr;
+  size_t kv_layer_stride = 0;  // elements between layers in the pool
+  std::vector<int> free_pages;
+  int *d_page_table = nullptr, *h_page_table = nullptr;
+  bool pt_dirty = true;
+  float *rope_cos = nullptr, *rope_sin = nullptr;
+  StepMeta meta;
+  std::vector<Sequence> seqs;
+  int last_rows = 0;  // logits rows of the last call
+  // decode graphs keyed by (T, n_splits, all_greedy)
+  std::map<uint64_t, cudaGraphExec_t> graphs;
+  std::map<uint64_t, uint64_t> graph_launches;  // kernels per replay of each graph
+  // projection output still to be added to the residual when enqueue_layers returns
+  const float *pend_ptr = nullptr;
+  int pend_count = 0;
+  long long pend_str = 0;
+  // per-kernel-class timing of an eager step (dis_engine_profile_decode)
+  enum ProfClass { P_NORM = 0, P_QKV, P_ROPE, P_ATTN, P_OPROJ, P_GATEUP, P_DOWN, P_ALLREDUCE, P_HEAD_NORM, P_LM_HEAD, P_SAMPLE, P_COUNT };
+  bool profiling = false;
+  std::vector<cudaEvent_t> prof_events;  // pool
+  std::vector<std::pair<int, int>> prof_marks;  // (class, index of the event recorded BEFORE that class)
+  void prof_mark(int cls);
+  int profile_decode(int n, const int *slots, uint32_t *out_tokens, int *out_finish, float *class_ms, int *class_launches);
+  // tensor parallel
+  NcclApi *nccl = nullptr;
+  void *comm = nullptr;
+
+  ~Engine();
+  int fail(int code, const std::string &msg);
+  int init(const dis_engine_config *c);
+  int load_tensor(int kind, int layer, const void *host, int dtype);
+  int load_synthetic(uint64_t seed);
+  int read_tensor(int kind, int layer, uint16_t *host, size_t *n);
+  int finalize();
+  int seq_add(const uint32_t *prompt, int n, const dis_sampling_params *p, int *slot);
+  int seq_remove(int slot);
+  int prefill(int n, const int *slots, uint32_t *out_tokens, int *out_finish);
+  int decode(int n, const int *slots, uint32_t *out_tokens, int *out_finish);
+  int last_logits_host(float *host, int rows);
+  int status(dis_worker_status *out);
+
+  // internals
+  bool ensure_pages(Sequence &s, int slot, int n_tokens);
+  void release_pages(Sequence &s);
+  cudaError_t upload_step(int T, int R);
+  cudaError_t enqueue_layers(int T, int n_splits);
+  cudaError_t enqueue_head(int R, bool all_greedy);
+  cudaError_t linear_partial(const TmaMap *xmaps, const uint16_t *xptr, const TmaMap &wmap, const uint16_t *wptr,
+                             int w_row0, int T, int N, int K, int *split_out);
+  cudaError_t allreduce_partials(int split, int T);
+  cudaError_t gather_full_logits(int R);
+  int pick_attn_splits(int T, int max_ctx_in_batch) const;
+  void finish_check(Sequence &s, uint32_t tok);
+  struct TensorSlot { void *ptr; size_t rows, cols, ld, row0, col0, full_rows, full_cols; bool f32; };
+  bool tensor_slot(int kind, int layer, TensorSlot *out);
+};
+
+}  // namespace dis

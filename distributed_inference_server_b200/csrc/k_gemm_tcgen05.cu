@@ -1,0 +1,343 @@
+// k_gemm_tcgen05.cu -- the projection GEMM of the decoder, written for sm_100a:
+// TMA (cp.async.bulk.tensor) stages bf16 tiles into 128B-swizzled shared memory, one elected thread
+// issues tcgen05.mma with the fp32 accumulator in TMEM, four epilogue warps read it back with
+// tcgen05.ld.  No reference counterpart (the reference has no tensor code at all).
+//
+// Orientation ("swap-AB"): the WEIGHT tile is the MMA's A operand (128 output features = 128 TMEM
+// lanes) and the TOKEN tile is the B operand (UMMA N = 32/64/128 tokens = TMEM columns).  Decode
+// batches of 32..128 tokens therefore fill a whole 128-row MMA instead of padding M to 128, and the
+// weight matrix -- the only large operand -- is streamed exactly once per launch.
+//
+//   Y[t][n] = sum_k X[t][k] * W[n][k]         X: [T][K] bf16 (K-major B),  W: [N][K] bf16 (K-major A)
+//
+// Epilogues:
+//   partial : out[s][t][n] fp32, s = split-K slice (consumers sum the slices: add_rmsnorm,
+//             rope_kv_write, the sampler reads slice 0 of the lm_head logits)
+//   silu    : two accumulators (gate rows, up rows of the fused [2I][K] weight) ->
+//             act[t][n] = bf16(silu(gate) * up)
+//
+// Roofline: HBM-bound for T <= ~128 (AI ~ T flop/B against ~210 flop/B machine balance).
+// Algorithmic bytes per launch = 2*N*K (weights) + 2*T*K (activations) + 4*S*T*N (partials) or 2*T*I.
+#include <cuda.h>
+
+#include "kernels.h"
+
+namespace dis {
+
+// ------------------------------------------------------------------------------------ PTX wrappers
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  uint32_t ok;
+  do {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(bar), "r"(parity)
+        : "memory");
+  } while (!ok);
+}
+__device__ __forceinline__ void fence_barrier_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+
+__device__ __forceinline__ void tma_prefetch_desc(const void *map) {
+  asm volatile("prefetch.tensormap [%0];" ::"l"(map) : "memory");
+}
+// 2-D tile load: coordinates {c0 = element offset along the contiguous dim, c1 = row}
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const void *map, int c0, int c1, uint32_t bar,
+                                            uint64_t policy) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint"
+      " [%0], [%1, {%3, %4}], [%2], %5;"
+      ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1), "l"(policy)
+      : "memory");
+}
+constexpr uint64_t kEvictFirst = 0x12F0000000000000ull;  // stream-once data (weights)
+constexpr uint64_t kEvictLast = 0x14F0000000000000ull;   // data every CTA re-reads (activations)
+
+template <int kCols>
+__device__ __forceinline__ void tmem_alloc(uint32_t dst_smem) {
+  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(dst_smem), "n"(kCols) : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+template <int kCols>
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr) {
+  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "n"(kCols) : "memory");
+}
+// D[tmem] (+)= A[smem] * B[smem]^T, bf16 x bf16 -> fp32
+__device__ __forceinline__ void umma_bf16(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc,
+                                          uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// mbarrier arrives once all MMAs issued so far by this thread have completed
+__device__ __forceinline__ void umma_commit(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+// 32 lanes x 32 consecutive fp32 columns -> 32 registers per thread (thread = lane = accumulator row)
+__device__ __forceinline__ void tmem_ld_32x32(uint32_t taddr, uint32_t (&r)[32]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,"
+      "%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+        "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
+        "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
+        "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+// Shared-memory matrix descriptor, K-major operand in the canonical 128B-swizzle layout
+// (rows of 64 bf16 = 128 B, 8-row groups 1024 B apart): start>>4 | LBO=1 | SBO=64 | version=1 | SW128.
+__device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t smem_addr) {
+  return (uint64_t)((smem_addr >> 4) & 0x3FFFu) | (1ull << 16) | (64ull << 32) | (1ull << 46) | (2ull << 61);
+}
+// Instruction descriptor: D=f32, A=B=bf16, both K-major, M=128, N=kN.
+template <int kN>
+__host__ __device__ constexpr uint32_t umma_idesc() {
+  return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(kN >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+}
+
+// ------------------------------------------------------------------------------------ tile config
+constexpr int kBM = 128;  // output features per CTA (TMEM lanes)
+constexpr int kBK = 64;   // bf16 per 128-byte swizzle row
+constexpr int kGemmThreads = 192;  // warp 0 TMA, warp 1 MMA + TMEM alloc, warps 2-5 epilogue
+
+template <int BN, bool kDual>
+struct GemmCfg {
+  static constexpr int kABytes = kBM * kBK * 2;
+  static constexpr int kBBytes = BN * kBK * 2;
+  static constexpr int kStageBytes = (kDual ? 2 : 1) * kABytes + kBBytes;
+  static constexpr bool kTwoPerSM = kStageBytes * 3 <= 110 * 1024;
+  static constexpr int kStagesRaw = (kTwoPerSM ? 110 * 1024 : 220 * 1024) / kStageBytes;
+  static constexpr int kStages = kStagesRaw > 8 ? 8 : kStagesRaw;
+  static constexpr int kAccCols = (kDual ? 2 : 1) * BN;
+  static constexpr int kTmemCols = kAccCols <= 32 ? 32 : kAccCols <= 64 ? 64 : kAccCols <= 128 ? 128 : kAccCols <= 256 ? 256 : 512;
+  static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*barriers*/;
+};
+
+template <int BN, bool kDual>
+__global__ void __launch_bounds__(kGemmThreads)
+gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_constant__ CUtensorMap x_map,
+                    float *__restrict__ out_partial, uint16_t *__restrict__ out_act, int T, int N, int K,
+                    int w_row0, int up_row_off, int kb_per_split) {
+  using Cfg = GemmCfg<BN, kDual>;
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t bar_base = smem_base + Cfg::kStages * Cfg::kStageBytes;
+  // barriers: full[kStages], empty[kStages], tmem_full, then the TMEM base address word
+  auto full_bar = [&](int s) { return bar_base + 8u * s; };
+  auto empty_bar = [&](int s) { return bar_base + 8u * (Cfg::kStages + s); };
+  const uint32_t tmem_full_bar = bar_base + 8u * (2 * Cfg::kStages);
+  const uint32_t tmem_slot = tmem_full_bar + 8u;
+  auto a_tile = [&](int s) { return smem_base + s * Cfg::kStageBytes; };
+  auto a2_tile = [&](int s) { return a_tile(s) + Cfg::kABytes; };
+  auto b_tile = [&](int s) { return a_tile(s) + (kDual ? 2 : 1) * Cfg::kABytes; };
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int n0 = blockIdx.x * kBM;
+  const int t0 = blockIdx.y * BN;
+  const int num_kb = (K + kBK - 1) / kBK;
+  const int kb0 = blockIdx.z * kb_per_split;
+  const int kb1 = min(num_kb, kb0 + kb_per_split);
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&w_map);
+    tma_prefetch_desc(&x_map);
+    for (int s = 0; s < Cfg::kStages; s++) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
+    mbar_init(tmem_full_bar, 1);
+    fence_barrier_init();
+    fence_proxy_async();
+  }
+  if (warp == 1) tmem_alloc<Cfg::kTmemCols>(tmem_slot);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  uint32_t tmem_base;
+  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
+
+  if (warp == 0) {
+    // ===== TMA producer =====
+    if (lane == 0) {
+      int s = 0;
+      uint32_t phase = 0;
+      for (int kb = kb0; kb < kb1; kb++) {
+        mbar_wait(empty_bar(s), phase ^ 1u);
+        mbar_expect_tx(full_bar(s), Cfg::kStageBytes);
+        tma_load_2d(a_tile(s), &w_map, kb * kBK, w_row0 + n0, full_bar(s), kEvictFirst);
+        if (kDual) tma_load_2d(a2_tile(s), &w_map, kb * kBK, w_row0 + up_row_off + n0, full_bar(s), kEvictFirst);
+        tma_load_2d(b_tile(s), &x_map, kb * kBK, t0, full_bar(s), kEvictLast);
+        if (++s == Cfg::kStages) { s = 0; phase ^= 1u; }
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer (one thread) =====
+    if (lane == 0) {
+      constexpr uint32_t idesc = umma_idesc<BN>();
+      int s = 0;
+      uint32_t phase = 0;
+      for (int kb = kb0; kb < kb1; kb++) {
+        mbar_wait(full_bar(s), phase);
+        tc_fence_after();
+#pragma unroll
+        for (int k = 0; k < kBK / 16; k++) {
+          const uint32_t acc = (kb > kb0 || k > 0) ? 1u : 0u;
+          const uint64_t bd = umma_desc_sw128(b_tile(s) + k * 32);
+          umma_bf16(tmem_base, umma_desc_sw128(a_tile(s) + k * 32), bd, idesc, acc);
+          if (kDual) umma_bf16(tmem_base + BN, umma_desc_sw128(a2_tile(s) + k * 32), bd, idesc, acc);
+        }
+        umma_commit(empty_bar(s));  // slot reusable once these MMAs have read it
+        if (++s == Cfg::kStages) { s = 0; phase ^= 1u; }
+      }
+      umma_commit(tmem_full_bar);  // accumulator complete
+    }
+  } else {
+    // ===== epilogue: TMEM -> registers -> global =====
+    mbar_wait(tmem_full_bar, 0);
+    tc_fence_after();
+    const int quarter = warp & 3;  // a warp may only touch TMEM lanes [32*(warp%4), +32)
+    const int n = n0 + quarter * 32 + lane;
+    const uint32_t lane_addr = tmem_base + ((uint32_t)(quarter * 32) << 16);
+#pragma unroll 1
+    for (int c = 0; c < BN; c += 32) {
+      uint32_t g[32];
+      tmem_ld_32x32(lane_addr + c, g);
+      if (kDual) {
+        uint32_t u[32];
+        tmem_ld_32x32(lane_addr + BN + c, u);
+        tmem_ld_wait();
+        if (n < N) {
+#pragma unroll
+          for (int jj = 0; jj < 32; jj++) {
+            const int t = t0 + c + jj;
+            if (t < T) {
+              const float gv = __uint_as_float(g[jj]), uv = __uint_as_float(u[jj]);
+              out_act[(size_t)t * N + n] = float_to_bf16_bits((gv / (1.0f + expf(-gv))) * uv);
+            }
+          }
+        }
+      } else {
+        tmem_ld_wait();
+        if (n < N) {
+          float *o = out_partial + ((size_t)blockIdx.z * T + t0 + c) * N + n;
+#pragma unroll
+          for (int jj = 0; jj < 32; jj++)
+            if (t0 + c + jj < T) o[(size_t)jj * N] = __uint_as_float(g[jj]);
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc<Cfg::kTmemCols>(tmem_base);
+}
+
+// ------------------------------------------------------------------------------------ host side
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                  const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  if (!fn) {
+    void *p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = (EncodeTiledFn)p;
+  }
+  return fn;
+}
+
+static_assert(sizeof(TmaMap) == sizeof(CUtensorMap), "TmaMap must mirror CUtensorMap");
+
+cudaError_t make_tma_map_2d(TmaMap *out, const void *base, uint64_t rows, uint64_t cols, uint32_t box_rows) {
+  EncodeTiledFn fn = get_encode_fn();
+  if (!fn) { set_last_error("cuTensorMapEncodeTiled is not available from this driver"); return cudaErrorNotSupported; }
+  if (cols % 8 != 0 || ((uintptr_t)base & 15u)) { set_last_error("TMA map: row length must be a multiple of 8 bf16 and base 16-byte aligned"); return cudaErrorInvalidValue; }
+  if (box_rows == 0 || box_rows > 256) { set_last_error("TMA map: box rows must be 1..256"); return cudaErrorInvalidValue; }
+  const cuuint64_t dims[2] = {cols, rows};
+  const cuuint64_t strides[1] = {cols * 2};
+  const cuuint32_t box[2] = {(cuuint32_t)kBK, box_rows};
+  const cuuint32_t estr[2] = {1, 1};
+  const CUresult r = fn(reinterpret_cast<CUtensorMap *>(out), CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void *>(base),
+                        dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                        CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) { set_last_error("cuTensorMapEncodeTiled failed with CUresult " + std::to_string((int)r)); return cudaErrorInvalidValue; }
+  return cudaSuccess;
+}
+
+int gemm_token_tile(int T) { return T <= 32 ? 32 : (T <= 64 ? 64 : 128); }
+
+// Split-K factor: enough CTAs to keep every SM streaming (two CTAs per SM), each with >= 4 k-blocks.
+int gemm_pick_split_k(int T, int N, int K) {
+  const int bn = gemm_token_tile(T);
+  const int tiles = ((N + kBM - 1) / kBM) * ((T + bn - 1) / bn);
+  const int num_kb = (K + kBK - 1) / kBK;
+  if (tiles >= kNumSMs) return 1;
+  int s = (2 * kNumSMs) / tiles;
+  s = s > 16 ? 16 : s;
+  s = s > num_kb / 4 ? num_kb / 4 : s;
+  if (s < 1) s = 1;
+  const int per = (num_kb + s - 1) / s;
+  return (num_kb + per - 1) / per;  // no empty slices
+}
+
+template <int BN, bool kDual>
+static cudaError_t gemm_launch(const TmaMap &w_map, const TmaMap &x_map, float *out, uint16_t *act, int T, int N,
+                               int K, int w_row0, int up_off, int split_k, cudaStream_t st) {
+  using Cfg = GemmCfg<BN, kDual>;
+  auto kern = gemm_tcgen05_kernel<BN, kDual>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    DIS_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
+    attr_set = true;
+  }
+  const int num_kb = (K + kBK - 1) / kBK;
+  const int per = (num_kb + split_k - 1) / split_k;
+  if ((num_kb + per - 1) / per != split_k) { set_last_error("gemm: split_k leaves an empty K slice; use gemm_pick_split_k"); return cudaErrorInvalidValue; }
+  dim3 grid((N + kBM - 1) / kBM, (T + BN - 1) / BN, split_k);
+  kern<<<grid, kGemmThreads, Cfg::kSmemBytes, st>>>(*reinterpret_cast<const CUtensorMap *>(&w_map),
+                                                    *reinterpret_cast<const CUtensorMap *>(&x_map), out, act, T, N, K,
+                                                    w_row0, up_off, per);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_gemm_partial(const TmaMap &w_map, const TmaMap &x_map, float *out, int T, int N, int K,
+                                int w_row0, int split_k, cudaStream_t st) {
+  if (T <= 0) return cudaSuccess;
+  if (split_k < 1) { set_last_error("gemm: split_k must be >= 1"); return cudaErrorInvalidValue; }
+  switch (gemm_token_tile(T)) {
+    case 32: return gemm_launch<32, false>(w_map, x_map, out, nullptr, T, N, K, w_row0, 0, split_k, st);
+    case 64: return gemm_launch<64, false>(w_map, x_map, out, nullptr, T, N, K, w_row0, 0, split_k, st);
+    default: return gemm_launch<128, false>(w_map, x_map, out, nullptr, T, N, K, w_row0, 0, split_k, st);
+  }
+}
+
+cudaError_t launch_gemm_silu(const TmaMap &w_map, const TmaMap &x_map, uint16_t *act, int T, int I, int K,
+                             int w_row0, cudaStream_t st) {
+  if (T <= 0) return cudaSuccess;
+  switch (gemm_token_tile(T)) {
+    case 32: return gemm_launch<32, true>(w_map, x_map, nullptr, act, T, I, K, w_row0, I, 1, st);
+    case 64: return gemm_launch<64, true>(w_map, x_map, nullptr, act, T, I, K, w_row0, I, 1, st);
+    default: return gemm_launch<128, true>(w_map, x_map, nullptr, act, T, I, K, w_row0, I, 1, st);
+  }
+}
+
+}  // namespace dis

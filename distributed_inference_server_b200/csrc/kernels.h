@@ -1,0 +1,52 @@
+// kernels.h -- host-side launchers of the sm_100a kernels (internal; the C ABI is include/dis_engine.h).
+#pragma once
+#include "common.cuh"
+
+namespace dis {
+
+// k_elementwise.cu
+cudaError_t launch_add_rmsnorm(float *x, const uint32_t *tokens, const uint16_t *embed, const float *partial,
+                               int n_partial, long long partial_stride, const float *gain, uint16_t *xn,
+                               const int *row_map, int T, int H, float eps, cudaStream_t st);
+cudaError_t launch_reduce_partials(const float *partial, int n_partial, long long stride, float *out, long long n,
+                                   cudaStream_t st);
+cudaError_t launch_rope_kv_write(const float *qkv, int n_partial, long long partial_stride, uint16_t *q,
+                                 uint16_t *kv_pool, const int *page_table, int max_pages, const int *pt_row,
+                                 const int *pos, const float *rope_cos, const float *rope_sin, int T,
+                                 int n_heads, int n_kv, int d, int page_size, cudaStream_t st);
+cudaError_t launch_sample(const float *logits, long long ld, int T, int V, const float *temperature,
+                          const float *top_p, const unsigned long long *seeds, const unsigned long long *steps,
+                          uint32_t *out_tokens, int vocab_offset, float *out_val, cudaStream_t st);
+cudaError_t launch_argmax_merge(const float *cand_val, const uint32_t *cand_tok, int tp, int T, uint32_t *out,
+                                cudaStream_t st);
+cudaError_t launch_synth_bf16(uint16_t *dst, size_t n, unsigned long long seed, int kind, int layer, float amp,
+                              float offset, size_t idx0, size_t row_len, size_t src_ld, size_t src_col0,
+                              cudaStream_t st);
+cudaError_t launch_bf16_to_f32(const uint16_t *src, float *dst, size_t n, cudaStream_t st);
+
+// k_gemv.cu : out[t][n] = sum_k X[t][k] W[n][k]  (T <= kGemvMaxT per launch; launcher loops)
+constexpr int kGemvMaxT = 4;
+cudaError_t launch_gemv(const uint16_t *X, const uint16_t *W, float *out, int T, int N, int K, cudaStream_t st);
+cudaError_t launch_gemv_silu(const uint16_t *X, const uint16_t *Wgu, uint16_t *act, int T, int I, int K,
+                             cudaStream_t st);
+
+// k_attn_paged.cu
+size_t attn_scratch_elems(int T, int n_heads, int d, int n_splits);
+cudaError_t launch_attn_paged(const uint16_t *q, const uint16_t *kv_pool, const int *page_table, int max_pages,
+                              const int *pt_row, const int *ctx, uint16_t *out, float *scratch, int n_splits,
+                              int T, int n_heads, int n_kv, int d, int page_size, cudaStream_t st);
+
+// k_gemm_tcgen05.cu
+// A 2-D bf16 row-major [rows][cols] tensor map with a {64, box_rows} box and 128-byte swizzle.
+struct TmaMap { alignas(64) unsigned char bytes[128]; };
+cudaError_t make_tma_map_2d(TmaMap *out, const void *base, uint64_t rows, uint64_t cols, uint32_t box_rows);
+int gemm_token_tile(int T);  // 32 / 64 / 128: the UMMA N used for T tokens
+// out[S][T][N] fp32 partials.  w_row0: first row of W's map to use (stacked per-layer weights).
+cudaError_t launch_gemm_partial(const TmaMap &w_map, const TmaMap &x_map, float *out, int T, int N, int K,
+                                int w_row0, int split_k, cudaStream_t st);
+// act[T][I] = bf16(silu(gate) * up); gate rows at w_row0, up rows at w_row0 + I.
+cudaError_t launch_gemm_silu(const TmaMap &w_map, const TmaMap &x_map, uint16_t *act, int T, int I, int K,
+                             int w_row0, cudaStream_t st);
+int gemm_pick_split_k(int T, int N, int K);
+
+}  // namespace dis

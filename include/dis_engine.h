@@ -1,0 +1,244 @@
+/*
+ * dis_engine.h -- C ABI of the B200-native decoder forward path for
+ * its-me-ojas/distributed-inference-server.
+ *
+ * The reference has no FFI boundary today (no extern "C", no build.rs).  Its only seam
+ * for this path is the spec'd `InferenceWorker` trait (.kiro/specs/distributed-inference-server/
+ * design.md:334-342), whose implementing file is empty (crates/inference/src/worker.rs:1).  Every
+ * entry point below is what a Rust `impl InferenceWorker` in crates/inference would bind through a
+ * `-sys` shim; each cites the reference item it serves.  INTEGRATION.md shows that binding.
+ *
+ * Conventions
+ *  - Plain C: pointers, sizes, PODs.  No torch / C++ types.  Handles are opaque.
+ *  - The caller owns every host buffer passed in or out (Vec<u32> in, Vec<u32> out:
+ *    design.md:244,355); the engine owns all device memory.
+ *  - Every function returns a dis_status code.  The codes mirror `WorkerError`
+ *    (crates/core/src/error.rs:115-128); the `String` payload of `InferenceFailed` is
+ *    dis_engine_last_error().
+ *  - The trait is `Send + Sync` with `&self` methods (design.md:335-338): calls may come from any
+ *    host thread; the engine serialises them per handle.  Blocking; never calls back.
+ *  - There is no CPU fallback: every compute entry point needs a CUDA device of compute
+ *    capability 10.0 and fails with DIS_ERR_INFERENCE_FAILED otherwise.
+ */
+#ifndef DIS_ENGINE_H_
+#define DIS_ENGINE_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DIS_API __attribute__((visibility("default")))
+#define DIS_ABI_VERSION 1
+
+/* ---- status codes: WorkerError, crates/core/src/error.rs:115-128 ------------------------------ */
+typedef enum dis_status {
+  DIS_OK = 0,
+  DIS_ERR_MODEL_NOT_LOADED = 1, /* WorkerError::ModelNotLoaded  error.rs:118 */
+  DIS_ERR_INFERENCE_FAILED = 2, /* WorkerError::InferenceFailed error.rs:121 (message: last_error) */
+  DIS_ERR_SHUTDOWN = 3,         /* WorkerError::Shutdown        error.rs:124 */
+  DIS_ERR_OUT_OF_MEMORY = 4,    /* WorkerError::OutOfMemory     error.rs:127 */
+  DIS_ERR_INVALID_ARGUMENT = 5  /* caller bug; a Rust shim maps it to InferenceFailed */
+} dis_status;
+
+/* ---- FinishReason: crates/core/src/models.rs:26-32 (plus "still running") ---------------------- */
+typedef enum dis_finish_reason {
+  DIS_FINISH_NONE = 0,          /* not finished */
+  DIS_FINISH_STOP = 1,          /* FinishReason::Stop         (EOS token) */
+  DIS_FINISH_LENGTH = 2,        /* FinishReason::Length       (max_tokens or context limit) */
+  DIS_FINISH_STOP_SEQUENCE = 3, /* FinishReason::StopSequence */
+  DIS_FINISH_FAILED = 4         /* per-sequence failure (design.md:812-816, Property 22) */
+} dis_finish_reason;
+
+/* ---- tensors of the model (for weight loading) -------------------------------------------------- */
+typedef enum dis_tensor_kind {
+  DIS_T_EMBED = 0, DIS_T_ATTN_NORM = 1, DIS_T_WQ = 2, DIS_T_WK = 3, DIS_T_WV = 4, DIS_T_WO = 5,
+  DIS_T_MLP_NORM = 6, DIS_T_WGATE = 7, DIS_T_WUP = 8, DIS_T_WDOWN = 9, DIS_T_FINAL_NORM = 10,
+  DIS_T_LM_HEAD = 11
+} dis_tensor_kind;
+
+typedef enum dis_dtype { DIS_F32 = 0, DIS_BF16 = 1 } dis_dtype;
+
+/* Llama decoder dimensions.  The reference names the model family only ("Llama-3 8B or compatible",
+ * requirements.md:5); ModelInfo is named but never defined (design.md:341). */
+typedef struct dis_model_config {
+  int32_t vocab, hidden, layers, n_heads, n_kv_heads, head_dim, inter, max_ctx;
+  float rope_theta, rms_eps;
+} dis_model_config;
+
+/* Engine configuration: WorkerConfig (design.md:316-322) plus what it lacks for a GPU path.
+ * `Quantization` (design.md:326-332) has no bf16 variant; this engine is bf16 weights / fp32
+ * accumulate only. */
+#define DIS_FLAG_NO_GRAPH 1u   /* do not capture the decode step in a CUDA graph */
+#define DIS_FLAG_FORCE_GEMV 2u /* debugging: run every projection through the GEMV kernel */
+typedef struct dis_engine_config {
+  dis_model_config model;
+  int32_t device;              /* CUDA ordinal (WorkerConfig.gpu_layers has no meaning here) */
+  int32_t tp_rank, tp_size;    /* Megatron tensor parallel position; 0,1 = single GPU */
+  int32_t max_batch;           /* concurrent sequences (requirements.md:46 default 32) */
+  int32_t max_step_tokens;     /* tokens per forward pass (prefill chunk); 0 = default */
+  int32_t page_size;           /* tokens per KV page; 0 = 64 */
+  int64_t kv_pages;            /* KV pages to allocate; 0 = derive from kv_mem_fraction */
+  float kv_mem_fraction;       /* of free device memory after weights; 0 = 0.85 */
+  uint32_t flags;
+  int32_t eos_token;           /* -1 = none */
+  void *stream;                /* cudaStream_t to run on; NULL = engine-owned stream */
+  uint8_t nccl_id[128];        /* ncclUniqueId from dis_tp_unique_id when tp_size > 1 */
+} dis_engine_config;
+
+/* InferenceParams: design.md:666-671, fed from GenerateRequest.{max_tokens,temperature,top_p,
+ * stop_sequences} (models.rs:60-74).  temperature 0 = greedy (0.0 is valid: validator.rs:22).
+ * There is no top_k in the reference's request model. */
+typedef struct dis_sampling_params {
+  int32_t max_tokens;
+  float temperature;
+  float top_p;
+  uint64_t seed;
+  const uint32_t *stop_tokens; /* concatenated stop sequences (Vec<Vec<u32>>) */
+  const int32_t *stop_lens;    /* length of each */
+  int32_t n_stop;
+} dis_sampling_params;
+
+/* WorkerStatus: design.md:290-297. */
+typedef struct dis_worker_status {
+  int32_t active_sequences;    /* WorkerStatus.active_batches, at sequence granularity */
+  int32_t is_healthy;
+  uint64_t memory_used;        /* bytes of device memory held by this engine */
+  uint64_t memory_available;   /* bytes still free on the device */
+  int64_t kv_pages_total, kv_pages_free;
+  uint64_t tokens_generated;   /* BatchResult.tokens_generated, cumulative (design.md:349) */
+  double last_step_ms;         /* device time of the last prefill/decode call (CUDA events) */
+  uint64_t kernel_launches;    /* kernels launched by this engine so far (incl. graph replays) */
+} dis_worker_status;
+
+typedef struct dis_engine dis_engine;
+
+/* ---- lifecycle: InferenceWorker::initialize / shutdown (design.md:337,339) --------------------- */
+DIS_API int dis_abi_version(void);
+DIS_API int dis_engine_create(const dis_engine_config *cfg, dis_engine **out);
+DIS_API int dis_engine_destroy(dis_engine *e);
+/* Global message for failures that have no handle yet (create). */
+DIS_API const char *dis_last_error(void);
+DIS_API const char *dis_engine_last_error(dis_engine *e);
+
+/* Weights.  WorkerConfig.model_path (design.md:317) is resolved by the host: it hands every tensor
+ * over as a full, unsharded [out,in] row-major matrix and the engine keeps its tensor-parallel
+ * slice.  `layer` is ignored for EMBED / FINAL_NORM / LM_HEAD. */
+DIS_API int dis_engine_load_tensor(dis_engine *e, int kind, int layer, const void *host, int dtype);
+/* Random-init weights generated on the device from a counter-based hash (benchmarks, tests). */
+DIS_API int dis_engine_load_synthetic(dis_engine *e, uint64_t seed);
+/* Copy the engine's (sharded) copy of a tensor back as bf16 bit patterns; *n_elems in = capacity. */
+DIS_API int dis_engine_read_tensor(dis_engine *e, int kind, int layer, uint16_t *host, size_t *n_elems);
+/* After this the model counts as loaded; compute calls before it return MODEL_NOT_LOADED. */
+DIS_API int dis_engine_finalize(dis_engine *e);
+
+/* ---- InferenceWorker::infer, step-wise (design.md:338; InferenceBatch design.md:241-248) -------- *
+ * Step-wise so that the host can emit TokenEvent::Token per token (models.rs:272-277, design.md:265),
+ * drop a sequence when its client disconnects (requirements.md:85) and admit new sequences between
+ * decode steps. */
+/* Register one request: prompt tokens + params.  Reserves KV pages for the prompt. */
+DIS_API int dis_engine_seq_add(dis_engine *e, const uint32_t *prompt, int32_t n_prompt,
+                               const dis_sampling_params *params, int32_t *out_slot);
+DIS_API int dis_engine_seq_remove(dis_engine *e, int32_t slot);
+/* Run the prompts of `n` registered sequences and sample their first token.
+ * out_tokens[n], out_finish[n] (dis_finish_reason). */
+DIS_API int dis_engine_prefill(dis_engine *e, int32_t n, const int32_t *slots, uint32_t *out_tokens,
+                               int32_t *out_finish);
+/* One decode step: each listed sequence consumes its last sampled token and yields the next. */
+DIS_API int dis_engine_decode(dis_engine *e, int32_t n, const int32_t *slots, uint32_t *out_tokens,
+                              int32_t *out_finish);
+/* dis_engine_decode run eagerly with a CUDA event before every kernel class (no reference counterpart;
+ * it is how bench.py times the dominant kernel on the stream it runs on).  class_ms / class_launches
+ * have DIS_PROF_COUNT entries: device milliseconds and launches per class for this one step. */
+enum { DIS_PROF_NORM = 0, DIS_PROF_QKV, DIS_PROF_ROPE, DIS_PROF_ATTN, DIS_PROF_OPROJ, DIS_PROF_GATEUP, DIS_PROF_DOWN,
+       DIS_PROF_ALLREDUCE, DIS_PROF_HEAD_NORM, DIS_PROF_LM_HEAD, DIS_PROF_SAMPLE, DIS_PROF_COUNT };
+DIS_API int dis_engine_profile_decode(dis_engine *e, int32_t n, const int32_t *slots, uint32_t *out_tokens,
+                                      int32_t *out_finish, float *class_ms, int32_t *class_launches);
+/* Logits of the last prefill/decode call, row i = i-th listed sequence, [n][vocab] fp32 (gathered
+ * across tensor-parallel ranks). For parity tests and TokenEvent.logprob (models.rs:276). */
+DIS_API int dis_engine_last_logits(dis_engine *e, float *host, int32_t n_rows);
+
+/* ---- InferenceWorker::status / model_info (design.md:340-341) ---------------------------------- */
+DIS_API int dis_engine_status(dis_engine *e, dis_worker_status *out);
+DIS_API int dis_engine_model_info(dis_engine *e, dis_model_config *out);
+
+/* ---- tensor parallel bootstrap (no reference counterpart: the reference specifies replicas only,
+ * requirements.md:100-110; north_star asks for Megatron TP) ------------------------------------- */
+DIS_API int dis_tp_unique_id(uint8_t out[128]);
+
+/* ---- InferenceWorker::infer as one blocking call (design.md:338,345-360) ------------------------ *
+ * The C++ InferenceWorker mirror (csrc/worker.hpp) exported for non-C++ hosts.  input_ids is the
+ * padded [n][stride] batch of InferenceBatch (design.md:244), lens[b] the unpadded length
+ * (BatchedRequest.original_length, design.md:261).  out_tokens is [n][max_new_cap].
+ * on_token (optional) is called once per generated token, in step order, from the calling thread
+ * (TokenEvent::Token, models.rs:272-277); returning non-zero drops that sequence. */
+typedef int (*dis_token_callback)(void *user, int32_t request_index, uint32_t token, int32_t index,
+                                  int32_t finish_reason);
+typedef struct dis_batch_result {
+  double inference_ms;          /* BatchResult.inference_time  design.md:348 */
+  double ttft_ms;               /* time to first token of the batch (prefill) */
+  uint64_t tokens_generated;    /* BatchResult.tokens_generated design.md:349 */
+} dis_batch_result;
+DIS_API int dis_worker_infer(dis_engine *e, int32_t n, const uint32_t *input_ids, int32_t stride,
+                             const int32_t *lens, const dis_sampling_params *params /*[n]*/,
+                             uint32_t *out_tokens, int32_t max_new_cap, int32_t *out_lens,
+                             int32_t *out_finish, dis_batch_result *result, dis_token_callback on_token,
+                             void *user);
+
+/* ---- kernel-level entry points ------------------------------------------------------------------ *
+ * One per hand-written kernel, taking DEVICE pointers and a cudaStream_t (NULL = default stream).
+ * They exist so that parity tests can drive each kernel through the C ABI; the reference has no
+ * counterpart for any of them ("None").  bf16 buffers are uint16_t bit patterns. */
+
+/* x[T][H] fp32 residual.  If tokens != NULL: v = embed[tokens[r]] (bf16 table); else
+ * v = x[r] + sum_s partial[s*partial_stride + r*H ...] (n_partial may be 0), with r = row_map ? row_map[t] : t.
+ * Then xn[t] = bf16(v * rsqrt(mean v^2 + eps) * gain).  Without row_map, x[t] = v is written back;
+ * with row_map (the rows that need logits) x is left untouched and xn rows are compact. */
+DIS_API int dis_k_add_rmsnorm(float *x, const uint32_t *tokens, const uint16_t *embed, const float *partial,
+                              int32_t n_partial, int64_t partial_stride, const float *gain, uint16_t *xn,
+                              const int32_t *row_map, int32_t T, int32_t H, float eps, void *stream);
+/* Y = X[T][K] * W[N][K]^T, bf16 in, fp32 out as split-K partials out[S][T][N] (S chosen by the
+ * caller, 1 = plain result).  tcgen05/TMEM/TMA kernel. */
+DIS_API int dis_k_gemm(const uint16_t *X, const uint16_t *W, float *out, int32_t T, int32_t N, int32_t K,
+                       int32_t split_k, void *stream);
+/* The split-K factor the engine uses for a [T][K] x [N][K]^T projection (never leaves a slice empty). */
+DIS_API int dis_k_gemm_pick_split(int32_t T, int32_t N, int32_t K);
+/* act[T][I] = bf16(silu(X*Wg^T) * (X*Wu^T)); Wgu is [2I][K]: gate rows then up rows. */
+DIS_API int dis_k_gemm_silu(const uint16_t *X, const uint16_t *Wgu, uint16_t *act, int32_t T, int32_t I,
+                            int32_t K, void *stream);
+/* Same contracts on the bandwidth-bound CUDA-core GEMV path (batch-1 decode). */
+DIS_API int dis_k_gemv(const uint16_t *X, const uint16_t *W, float *out, int32_t T, int32_t N, int32_t K,
+                       void *stream);
+DIS_API int dis_k_gemv_silu(const uint16_t *X, const uint16_t *Wgu, uint16_t *act, int32_t T, int32_t I,
+                            int32_t K, void *stream);
+/* qkv partials [S][T][(nh+2nkv)*d] fp32 -> RoPE(q) bf16 [T][nh*d]; RoPE(k), v -> KV pages.
+ * Page pool layout (per layer): [page][2 (K,V)][nkv][page_size][d] bf16.  page_table is
+ * [rows][max_pages]; token t uses row pt_row[t] and position pos[t]. */
+DIS_API int dis_k_rope_kv_write(const float *qkv, int32_t n_partial, int64_t partial_stride, uint16_t *q,
+                                uint16_t *kv_pool, const int32_t *page_table, int32_t max_pages,
+                                const int32_t *pt_row, const int32_t *pos, const float *rope_cos,
+                                const float *rope_sin, int32_t T, int32_t n_heads, int32_t n_kv,
+                                int32_t d, int32_t page_size, void *stream);
+/* Attention of each query token over its paged history (ctx[t] tokens, causal by construction).
+ * out bf16 [T][nh*d].  n_splits > 1 uses `scratch` (fp32, dis_k_attn_scratch_elems()) for the
+ * split-KV partials and a combine pass. */
+DIS_API size_t dis_k_attn_scratch_elems(int32_t T, int32_t n_heads, int32_t d, int32_t n_splits);
+DIS_API int dis_k_attn_paged(const uint16_t *q, const uint16_t *kv_pool, const int32_t *page_table,
+                             int32_t max_pages, const int32_t *pt_row, const int32_t *ctx, uint16_t *out,
+                             float *scratch, int32_t n_splits, int32_t T, int32_t n_heads, int32_t n_kv,
+                             int32_t d, int32_t page_size, void *stream);
+/* Sampler over fp32 logits [T][V] (row stride ld): temperature 0 -> argmax, lowest index wins ties;
+ * else nucleus sampling as oracle/llama_oracle.c states it.  out_tokens[T]. */
+DIS_API int dis_k_sample(const float *logits, int64_t ld, int32_t T, int32_t V, const float *temperature,
+                         const float *top_p, const uint64_t *seeds, const uint64_t *steps,
+                         uint32_t *out_tokens, void *stream);
+/* Synthetic weights: dst[i] = bf16(offset + (2u-1)*amp), u from the counter hash (seed, kind, layer, i). */
+DIS_API int dis_k_synth_bf16(uint16_t *dst, size_t n, uint64_t seed, int32_t kind, int32_t layer, float amp,
+                             float offset, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DIS_ENGINE_H_ */

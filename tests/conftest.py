@@ -27,3 +27,13 @@ def pytest_collection_modifyitems(config, items):
     for it in items:
         if "gpu" in it.keywords:
             it.add_marker(skip)
+
+
+@pytest.fixture(autouse=True)
+def _release_device_tensors():
+    yield
+    try:
+        from tests import _gpu_util
+        _gpu_util._KEEP.clear()
+    except Exception:
+        pass

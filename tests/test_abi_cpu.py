@@ -1,0 +1,69 @@
+"""CPU-side checks of the boundary: the library loads, exports every symbol include/dis_engine.h
+declares, the ctypes structs match the header's layout, and compute calls fail loudly without a GPU
+(there is no CPU fallback)."""
+import ctypes as C
+import os
+import re
+import subprocess
+
+import pytest
+
+from distributed_inference_server_b200 import binding as B
+from distributed_inference_server_b200 import Engine, ModelShape, WorkerConfig, WorkerError
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+HEADER = os.path.join(ROOT, "include", "dis_engine.h")
+
+
+def declared_symbols():
+    src = open(HEADER).read()
+    return sorted(set(re.findall(r"DIS_API\s+[\w\s\*]+?\b(dis_\w+)\s*\(", src)))
+
+
+def test_library_exports_every_declared_symbol():
+    lib = B.load()
+    names = declared_symbols()
+    assert len(names) >= 25
+    for n in names:
+        assert hasattr(lib, n), n
+        assert n in B.PROTOTYPES, f"binding.py lacks a prototype for {n}"
+    assert lib.dis_abi_version() == 1
+
+
+def test_struct_layout_matches_header(tmp_path):
+    probe = tmp_path / "probe.c"
+    probe.write_text('#include <stdio.h>\n#include "dis_engine.h"\nint main(){printf("%zu %zu %zu %zu %zu %zu\\n",'
+                     'sizeof(dis_model_config),sizeof(dis_engine_config),sizeof(dis_sampling_params),'
+                     'sizeof(dis_worker_status),sizeof(dis_batch_result),offsetof(dis_engine_config,nccl_id));return 0;}\n')
+    exe = tmp_path / "probe"
+    subprocess.run(["gcc", "-I", os.path.join(ROOT, "include"), str(probe), "-o", str(exe)], check=True)
+    sizes = [int(x) for x in subprocess.run([str(exe)], capture_output=True, text=True, check=True).stdout.split()]
+    assert sizes == [C.sizeof(B.ModelConfig), C.sizeof(B.EngineConfig), C.sizeof(B.SamplingParams),
+                     C.sizeof(B.WorkerStatus), C.sizeof(B.BatchResult), B.EngineConfig.nccl_id.offset]
+
+
+def test_header_is_plain_c():
+    r = subprocess.run(["gcc", "-std=c99", "-pedantic", "-Wall", "-Werror", "-fsyntax-only", "-x", "c", HEADER],
+                       capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+
+
+def test_no_cpu_fallback():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    with pytest.raises(WorkerError) as ei:
+        Engine(WorkerConfig(ModelShape(1024, 256, 2, 4, 1, 128, 512, 128)))
+    assert "no CUDA device" in str(ei.value)
+    lib = B.load()
+    assert lib.dis_k_gemv(None, None, None, 1, 8, 8, None) == B.ERR_INFERENCE_FAILED
+    assert b"no CPU fallback" in lib.dis_last_error()
+
+
+def test_product_never_imports_the_oracle():
+    pkg = os.path.join(ROOT, "distributed_inference_server_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cpp", ".h", ".hpp", ".cuh")):
+                text = open(os.path.join(dirpath, f), errors="ignore").read()
+                assert "liboracle" not in text and "from oracle" not in text and "import oracle" not in text, f
