@@ -54,45 +54,55 @@ def model_bytes(shape, tp):
 
 # --------------------------------------------------------------------------------------- clocks
 class ClockSampler:
-    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
-         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    """Polls NVML (SM clock, power, clock-event reasons) every 20 ms on a thread; only samples taken
+    between mark_start() and mark_end() -- the timed region -- are summarised."""
+    REASONS = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown", 0x4: "sw_power_cap"}
 
     def __init__(self, index):
-        self.index = index
-        self.rows = []
-        self.proc = None
+        self.index, self.rows, self.stop_flag, self.t0, self.t1, self.thread, self.max = index, [], False, None, None, None, None
 
     def start(self):
         try:
-            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
-                                          "--format=csv,noheader,nounits", "-lms", "100"],
-                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
-            threading.Thread(target=self._read, daemon=True).start()
+            import pynvml
+            pynvml.nvmlInit()
+            h = pynvml.nvmlDeviceGetHandleByIndex(self.index)
+            self.max = pynvml.nvmlDeviceGetMaxClockInfo(h, pynvml.NVML_CLOCK_SM)
         except Exception:
-            self.proc = None
+            return
 
-    def _read(self):
-        for line in self.proc.stdout:
-            self.rows.append(line.strip())
+        def loop():
+            while not self.stop_flag:
+                try:
+                    sm = pynvml.nvmlDeviceGetClockInfo(h, pynvml.NVML_CLOCK_SM)
+                    rs = pynvml.nvmlDeviceGetCurrentClocksEventReasons(h)
+                    pw = pynvml.nvmlDeviceGetPowerUsage(h) / 1000.0
+                    self.rows.append((time.perf_counter(), sm, rs, pw))
+                except Exception:
+                    pass
+                time.sleep(0.02)
+        self.thread = threading.Thread(target=loop, daemon=True)
+        self.thread.start()
+
+    def mark_start(self):
+        self.t0 = time.perf_counter()
+
+    def mark_end(self):
+        self.t1 = time.perf_counter()
 
     def stop(self):
-        if self.proc:
-            self.proc.terminate()
-        sm, mx, reasons = [], 0.0, set()
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for r in self.rows:
-            f = [x.strip() for x in r.split(",")]
-            if len(f) < 7:
-                continue
-            try:
-                sm.append(float(f[0])); mx = max(mx, float(f[1]))
-            except ValueError:
-                continue
-            for n, v in zip(names, f[3:7]):
-                if v.lower().startswith("active"):
-                    reasons.add(n)
-        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": mx or None, "reasons": sorted(reasons),
-                "samples": len(sm)}
+        self.stop_flag = True
+        if self.thread:
+            self.thread.join(timeout=1.0)
+        inside = [r for r in self.rows if self.t0 is not None and self.t0 <= r[0] <= (self.t1 or 1e30)]
+        use = inside or self.rows[-3:]
+        reasons = set()
+        for r in use:
+            for bit, name in self.REASONS.items():
+                if r[2] & bit:
+                    reasons.add(name)
+        return {"sm_mhz": statistics.median([r[1] for r in use]) if use else None, "sm_max_mhz": self.max,
+                "reasons": sorted(reasons), "power_w_max": max([r[3] for r in use]) if use else None,
+                "samples": len(inside)}
 
 
 # --------------------------------------------------------------------------------------- CPU arm
@@ -192,14 +202,15 @@ def run_ours(args):
         shape = ModelShape(shape.vocab, shape.hidden, args.layers, shape.n_heads, shape.n_kv_heads, shape.head_dim,
                            shape.inter, shape.max_ctx, shape.rope_theta, shape.rms_eps)
     batch = args.batch or (32 if world == 1 else 64)
-    n_ttft = 3
+    n_ttft = max(1, args.ttft_runs)
     total_steps = args.warmup + args.steps + args.profile_steps + 2
     page = 64
     pages_per_seq = (args.prompt_len + total_steps + page) // page + 1
     stream = torch.cuda.current_stream()
     eng = Engine(WorkerConfig(shape, device=local, tp_rank=rank, tp_size=world, max_batch=batch,
                               max_step_tokens=args.prefill_chunk, page_size=page, kv_pages=batch * pages_per_seq,
-                              context_size=args.prompt_len + total_steps + 8, stream=stream.cuda_stream, nccl_id=nccl_id))
+                              context_size=args.prompt_len + total_steps + 8, stream=stream.cuda_stream, nccl_id=nccl_id,
+                              flags=B.FLAG_NO_GRAPH if args.no_graph else 0))
     eng.load_synthetic(0)
     eng.finalize()
 
@@ -225,15 +236,16 @@ def run_ours(args):
         eng.prefill(slots)
         torch.cuda.synchronize()
         ttft.append((time.perf_counter() - t0) * 1e3)
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
     # ---- warm-up (also captures the decode graph)
     for _ in range(args.warmup):
         eng.decode(slots)
     launches0 = eng.status().kernel_launches
-    sampler = ClockSampler(local)
-    if rank == 0:
-        sampler.start()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
+    sampler.mark_start()
     t0 = time.perf_counter()
     ev0.record(stream)
     for _ in range(args.steps):
@@ -241,6 +253,7 @@ def run_ours(args):
     ev1.record(stream)
     barrier()
     wall_ms = (time.perf_counter() - t0) * 1e3
+    sampler.mark_end()
     dev_ms = ev0.elapsed_time(ev1)
     clocks = sampler.stop() if rank == 0 else None
     launches = eng.status().kernel_launches - launches0
@@ -312,7 +325,7 @@ def run_ours(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=64)
+    ap.add_argument("--steps", type=int, default=128)
     ap.add_argument("--warmup", type=int, default=8)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--batch", type=int, default=0)
@@ -321,6 +334,8 @@ def main():
     ap.add_argument("--profile-steps", type=int, default=3)
     ap.add_argument("--layers", type=int, default=0, help="debug only: reduced depth")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-graph", action="store_true", help="run decode steps eagerly (profiling under ncu)")
+    ap.add_argument("--ttft-runs", type=int, default=3)
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)

@@ -10,14 +10,16 @@
 namespace dis {
 
 // ------------------------------------------------------------------------------ block reductions
+// kThreads = 0: use blockDim.x (a multiple of 32)
 template <int kThreads>
 __device__ __forceinline__ float block_sum(float v, float *sm) {
   v = warp_sum(v);
   const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+  const int nw = kThreads ? kThreads / 32 : (int)(blockDim.x >> 5);
   __syncthreads();
   if (l == 0) sm[w] = v;
   __syncthreads();
-  float r = (l < kThreads / 32) ? sm[l] : 0.f;
+  float r = (l < nw) ? sm[l] : 0.f;
   r = warp_sum(r);
   return r;  // every thread has the total
 }
@@ -25,28 +27,32 @@ template <int kThreads>
 __device__ __forceinline__ float block_max(float v, float *sm) {
   v = warp_max(v);
   const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+  const int nw = kThreads ? kThreads / 32 : (int)(blockDim.x >> 5);
   __syncthreads();
   if (l == 0) sm[w] = v;
   __syncthreads();
-  float r = (l < kThreads / 32) ? sm[l] : -INFINITY;
+  float r = (l < nw) ? sm[l] : -INFINITY;
   r = warp_max(r);
   return r;
 }
 
 // ------------------------------------------------------------------------------ add_rmsnorm
-constexpr int kNormThreads = 256;
-
-__global__ void __launch_bounds__(kNormThreads)
+// One CTA per row with H/4 threads (<= 1024): every thread owns one float4 column group per pass, so
+// the S split-K slices of a row are fetched with S independent 16-byte loads per thread in flight.
+__global__ void __launch_bounds__(1024)
 add_rmsnorm_kernel(float *__restrict__ x, const uint32_t *__restrict__ tokens,
                    const uint16_t *__restrict__ embed, const float *__restrict__ partial, int n_partial,
                    long long partial_stride, const float *__restrict__ gain, uint16_t *__restrict__ xn,
                    const int *__restrict__ row_map, int H, float eps) {
   __shared__ float red[32];
-  extern __shared__ float row[];  // H floats
+  extern __shared__ float row[];  // H floats (only used when a thread owns more than one group)
   const int t = blockIdx.x;
   const int src = row_map ? row_map[t] : t;
+  const int step = blockDim.x * 4;
+  const bool single = H <= step;
   float ss = 0.f;
-  for (int i = threadIdx.x * 4; i < H; i += kNormThreads * 4) {
+  float4 keep = make_float4(0.f, 0.f, 0.f, 0.f);
+  for (int i = threadIdx.x * 4; i < H; i += step) {
     float4 v;
     if (tokens) {
       const uint2 e = *reinterpret_cast<const uint2 *>(embed + (size_t)tokens[src] * H + i);
@@ -54,19 +60,21 @@ add_rmsnorm_kernel(float *__restrict__ x, const uint32_t *__restrict__ tokens,
       v = make_float4(a.x, a.y, b.x, b.y);
     } else {
       v = *reinterpret_cast<const float4 *>(x + (size_t)src * H + i);
+      const float *pp = partial + (size_t)src * H + i;
+#pragma unroll 4
       for (int s = 0; s < n_partial; s++) {
-        const float4 p = *reinterpret_cast<const float4 *>(partial + (size_t)s * partial_stride + (size_t)src * H + i);
+        const float4 p = *reinterpret_cast<const float4 *>(pp + (size_t)s * partial_stride);
         v.x += p.x; v.y += p.y; v.z += p.z; v.w += p.w;
       }
     }
     if (!row_map) *reinterpret_cast<float4 *>(x + (size_t)t * H + i) = v;
-    *reinterpret_cast<float4 *>(row + i) = v;
+    if (single) keep = v; else *reinterpret_cast<float4 *>(row + i) = v;
     ss += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
   }
-  ss = block_sum<kNormThreads>(ss, red);
+  ss = block_sum<0>(ss, red);
   const float inv = rsqrtf(ss / (float)H + eps);
-  for (int i = threadIdx.x * 4; i < H; i += kNormThreads * 4) {
-    const float4 v = *reinterpret_cast<const float4 *>(row + i);
+  for (int i = threadIdx.x * 4; i < H; i += step) {
+    const float4 v = single ? keep : *reinterpret_cast<const float4 *>(row + i);
     const float4 g = *reinterpret_cast<const float4 *>(gain + i);
     uint2 o;
     o.x = float2_to_bf16x2(v.x * inv * g.x, v.y * inv * g.y);
@@ -80,9 +88,11 @@ cudaError_t launch_add_rmsnorm(float *x, const uint32_t *tokens, const uint16_t 
                                const int *row_map, int T, int H, float eps, cudaStream_t st) {
   if (T <= 0) return cudaSuccess;
   if (H % 4 != 0 || H * 4 > 200 * 1024) { set_last_error("add_rmsnorm: H must be a multiple of 4 and <= 51200"); return cudaErrorInvalidValue; }
-  const size_t smem = (size_t)H * sizeof(float);
+  int threads = (H / 4 + 31) / 32 * 32;
+  threads = threads > 1024 ? 1024 : threads;
+  const size_t smem = H <= threads * 4 ? 0 : (size_t)H * sizeof(float);
   if (smem > 48 * 1024) DIS_CUDA_TRY(cudaFuncSetAttribute(add_rmsnorm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  add_rmsnorm_kernel<<<T, kNormThreads, smem, st>>>(x, tokens, embed, partial, n_partial, partial_stride, gain, xn, row_map, H, eps);
+  add_rmsnorm_kernel<<<T, threads, smem, st>>>(x, tokens, embed, partial, n_partial, partial_stride, gain, xn, row_map, H, eps);
   return cudaGetLastError();
 }
 
@@ -110,16 +120,26 @@ cudaError_t launch_reduce_partials(const float *partial, int n_partial, long lon
 }
 
 // ------------------------------------------------------------------------------ rope_kv_write
-// One CTA per token.  Work units are element PAIRS (i, i+d/2) of a head for q and k (rotate-half
-// RoPE) and adjacent pairs for v.
-__global__ void __launch_bounds__(256)
+// One CTA per token.  A work unit is four adjacent rotate-half pairs (i..i+3, i+d/2..i+d/2+3) of a q
+// or k head, or four adjacent v elements: two (one) float4 loads per split-K slice, all independent.
+__device__ __forceinline__ float4 sum_slices(const float *p, int n_partial, long long stride) {
+  float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 4
+  for (int s = 0; s < n_partial; s++) {
+    const float4 v = *reinterpret_cast<const float4 *>(p + (size_t)s * stride);
+    a.x += v.x; a.y += v.y; a.z += v.z; a.w += v.w;
+  }
+  return a;
+}
+
+__global__ void __launch_bounds__(1024)
 rope_kv_write_kernel(const float *__restrict__ qkv, int n_partial, long long partial_stride,
                      uint16_t *__restrict__ q, uint16_t *__restrict__ kv_pool,
                      const int *__restrict__ page_table, int max_pages, const int *__restrict__ pt_row,
                      const int *__restrict__ pos, const float *__restrict__ rope_cos,
                      const float *__restrict__ rope_sin, int n_heads, int n_kv, int d, int page_size) {
   const int t = blockIdx.x;
-  const int half = d >> 1;
+  const int half = d >> 1, hq = half >> 2;  // hq: units per head
   const int p = pos[t];
   const int nq = n_heads * d, nk = n_kv * d;
   const int ntot = nq + 2 * nk;
@@ -131,39 +151,32 @@ rope_kv_write_kernel(const float *__restrict__ qkv, int n_partial, long long par
   uint16_t *vpage = kpage + (size_t)n_kv * page_size * d;
   const float *cs = rope_cos + (size_t)p * half, *sn = rope_sin + (size_t)p * half;
 
-  const int q_pairs = n_heads * half, k_pairs = n_kv * half, v_pairs = nk >> 1;
-  for (int u = threadIdx.x; u < q_pairs + k_pairs + v_pairs; u += blockDim.x) {
-    if (u < q_pairs + k_pairs) {
-      const bool is_q = u < q_pairs;
-      const int uu = is_q ? u : u - q_pairs;
-      const int h = uu / half, i = uu - h * half;
+  const int q_units = n_heads * hq, k_units = n_kv * hq, v_units = nk >> 2;
+  for (int u = threadIdx.x; u < q_units + k_units + v_units; u += blockDim.x) {
+    if (u < q_units + k_units) {
+      const bool is_q = u < q_units;
+      const int uu = is_q ? u : u - q_units;
+      const int h = uu / hq, i = (uu - h * hq) * 4;
       const int col = (is_q ? 0 : nq) + h * d + i;
-      float a = 0.f, b = 0.f;
-      for (int s = 0; s < n_partial; s++) {
-        a += base[(size_t)s * partial_stride + col];
-        b += base[(size_t)s * partial_stride + col + half];
-      }
-      const float c = cs[i], sv = sn[i];
-      const float ra = a * c - b * sv, rb = b * c + a * sv;
-      if (is_q) {
-        q[(size_t)t * nq + h * d + i] = float_to_bf16_bits(ra);
-        q[(size_t)t * nq + h * d + i + half] = float_to_bf16_bits(rb);
-      } else {
-        uint16_t *dst = kpage + ((size_t)h * page_size + slot) * d;
-        dst[i] = float_to_bf16_bits(ra);
-        dst[i + half] = float_to_bf16_bits(rb);
-      }
+      const float4 a = sum_slices(base + col, n_partial, partial_stride);
+      const float4 b = sum_slices(base + col + half, n_partial, partial_stride);
+      const float4 c = *reinterpret_cast<const float4 *>(cs + i), sv = *reinterpret_cast<const float4 *>(sn + i);
+      uint2 lo, hi;
+      lo.x = float2_to_bf16x2(a.x * c.x - b.x * sv.x, a.y * c.y - b.y * sv.y);
+      lo.y = float2_to_bf16x2(a.z * c.z - b.z * sv.z, a.w * c.w - b.w * sv.w);
+      hi.x = float2_to_bf16x2(b.x * c.x + a.x * sv.x, b.y * c.y + a.y * sv.y);
+      hi.y = float2_to_bf16x2(b.z * c.z + a.z * sv.z, b.w * c.w + a.w * sv.w);
+      uint16_t *dst = is_q ? q + (size_t)t * nq + h * d + i : kpage + ((size_t)h * page_size + slot) * d + i;
+      *reinterpret_cast<uint2 *>(dst) = lo;
+      *reinterpret_cast<uint2 *>(dst + half) = hi;
     } else {
-      const int uu = (u - q_pairs - k_pairs) * 2;
+      const int uu = (u - q_units - k_units) * 4;
       const int h = uu / d, i = uu - h * d;
-      const int col = nq + nk + uu;
-      float a = 0.f, b = 0.f;
-      for (int s = 0; s < n_partial; s++) {
-        a += base[(size_t)s * partial_stride + col];
-        b += base[(size_t)s * partial_stride + col + 1];
-      }
-      uint16_t *dst = vpage + ((size_t)h * page_size + slot) * d + i;
-      *reinterpret_cast<uint32_t *>(dst) = float2_to_bf16x2(a, b);
+      const float4 a = sum_slices(base + nq + nk + uu, n_partial, partial_stride);
+      uint2 o;
+      o.x = float2_to_bf16x2(a.x, a.y);
+      o.y = float2_to_bf16x2(a.z, a.w);
+      *reinterpret_cast<uint2 *>(vpage + ((size_t)h * page_size + slot) * d + i) = o;
     }
   }
 }
@@ -173,9 +186,12 @@ cudaError_t launch_rope_kv_write(const float *qkv, int n_partial, long long part
                                  const int *pos, const float *rope_cos, const float *rope_sin, int T,
                                  int n_heads, int n_kv, int d, int page_size, cudaStream_t st) {
   if (T <= 0) return cudaSuccess;
-  if (d % 2 != 0) { set_last_error("rope_kv_write: head_dim must be even"); return cudaErrorInvalidValue; }
-  rope_kv_write_kernel<<<T, 256, 0, st>>>(qkv, n_partial, partial_stride, q, kv_pool, page_table, max_pages,
-                                          pt_row, pos, rope_cos, rope_sin, n_heads, n_kv, d, page_size);
+  if (d % 8 != 0) { set_last_error("rope_kv_write: head_dim must be a multiple of 8"); return cudaErrorInvalidValue; }
+  const int units = (n_heads + n_kv) * (d / 8) + n_kv * d / 4;
+  int threads = (units + 31) / 32 * 32;
+  threads = threads > 1024 ? 1024 : threads;
+  rope_kv_write_kernel<<<T, threads, 0, st>>>(qkv, n_partial, partial_stride, q, kv_pool, page_table, max_pages,
+                                              pt_row, pos, rope_cos, rope_sin, n_heads, n_kv, d, page_size);
   return cudaGetLastError();
 }
 
