@@ -210,7 +210,7 @@ def run_ours(args):
     eng = Engine(WorkerConfig(shape, device=local, tp_rank=rank, tp_size=world, max_batch=batch,
                               max_step_tokens=args.prefill_chunk, page_size=page, kv_pages=batch * pages_per_seq,
                               context_size=args.prompt_len + total_steps + 8, stream=stream.cuda_stream, nccl_id=nccl_id,
-                              flags=B.FLAG_NO_GRAPH if args.no_graph else 0))
+                              flags=(B.FLAG_NO_GRAPH if args.no_graph else 0) | (B.FLAG_NO_PDL if args.no_pdl else 0)))
     eng.load_synthetic(0)
     eng.finalize()
 
@@ -336,6 +336,7 @@ def main():
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-graph", action="store_true", help="run decode steps eagerly (profiling under ncu)")
     ap.add_argument("--ttft-runs", type=int, default=3)
+    ap.add_argument("--no-pdl", action="store_true", help="disable programmatic dependent launch (A/B)")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)

@@ -14,7 +14,7 @@ FINISH_NONE, FINISH_STOP, FINISH_LENGTH, FINISH_STOP_SEQUENCE, FINISH_FAILED = r
 (T_EMBED, T_ATTN_NORM, T_WQ, T_WK, T_WV, T_WO, T_MLP_NORM, T_WGATE, T_WUP, T_WDOWN, T_FINAL_NORM,
  T_LM_HEAD) = range(12)
 F32, BF16 = 0, 1
-FLAG_NO_GRAPH, FLAG_FORCE_GEMV = 1, 2
+FLAG_NO_GRAPH, FLAG_FORCE_GEMV, FLAG_NO_PDL = 1, 2, 4
 PROF_CLASSES = ("norm", "qkv", "rope", "attn", "oproj", "gateup", "down", "allreduce", "head_norm", "lm_head",
                 "sample")
 
@@ -84,8 +84,8 @@ PROTOTYPES = {
     "dis_k_rope_kv_write": (C.c_int, [vp, C.c_int32, C.c_int64, vp, vp, vp, C.c_int32, vp, vp, vp, vp, C.c_int32,
                                       C.c_int32, C.c_int32, C.c_int32, C.c_int32, vp]),
     "dis_k_attn_scratch_elems": (C.c_size_t, [C.c_int32, C.c_int32, C.c_int32, C.c_int32]),
-    "dis_k_attn_paged": (C.c_int, [vp, vp, vp, C.c_int32, vp, vp, vp, vp, C.c_int32, C.c_int32, C.c_int32, C.c_int32,
-                                   C.c_int32, C.c_int32, vp]),
+    "dis_k_attn_paged": (C.c_int, [vp, vp, C.c_int64, vp, C.c_int32, vp, vp, vp, vp, C.c_int32, C.c_int32, C.c_int32,
+                                   C.c_int32, C.c_int32, C.c_int32, vp]),
     "dis_k_sample": (C.c_int, [vp, C.c_int64, C.c_int32, C.c_int32, vp, vp, vp, vp, vp, vp]),
     "dis_k_synth_bf16": (C.c_int, [vp, C.c_size_t, C.c_uint64, C.c_int32, C.c_int32, C.c_float, C.c_float, vp]),
 }

@@ -169,12 +169,15 @@ int dis_k_rope_kv_write(const float *qkv, int32_t n_partial, int64_t partial_str
 size_t dis_k_attn_scratch_elems(int32_t T, int32_t n_heads, int32_t d, int32_t n_splits) {
   return dis::attn_scratch_elems(T, n_heads, d, n_splits);
 }
-int dis_k_attn_paged(const uint16_t *q, const uint16_t *kv_pool, const int32_t *page_table, int32_t max_pages,
-                     const int32_t *pt_row, const int32_t *ctx, uint16_t *out, float *scratch, int32_t n_splits, int32_t T,
-                     int32_t n_heads, int32_t n_kv, int32_t d, int32_t page_size, void *stream) {
+int dis_k_attn_paged(const uint16_t *q, const uint16_t *kv_pool, int64_t n_pages, const int32_t *page_table,
+                     int32_t max_pages, const int32_t *pt_row, const int32_t *ctx, uint16_t *out, float *scratch,
+                     int32_t n_splits, int32_t T, int32_t n_heads, int32_t n_kv, int32_t d, int32_t page_size, void *stream) {
   if (int rc = need_gpu()) return rc;
-  return k_ret(dis::launch_attn_paged(q, kv_pool, page_table, max_pages, pt_row, ctx, out, scratch, n_splits, T, n_heads,
-                                      n_kv, d, page_size, (cudaStream_t)stream));
+  dis::TmaMap map;
+  cudaError_t e = dis::make_kv_map(&map, kv_pool, (long long)n_pages * 2 * n_kv * page_size, d, page_size);
+  if (e != cudaSuccess) return k_ret(e);
+  return k_ret(dis::launch_attn_paged(map, 0, q, page_table, max_pages, pt_row, ctx, out, scratch, n_splits, T, n_heads, n_kv,
+                                      d, page_size, (cudaStream_t)stream));
 }
 int dis_k_sample(const float *logits, int64_t ld, int32_t T, int32_t V, const float *temperature, const float *top_p,
                  const uint64_t *seeds, const uint64_t *steps, uint32_t *out_tokens, void *stream) {

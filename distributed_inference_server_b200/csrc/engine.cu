@@ -77,7 +77,7 @@ int Engine::init(const dis_engine_config *c) {
   cap_tokens = c->max_step_tokens > 0 ? c->max_step_tokens : 8192;
   cap_tokens = std::max(cap_tokens, max_batch);
   page_size = c->page_size > 0 ? c->page_size : 64;
-  if (page_size & (page_size - 1)) return fail(DIS_ERR_INVALID_ARGUMENT, "page_size must be a power of two");
+  if ((page_size & (page_size - 1)) || page_size < 8) return fail(DIS_ERR_INVALID_ARGUMENT, "page_size must be a power of two >= 8");
   max_pages = (m.max_ctx + page_size - 1) / page_size;
 
   int ndev = 0;
@@ -189,6 +189,10 @@ int Engine::init(const dis_engine_config *c) {
     n_pages = want;
     kv_layer_stride = (size_t)n_pages * page_elems;
     ENG_CUDA(dev_alloc(&kv_pool, kv_layer_stride * L, &bytes_allocated));
+    // stale rows inside a TMA box get probability 0 in attention, so they must never be NaN
+    ENG_CUDA(cudaMemset(kv_pool, 0, kv_layer_stride * L * sizeof(uint16_t)));
+    kv_rows_per_layer = (long long)n_pages * 2 * nkv_l * page_size;
+    ENG_CUDA(make_kv_map(&kv_map, kv_pool, kv_rows_per_layer * (long long)L, m.head_dim, page_size));
     free_pages.resize((size_t)n_pages);
     for (int64_t i = 0; i < n_pages; i++) free_pages[(size_t)i] = (int)(n_pages - 1 - i);
     ENG_CUDA(dev_alloc(&d_page_table, (size_t)max_batch * max_pages, &bytes_allocated));
@@ -196,6 +200,7 @@ int Engine::init(const dis_engine_config *c) {
     memset(h_page_table, 0, (size_t)max_batch * max_pages * sizeof(int));
   }
   seqs.resize((size_t)max_batch);
+  use_pdl = !(c->flags & DIS_FLAG_NO_PDL);
   // ---- tensor parallel communicator
   if (tp_size > 1) {
     std::string err;
@@ -439,10 +444,9 @@ cudaError_t Engine::upload_step(int T, int R) {
 }
 
 int Engine::pick_attn_splits(int T, int max_ctx_in_batch) const {
-  const int hpk = nh_l / nkv_l;
-  const int gpk = hpk >= 4 ? hpk / 4 : 1;
-  const int ctas = T * nkv_l * gpk;
-  int want = (2 * kNumSMs + ctas - 1) / ctas;
+  const int ctas = T * nkv_l;
+  // two CTAs fit per SM; splitting only pays while a single wave is far from full
+  int want = ctas * 4 >= 2 * kNumSMs * 3 ? 1 : (2 * kNumSMs + ctas - 1) / ctas;
   const int cap = std::max(1, max_ctx_in_batch / 128);
   want = std::min(std::min(want, cap), 32);
   while ((size_t)T * nh_l * want * (2 + m.head_dim) > attn_scratch_elems && want > 1) want--;
@@ -489,9 +493,11 @@ cudaError_t Engine::enqueue_layers(int T, int n_splits) {
   for (int l = 0; l < m.layers; l++) {
     // x (+)= pending; xn = RMSNorm(x)
     prof_mark(P_NORM);
+    pdl_enabled() = use_pdl && !profiling && tp_size == 1 && l > 0;  // the step's first kernel follows a memcpy
     RET_CUDA(launch_add_rmsnorm(x, l == 0 ? tokens : nullptr, embed, pend, pend_n, pend_stride, attn_norm + (size_t)l * H,
                                 xn, nullptr, T, H, m.rms_eps, stream));
     kernel_launches++;
+    pdl_enabled() = use_pdl && !profiling && tp_size == 1;
     int s_qkv = 1;
     prof_mark(P_QKV);
     RET_CUDA(linear_partial(xn_map, xn, wqkv_map, wqkv, l * nqkv_l, T, nqkv_l, H, &s_qkv));
@@ -500,8 +506,8 @@ cudaError_t Engine::enqueue_layers(int T, int n_splits) {
     RET_CUDA(launch_rope_kv_write(partial, s_qkv, (long long)T * nqkv_l, q, pool, d_page_table, max_pages, ptrow, pos,
                                   rope_cos, rope_sin, T, nh_l, nkv_l, d, page_size, stream));
     prof_mark(P_ATTN);
-    RET_CUDA(launch_attn_paged(q, pool, d_page_table, max_pages, ptrow, ctx, attn, attn_scratch, n_splits, T, nh_l,
-                               nkv_l, d, page_size, stream));
+    RET_CUDA(launch_attn_paged(kv_map, (long long)l * kv_rows_per_layer, q, d_page_table, max_pages, ptrow, ctx, attn,
+                               attn_scratch, n_splits, T, nh_l, nkv_l, d, page_size, stream));
     kernel_launches += n_splits > 1 ? 3 : 2;
     int s_o = 1;
     prof_mark(P_OPROJ);
@@ -527,6 +533,7 @@ cudaError_t Engine::enqueue_layers(int T, int n_splits) {
     else { pend = partial; pend_n = s_d; pend_stride = (long long)T * H; }
   }
   pend_ptr = pend; pend_count = pend_n; pend_str = pend_stride;
+  pdl_enabled() = false;
   return cudaSuccess;
 }
 

@@ -8,6 +8,7 @@
 
 #include "../../include/dis_engine.h"
 #include "kernels.h"
+#include "ptx.cuh"
 
 namespace dis {
 
@@ -85,6 +86,9 @@ struct Engine {
   // KV
   uint16_t *kv_pool = nullptr;
   size_t kv_layer_stride = 0;  // elements between layers in the pool
+  long long kv_rows_per_layer = 0;
+  TmaMap kv_map;  // the whole pool as [rows][head_dim]
+  bool use_pdl = true;  // programmatic dependent launch between the kernels of a step
   std::vector<int> free_pages;
   int *d_page_table = nullptr, *h_page_table = nullptr;
   bool pt_dirty = true;

@@ -1,10 +1,11 @@
 // k_attn_paged.cu -- attention of single query tokens over a paged bf16 KV cache.
 //
-// One CTA handles one (query token, kv head, split of the history) for up to 4 query heads of the
-// GQA group, so K and V are read from HBM once per group.  64-token K/V tiles are staged into
-// shared memory through a 3-4 stage cp.async ring (64-96 KB in flight per CTA, two CTAs per SM);
-// scores use 16 elements per lane and a short shuffle reduction, the softmax is online across
-// tiles, and P.V is accumulated with 8 output dims per thread.  HBM-bound: algorithmic
+// One CTA handles one (query token, kv head, split of the history) for all query heads of the GQA
+// group, so K and V are read from HBM once per group.  64-token K/V tiles are staged by TMA into
+// 128B-swizzled shared memory through a 3-4 stage mbarrier ring (64-96 KB in flight per CTA, two
+// CTAs per SM); Q K^T and P V run on mma.sync m16n8k16 (bf16 in, fp32 accumulate) with ldmatrix operand
+// loads -- on CUDA cores the 4 FMA per KV byte of a 4:1 GQA group is issue-bound well below the HBM
+// rate (measured: 56 us vs 5 us per layer at batch 32, ctx 512).  HBM-bound: algorithmic
 // bytes = 2 (K,V) * ctx * n_kv * d * 2 B per query token (+ q and out, negligible).
 //
 // KV page pool layout, per layer: [page][2 (K,V)][n_kv][page_size][d] bf16 -- each (page, kv head)
@@ -13,209 +14,238 @@
 // With n_splits > 1 every split writes (m, l, unnormalised o) to scratch and a combine pass merges
 // them (flash-decoding); that keeps all 148 SMs busy at batch 1.
 #include "kernels.h"
+#include "ptx.cuh"
 
 namespace dis {
 
 constexpr int kAttnThreads = 128;
-constexpr int kAttnTile = 64;  // tokens per pipeline stage
+constexpr int kAttnTile = 64;  // tokens per pipeline stage: 16 per warp
 
 template <int D>
 struct AttnCfg {
-  static constexpr int kStageBytes = 2 * kAttnTile * D * 2;              // K tile + V tile, bf16
-  static constexpr int kStages = D == 128 ? 3 : 4;                       // 96 KB / 64 KB -> 2+ CTAs per SM
-  static constexpr int kSmemBytes = kStages * kStageBytes;
+  static constexpr int kHalves = D / 64;                                  // 128-byte column blocks per row
+  static constexpr int kHalfBytes = kAttnTile * 128;                      // one [64 tokens][64 dims] block
+  static constexpr int kStageBytes = 2 * kHalves * kHalfBytes;            // K tile + V tile, bf16
+  static constexpr int kStages = D == 128 ? 3 : 4;                        // 96 KB / 64 KB -> two CTAs per SM
+  static constexpr int kSmemBytes = kStages * kStageBytes + 1024 + 64;    // + alignment slack + barriers
 };
 
-__device__ __forceinline__ void cp_async_16(uint32_t dst, const void *src, int src_bytes) {
-  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(src_bytes) : "memory");
+__device__ __forceinline__ void ldmatrix_x4(uint32_t addr, uint32_t &r0, uint32_t &r1, uint32_t &r2, uint32_t &r3) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3) : "r"(addr));
 }
-__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
-template <int N>
-__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+__device__ __forceinline__ void ldmatrix_x4_trans(uint32_t addr, uint32_t &r0, uint32_t &r1, uint32_t &r2, uint32_t &r3) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3) : "r"(addr));
+}
+// D(16x8, f32) += A(16x16, bf16, row) * B(16x8, bf16, col)
+__device__ __forceinline__ void mma_bf16_16816(float (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3,
+                                               uint32_t b0, uint32_t b1) {
+  asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+               : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+               : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
 
+// One CTA = one (query token, kv head, split).  The GQA group's query heads (<= 8) are rows 0..G-1 of a
+// 16-row MMA tile; rows G..15 are zero padding (the kernel is HBM-bound, the wasted MMA rows are free).
+// K/V tiles of 64 tokens arrive by TMA (one elected thread, 128B-swizzled boxes of min(page,64) rows,
+// mbarrier completion) into a 3-4 stage ring.  Each of the 4 warps owns 16 of a tile's 64 tokens and
+// keeps its own online-softmax state (m, l, O[16 x D] in mma accumulator fragments); the four states
+// are merged once at the end.  P is rounded to bf16 for the P.V MMA (the usual flash-attention choice).
+// Rows past the context inside a box hold stale (finite) cache contents and get probability 0; the
+// engine zero-fills the pool once so that they can never be NaN.
 template <int D, int G>
 __global__ void __launch_bounds__(kAttnThreads, 2)
-attn_paged_kernel(const uint16_t *__restrict__ q, const uint16_t *__restrict__ kv_pool,
+attn_paged_kernel(const __grid_constant__ CUtensorMap kv_map, long long row0, const uint16_t *__restrict__ q,
                   const int *__restrict__ page_table, int max_pages, const int *__restrict__ pt_row,
                   const int *__restrict__ ctx_len, uint16_t *__restrict__ out, float *__restrict__ scratch,
-                  int n_splits, int T, int n_heads, int n_kv, int page_size, int groups_per_kv) {
+                  int n_splits, int T, int n_heads, int n_kv, int page_shift) {
   using Cfg = AttnCfg<D>;
-  constexpr int LPT = D / 16;              // lanes per token in the QK phase (16 elements each)
-  constexpr int TPW = 32 / LPT;            // tokens per warp per pass
-  constexpr int TPI = TPW * (kAttnThreads / 32);
-  constexpr int CPR = D / 8;               // 16-byte chunks per K/V row
-  constexpr int RPAR = kAttnThreads / CPR;  // V rows processed in parallel
-  constexpr int kChunks = 2 * kAttnTile * CPR;  // 16-byte chunks per stage
+  constexpr int KS = D / 16;  // k-steps of the QK^T MMA
+  constexpr int NT = D / 8;   // n-tiles of the P.V MMA
 
-  extern __shared__ __align__(128) uint8_t smem[];
-  __shared__ __align__(16) float s_p[kAttnTile][G];
-  __shared__ float s_scale[G], s_m[G], s_l[G];
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;  // 128B swizzle atoms are 1024-byte aligned
+  uint8_t *smem = smem_raw + (smem_base - smem_u32(smem_raw));
+  const uint32_t bar_base = smem_base + Cfg::kStages * Cfg::kStageBytes;
+  auto full_bar = [&](int s) { return bar_base + 8u * s; };
 
   const int t = blockIdx.z;
-  const int kvh = blockIdx.y / groups_per_kv;
-  const int sub = blockIdx.y - kvh * groups_per_kv;
+  const int kvh = blockIdx.y;
   const int split = blockIdx.x;
-  const int heads_per_kv = n_heads / n_kv;
-  const int h0 = kvh * heads_per_kv + sub * G;  // first query head of this CTA
+  const int h0 = kvh * G;  // first query head of this CTA (G = n_heads / n_kv)
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int g = lane >> 2, tq = lane & 3;  // mma fragment coordinates
 
+  if (threadIdx.x == 0) {
+    tma_prefetch_desc(&kv_map);
+    for (int s = 0; s < Cfg::kStages; s++) mbar_init(full_bar(s), 1);
+    fence_barrier_init();
+    fence_proxy_async();
+  }
+  pdl_launch_dependents();
+  pdl_wait();  // q, the page table and this step's K/V rows come from the previous kernels
+  __syncthreads();
+
+  const int page_size = 1 << page_shift;
+  const int box_rows = min(page_size, kAttnTile);
   const int ctx = ctx_len[t];
   int chunk = (ctx + n_splits - 1) / n_splits;
   chunk = (chunk + kAttnTile - 1) / kAttnTile * kAttnTile;
   const int begin = split * chunk;
   const int end = min(ctx, begin + chunk);
   const int n_tiles = end > begin ? (end - begin + kAttnTile - 1) / kAttnTile : 0;
-
   const int *pt = page_table + (size_t)pt_row[t] * max_pages;
-  const size_t page_stride = (size_t)2 * n_kv * page_size * D;
-  const uint16_t *kbase = kv_pool + (size_t)kvh * page_size * D;
-  const size_t v_off = (size_t)n_kv * page_size * D;
-  const uint32_t smem_base = (uint32_t)__cvta_generic_to_shared(smem);
 
-  // stage <- tokens [begin + tile*64, +64): K rows then V rows, [row][D] bf16, 16 B per cp.async
-  auto load_tile = [&](int tile, int stage) {
+  // pool rows: [page][2 (K,V)][n_kv][page_size] of d elements each
+  auto load_tile = [&](int tile, int stage) {  // one thread
     const int tile0 = begin + tile * kAttnTile;
     const uint32_t sbase = smem_base + stage * Cfg::kStageBytes;
+    mbar_expect_tx(full_bar(stage), Cfg::kStageBytes);
+    for (int r = 0; r < kAttnTile; r += box_rows) {
+      const int pos = tile0 + r;
+      const long long page = pt[min(pos >> page_shift, max_pages - 1)];
+      const long long krow = row0 + ((page * 2 + 0) * n_kv + kvh) * page_size + (pos & (page_size - 1));
+      const long long vrow = krow + (long long)n_kv * page_size;
 #pragma unroll
-    for (int id = threadIdx.x; id < kChunks; id += kAttnThreads) {
-      const int kv = id / (kAttnTile * CPR);
-      const int row = (id / CPR) % kAttnTile;
-      const int c = id % CPR;
-      const int pos = tile0 + row;
-      const bool valid = pos < end;
-      const uint16_t *src = kbase;
-      if (valid) src = kbase + (size_t)pt[pos / page_size] * page_stride + (kv ? v_off : 0) + (size_t)(pos % page_size) * D + c * 8;
-      cp_async_16(sbase + (uint32_t)(kv * kAttnTile * D * 2 + row * D * 2 + c * 16), src, valid ? 16 : 0);
+      for (int h = 0; h < Cfg::kHalves; h++) {
+        tma_load_2d(sbase + h * Cfg::kHalfBytes + r * 128, &kv_map, h * 64, (int)krow, full_bar(stage), kEvictFirst);
+        tma_load_2d(sbase + (Cfg::kHalves + h) * Cfg::kHalfBytes + r * 128, &kv_map, h * 64, (int)vrow, full_bar(stage), kEvictFirst);
+      }
     }
   };
 
-  // ---- q fragment: elements [j*8, j*8+8) and [D/2 + j*8, D/2 + j*8 + 8) of each head, fp32 registers
-  const int j = lane % LPT, grp = lane / LPT;
-  float qf[G][16];
-#pragma unroll
-  for (int g = 0; g < G; g++) {
-    const uint16_t *qp = q + ((size_t)t * n_heads + h0 + g) * D;
-    const uint4 a = *reinterpret_cast<const uint4 *>(qp + j * 8);
-    const uint4 b = *reinterpret_cast<const uint4 *>(qp + D / 2 + j * 8);
-    const uint32_t w[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
-#pragma unroll
-    for (int i = 0; i < 8; i++) { const float2 f = bf16x2_to_float2(w[i]); qf[g][2 * i] = f.x; qf[g][2 * i + 1] = f.y; }
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < Cfg::kStages - 1; s++)
+      if (s < n_tiles) load_tile(s, s);
   }
-  const float scale = rsqrtf((float)D);
 
-  float acc[G][8];
+  // ---- Q as the A operand: row g = head g (g < G), everything else zero
+  uint32_t qa[KS][2];
 #pragma unroll
-  for (int g = 0; g < G; g++)
-#pragma unroll
-    for (int i = 0; i < 8; i++) acc[g][i] = 0.f;
-  if (threadIdx.x < G) { s_m[threadIdx.x] = -INFINITY; s_l[threadIdx.x] = 0.f; }
-
-  // ---- pipeline prologue
-#pragma unroll
-  for (int s = 0; s < Cfg::kStages - 1; s++) {
-    if (s < n_tiles) load_tile(s, s);
-    cp_async_commit();
+  for (int ks = 0; ks < KS; ks++) {
+    qa[ks][0] = 0u; qa[ks][1] = 0u;
+    if (g < G) {
+      const uint16_t *qp = q + ((size_t)t * n_heads + h0 + g) * D + ks * 16 + tq * 2;
+      qa[ks][0] = *reinterpret_cast<const uint32_t *>(qp);
+      qa[ks][1] = *reinterpret_cast<const uint32_t *>(qp + 8);
+    }
   }
-  const int vr = threadIdx.x / CPR, vc = threadIdx.x % CPR;
+  const float scale_log2 = rsqrtf((float)D) * 1.4426950408889634f;  // scores are kept in the log2 domain
 
+  float oacc[NT][4];
+#pragma unroll
+  for (int n = 0; n < NT; n++) { oacc[n][0] = 0.f; oacc[n][1] = 0.f; oacc[n][2] = 0.f; oacc[n][3] = 0.f; }
+  float m_run = -INFINITY, l_run = 0.f;  // row g; l_run is this thread's partial sum (quad-reduced at the end)
+
+  const int wtok = warp * 16;  // this warp's token slice inside a tile
   for (int tile = 0; tile < n_tiles; tile++) {
-    cp_async_wait<Cfg::kStages - 2>();
-    __syncthreads();  // tile's bytes are visible to all; the stage consumed last iteration is free
-    {
+    __syncthreads();  // everyone is done with the stage consumed last iteration
+    if (threadIdx.x == 0) {
       const int nt = tile + Cfg::kStages - 1;
       if (nt < n_tiles) load_tile(nt, nt % Cfg::kStages);
-      cp_async_commit();
     }
     const int stage = tile % Cfg::kStages;
-    const uint8_t *ks = smem + stage * Cfg::kStageBytes;
-    const uint8_t *vs = ks + kAttnTile * D * 2;
+    mbar_wait(full_bar(stage), (uint32_t)(tile / Cfg::kStages) & 1u);
+    const uint32_t ks_addr = smem_base + stage * Cfg::kStageBytes;
+    const uint32_t vs_addr = ks_addr + Cfg::kHalves * Cfg::kHalfBytes;
     const int tile_len = min(kAttnTile, end - (begin + tile * kAttnTile));
-    // ---- scores: 16 elements per lane, LPT lanes per token
+    if (wtok >= tile_len) continue;  // warp-uniform: nothing of this tile belongs to this warp
+
+    // ---- S = Q K^T for this warp's 16 tokens (two n-tiles of 8)
+    float sacc[2][4];
 #pragma unroll
-    for (int base = warp * TPW; base < kAttnTile; base += TPI) {
-      const int tok = base + grp;
-      const uint4 k0 = *reinterpret_cast<const uint4 *>(ks + tok * D * 2 + j * 16);
-      const uint4 k1 = *reinterpret_cast<const uint4 *>(ks + tok * D * 2 + D + j * 16);
-      const uint32_t w[8] = {k0.x, k0.y, k0.z, k0.w, k1.x, k1.y, k1.z, k1.w};
-      float kf[16];
+    for (int n = 0; n < 2; n++) { sacc[n][0] = 0.f; sacc[n][1] = 0.f; sacc[n][2] = 0.f; sacc[n][3] = 0.f; }
+    {
+      const int mi = lane >> 3, r = lane & 7;
+      const int tok = wtok + (mi >> 1) * 8 + r;  // matrices 0,1 -> n-tile 0; 2,3 -> n-tile 1
 #pragma unroll
-      for (int i = 0; i < 8; i++) { const float2 f = bf16x2_to_float2(w[i]); kf[2 * i] = f.x; kf[2 * i + 1] = f.y; }
-#pragma unroll
-      for (int g = 0; g < G; g++) {
-        float d = 0.f;
-#pragma unroll
-        for (int i = 0; i < 16; i++) d = fmaf(qf[g][i], kf[i], d);
-#pragma unroll
-        for (int o = LPT / 2; o > 0; o >>= 1) d += __shfl_xor_sync(0xffffffffu, d, o);
-        if (j == 0) s_p[tok][g] = tok < tile_len ? d * scale : -INFINITY;
+      for (int ks = 0; ks < KS; ks++) {
+        const int c = ks * 2 + (mi & 1);  // 16-byte chunk of the row
+        uint32_t b0, b1, b2, b3;
+        ldmatrix_x4(ks_addr + (c >> 3) * Cfg::kHalfBytes + tok * 128 + (((c & 7) ^ (tok & 7)) << 4), b0, b1, b2, b3);
+        mma_bf16_16816(sacc[0], qa[ks][0], 0u, qa[ks][1], 0u, b0, b1);
+        mma_bf16_16816(sacc[1], qa[ks][0], 0u, qa[ks][1], 0u, b2, b3);
       }
     }
-    __syncthreads();
-    // ---- online softmax bookkeeping: warp g owns head g
-    if (warp < G) {
-      const float a = s_p[lane][warp], b = s_p[lane + 32][warp];
-      const float mx = warp_max(fmaxf(a, b));
-      const float m_old = s_m[warp];
-      const float m_new = fmaxf(m_old, mx);
-      const float pa = expf(a - m_new), pb = expf(b - m_new);  // exp(-inf) = 0 for masked tokens
-      s_p[lane][warp] = pa;
-      s_p[lane + 32][warp] = pb;
-      const float sum = warp_sum(pa + pb);
-      if (lane == 0) {
-        const float sc = expf(m_old - m_new);  // 0 on the first tile
-        s_scale[warp] = sc;
-        s_m[warp] = m_new;
-        s_l[warp] = s_l[warp] * sc + sum;
+    // ---- online softmax on row g (tokens wtok + n*8 + tq*2 + {0,1})
+    float mx = -INFINITY;
+#pragma unroll
+    for (int n = 0; n < 2; n++)
+#pragma unroll
+      for (int e = 0; e < 2; e++) {
+        const int tok = wtok + n * 8 + tq * 2 + e;
+        const float v = tok < tile_len ? sacc[n][e] * scale_log2 : -INFINITY;
+        sacc[n][e] = v;
+        mx = fmaxf(mx, v);
       }
+    mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 1));
+    mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 2));
+    const float m_new = fmaxf(m_run, mx);  // finite: token wtok is valid
+    const float corr = exp2f(m_run - m_new);  // 0 on the first tile
+    m_run = m_new;
+    float psum = 0.f;
+    uint32_t pa[2];
+#pragma unroll
+    for (int n = 0; n < 2; n++) {
+      const float p0 = exp2f(sacc[n][0] - m_new), p1 = exp2f(sacc[n][1] - m_new);
+      psum += p0 + p1;
+      pa[n] = float2_to_bf16x2(p0, p1);
     }
-    __syncthreads();
-    // ---- P.V: 8 output dims per thread, RPAR rows in parallel
+    l_run = l_run * corr + psum;
 #pragma unroll
-    for (int g = 0; g < G; g++) {
-      const float sc = s_scale[g];
+    for (int n = 0; n < NT; n++) { oacc[n][0] *= corr; oacc[n][1] *= corr; }
+    // ---- O += P V : A = P (rows g; rows g+8 are padding -> zero), B = V^T fragments via ldmatrix.trans
+    {
+      const int mi = lane >> 3, r = lane & 7;
+      const int tok = wtok + (mi & 1) * 8 + r;  // matrices 0,2 -> tokens 0-7; 1,3 -> tokens 8-15
 #pragma unroll
-      for (int i = 0; i < 8; i++) acc[g][i] *= sc;
-    }
-#pragma unroll 4
-    for (int tok = vr; tok < tile_len; tok += RPAR) {
-      const uint4 v = *reinterpret_cast<const uint4 *>(vs + tok * D * 2 + vc * 16);
-      const uint32_t w[4] = {v.x, v.y, v.z, v.w};
-      float vf[8];
-#pragma unroll
-      for (int i = 0; i < 4; i++) { const float2 f = bf16x2_to_float2(w[i]); vf[2 * i] = f.x; vf[2 * i + 1] = f.y; }
-      float p[G];
-#pragma unroll
-      for (int g = 0; g < G; g++) p[g] = s_p[tok][g];
-#pragma unroll
-      for (int g = 0; g < G; g++)
-#pragma unroll
-        for (int i = 0; i < 8; i++) acc[g][i] = fmaf(p[g], vf[i], acc[g][i]);
+      for (int n = 0; n < NT; n += 2) {
+        const int c = n + (mi >> 1);
+        uint32_t b0, b1, b2, b3;
+        ldmatrix_x4_trans(vs_addr + (c >> 3) * Cfg::kHalfBytes + tok * 128 + (((c & 7) ^ (tok & 7)) << 4), b0, b1, b2, b3);
+        mma_bf16_16816(oacc[n], pa[0], 0u, pa[1], 0u, b0, b1);
+        mma_bf16_16816(oacc[n + 1], pa[0], 0u, pa[1], 0u, b2, b3);
+      }
     }
   }
-  cp_async_wait<0>();
-  __syncthreads();
+  __syncthreads();  // all TMA loads issued were waited for above: the stage memory is free
 
-  // ---- reduce the RPAR row slots through the (now free) stage memory
-  float *s_red = reinterpret_cast<float *>(smem);  // [RPAR][G][D]
+  // ---- merge the four warps' (m, l, O) through the stage memory
+  float *s_o = reinterpret_cast<float *>(smem);        // [4 warps][G][D]
+  float *s_m = s_o + 4 * G * D;                        // [4][G]
+  float *s_l = s_m + 4 * G;                            // [4][G]
+  l_run += __shfl_xor_sync(0xffffffffu, l_run, 1);
+  l_run += __shfl_xor_sync(0xffffffffu, l_run, 2);
+  if (g < G) {
 #pragma unroll
-  for (int g = 0; g < G; g++)
-#pragma unroll
-    for (int i = 0; i < 8; i++) s_red[(vr * G + g) * D + vc * 8 + i] = acc[g][i];
+    for (int n = 0; n < NT; n++)
+      *reinterpret_cast<float2 *>(s_o + ((size_t)(warp * G + g) * D + n * 8 + tq * 2)) = make_float2(oacc[n][0], oacc[n][1]);
+    if (tq == 0) { s_m[warp * G + g] = m_run; s_l[warp * G + g] = l_run; }
+  }
   __syncthreads();
   for (int e = threadIdx.x; e < G * D; e += kAttnThreads) {
-    const int g = e / D, dd = e - g * D;
-    float o = 0.f;
+    const int hh = e / D, dd = e - hh * D;
+    float M = -INFINITY;
 #pragma unroll
-    for (int r = 0; r < RPAR; r++) o += s_red[(r * G + g) * D + dd];
-    const int h = h0 + g;
+    for (int w = 0; w < 4; w++) M = fmaxf(M, s_m[w * G + hh]);
+    float L = 0.f, o = 0.f;
+#pragma unroll
+    for (int w = 0; w < 4; w++) {
+      const float mw = s_m[w * G + hh];
+      const float wgt = mw == -INFINITY ? 0.f : exp2f(mw - M);
+      L += s_l[w * G + hh] * wgt;
+      o += s_o[(size_t)(w * G + hh) * D + dd] * wgt;
+    }
+    const int h = h0 + hh;
     if (n_splits == 1) {
-      out[((size_t)t * n_heads + h) * D + dd] = float_to_bf16_bits(o / s_l[g]);
+      out[((size_t)t * n_heads + h) * D + dd] = float_to_bf16_bits(o / L);
     } else {
-      // scratch: ml [T][n_heads][S][2] then o [T][n_heads][S][D]
+      // scratch: ml [T][n_heads][S][2] then o [T][n_heads][S][D]; m is in the log2 domain
       float *ml = scratch + (((size_t)t * n_heads + h) * n_splits + split) * 2;
       float *op = scratch + (size_t)T * n_heads * n_splits * 2 + (((size_t)t * n_heads + h) * n_splits + split) * D;
       op[dd] = o;
-      if (dd == 0) { ml[0] = s_m[g]; ml[1] = s_l[g]; }
+      if (dd == 0) { ml[0] = M; ml[1] = L; }
     }
   }
 }
@@ -224,13 +254,15 @@ template <int D>
 __global__ void attn_combine_kernel(const float *__restrict__ scratch, uint16_t *__restrict__ out, int n_splits,
                                     int T, int n_heads) {
   const int t = blockIdx.y, h = blockIdx.x, dd = threadIdx.x;
+  pdl_launch_dependents();
+  pdl_wait();
   const float *ml = scratch + ((size_t)t * n_heads + h) * n_splits * 2;
   const float *op = scratch + (size_t)T * n_heads * n_splits * 2 + ((size_t)t * n_heads + h) * n_splits * D;
   float M = -INFINITY;
   for (int s = 0; s < n_splits; s++) M = fmaxf(M, ml[2 * s]);
   float L = 0.f, o = 0.f;
   for (int s = 0; s < n_splits; s++) {
-    const float w = expf(ml[2 * s] - M);
+    const float w = ml[2 * s] == -INFINITY ? 0.f : exp2f(ml[2 * s] - M);
     L += ml[2 * s + 1] * w;
     o += op[(size_t)s * D + dd] * w;
   }
@@ -243,45 +275,47 @@ size_t attn_scratch_elems(int T, int n_heads, int d, int n_splits) {
 }
 
 template <int D, int G>
-static cudaError_t attn_launch(const uint16_t *q, const uint16_t *kv_pool, const int *page_table, int max_pages,
-                               const int *pt_row, const int *ctx, uint16_t *out, float *scratch, int n_splits,
-                               int T, int n_heads, int n_kv, int page_size, int groups_per_kv, cudaStream_t st) {
-  dim3 grid(n_splits, n_kv * groups_per_kv, T);
+static cudaError_t attn_launch(const TmaMap &kv_map, long long row0, const uint16_t *q, const int *page_table,
+                               int max_pages, const int *pt_row, const int *ctx, uint16_t *out, float *scratch,
+                               int n_splits, int T, int n_heads, int n_kv, int page_shift, cudaStream_t st) {
+  dim3 grid(n_splits, n_kv, T);
   static bool attr_set = false;
   if (!attr_set) {
     DIS_CUDA_TRY(cudaFuncSetAttribute(attn_paged_kernel<D, G>, cudaFuncAttributeMaxDynamicSharedMemorySize, AttnCfg<D>::kSmemBytes));
     attr_set = true;
   }
-  attn_paged_kernel<D, G><<<grid, kAttnThreads, AttnCfg<D>::kSmemBytes, st>>>(q, kv_pool, page_table, max_pages, pt_row, ctx, out,
-                                                         scratch, n_splits, T, n_heads, n_kv, page_size,
-                                                         groups_per_kv);
-  DIS_CUDA_TRY(cudaGetLastError());
-  if (n_splits > 1) {
-    attn_combine_kernel<D><<<dim3(n_heads, T), D, 0, st>>>(scratch, out, n_splits, T, n_heads);
-    DIS_CUDA_TRY(cudaGetLastError());
-  }
+  DIS_CUDA_TRY(launch_k(attn_paged_kernel<D, G>, grid, dim3(kAttnThreads), AttnCfg<D>::kSmemBytes, st,
+                        *reinterpret_cast<const CUtensorMap *>(&kv_map), row0, q, page_table, max_pages, pt_row, ctx, out,
+                        scratch, n_splits, T, n_heads, n_kv, page_shift));
+  if (n_splits > 1)
+    DIS_CUDA_TRY(launch_k(attn_combine_kernel<D>, dim3(n_heads, T), dim3(D), 0, st, (const float *)scratch, out, n_splits, T, n_heads));
   return cudaSuccess;
 }
 
-cudaError_t launch_attn_paged(const uint16_t *q, const uint16_t *kv_pool, const int *page_table, int max_pages,
-                              const int *pt_row, const int *ctx, uint16_t *out, float *scratch, int n_splits,
-                              int T, int n_heads, int n_kv, int d, int page_size, cudaStream_t st) {
+// The pool as a 2-D tensor of d-element rows, boxes of {64 dims, min(page_size, 64) rows}, 128B swizzle.
+cudaError_t make_kv_map(TmaMap *out, const uint16_t *pool, long long total_rows, int d, int page_size) {
+  return make_tma_map_2d(out, pool, (uint64_t)total_rows, (uint64_t)d, (uint32_t)(page_size < kAttnTile ? page_size : kAttnTile));
+}
+
+cudaError_t launch_attn_paged(const TmaMap &kv_map, long long row0, const uint16_t *q, const int *page_table,
+                              int max_pages, const int *pt_row, const int *ctx, uint16_t *out, float *scratch,
+                              int n_splits, int T, int n_heads, int n_kv, int d, int page_size, cudaStream_t st) {
   if (T <= 0) return cudaSuccess;
   if (n_kv <= 0 || n_heads % n_kv != 0) { set_last_error("attn_paged: n_heads must be a multiple of n_kv"); return cudaErrorInvalidValue; }
   if (n_splits < 1 || (n_splits > 1 && !scratch)) { set_last_error("attn_paged: n_splits > 1 needs scratch"); return cudaErrorInvalidValue; }
-  if (T > 65535) { set_last_error("attn_paged: T > 65535 tokens per launch"); return cudaErrorInvalidValue; }
-  const int hpk = n_heads / n_kv;
-  const int G = hpk >= 4 ? 4 : hpk;  // query heads per CTA
-  if (hpk % G != 0 || (G != 1 && G != 2 && G != 4)) { set_last_error("attn_paged: GQA group must be 1, 2 or a multiple of 4"); return cudaErrorInvalidValue; }
-  const int gpk = hpk / G;
+  if (T > 65535 || n_kv > 65535) { set_last_error("attn_paged: more than 65535 tokens or kv heads per launch"); return cudaErrorInvalidValue; }
+  if (page_size < 8 || (page_size & (page_size - 1))) { set_last_error("attn_paged: page_size must be a power of two >= 8"); return cudaErrorInvalidValue; }
+  int page_shift = 0;
+  while ((1 << page_shift) < page_size) page_shift++;
+  const int G = n_heads / n_kv;  // query heads per kv head, all handled by one CTA
 #define DIS_ATTN_CASE(DD, GG)                                                                                  \
   if (d == DD && G == GG)                                                                                      \
-    return attn_launch<DD, GG>(q, kv_pool, page_table, max_pages, pt_row, ctx, out, scratch, n_splits, T,      \
-                               n_heads, n_kv, page_size, gpk, st);
-  DIS_ATTN_CASE(128, 4) DIS_ATTN_CASE(128, 2) DIS_ATTN_CASE(128, 1)
-  DIS_ATTN_CASE(64, 4) DIS_ATTN_CASE(64, 2) DIS_ATTN_CASE(64, 1)
+    return attn_launch<DD, GG>(kv_map, row0, q, page_table, max_pages, pt_row, ctx, out, scratch, n_splits, T, \
+                               n_heads, n_kv, page_shift, st);
+  DIS_ATTN_CASE(128, 8) DIS_ATTN_CASE(128, 4) DIS_ATTN_CASE(128, 2) DIS_ATTN_CASE(128, 1)
+  DIS_ATTN_CASE(64, 8) DIS_ATTN_CASE(64, 4) DIS_ATTN_CASE(64, 2) DIS_ATTN_CASE(64, 1)
 #undef DIS_ATTN_CASE
-  set_last_error("attn_paged: head_dim must be 64 or 128");
+  set_last_error("attn_paged: head_dim must be 64 or 128 and the GQA group 1, 2, 4 or 8");
   return cudaErrorInvalidValue;
 }
 

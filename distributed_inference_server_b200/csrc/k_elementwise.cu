@@ -6,8 +6,14 @@
 //   synth_bf16       counter-hash synthetic weights
 // None of these has a reference counterpart; they implement §3.3's decoder step.
 #include "kernels.h"
+#include "ptx.cuh"
 
 namespace dis {
+
+bool &pdl_enabled() {
+  static thread_local bool on = false;
+  return on;
+}
 
 // ------------------------------------------------------------------------------ block reductions
 // kThreads = 0: use blockDim.x (a multiple of 32)
@@ -47,6 +53,8 @@ add_rmsnorm_kernel(float *__restrict__ x, const uint32_t *__restrict__ tokens,
   __shared__ float red[32];
   extern __shared__ float row[];  // H floats (only used when a thread owns more than one group)
   const int t = blockIdx.x;
+  pdl_launch_dependents();
+  pdl_wait();
   const int src = row_map ? row_map[t] : t;
   const int step = blockDim.x * 4;
   const bool single = H <= step;
@@ -92,13 +100,15 @@ cudaError_t launch_add_rmsnorm(float *x, const uint32_t *tokens, const uint16_t 
   threads = threads > 1024 ? 1024 : threads;
   const size_t smem = H <= threads * 4 ? 0 : (size_t)H * sizeof(float);
   if (smem > 48 * 1024) DIS_CUDA_TRY(cudaFuncSetAttribute(add_rmsnorm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  add_rmsnorm_kernel<<<T, threads, smem, st>>>(x, tokens, embed, partial, n_partial, partial_stride, gain, xn, row_map, H, eps);
-  return cudaGetLastError();
+  return launch_k(add_rmsnorm_kernel, dim3(T), dim3(threads), smem, st, x, tokens, embed, partial, n_partial, partial_stride, gain,
+                  xn, row_map, H, eps);
 }
 
 // ------------------------------------------------------------------------------ reduce_partials
 __global__ void reduce_partials_kernel(const float *__restrict__ partial, int n_partial, long long stride,
                                        float *__restrict__ out, long long n4) {
+  pdl_launch_dependents();
+  pdl_wait();
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n4; i += (long long)gridDim.x * blockDim.x) {
     float4 v = reinterpret_cast<const float4 *>(partial)[i];
     for (int s = 1; s < n_partial; s++) {
@@ -115,8 +125,7 @@ cudaError_t launch_reduce_partials(const float *partial, int n_partial, long lon
   if (n % 4 != 0) { set_last_error("reduce_partials: n must be a multiple of 4"); return cudaErrorInvalidValue; }
   const long long n4 = n / 4;
   const int blocks = (int)min((long long)kNumSMs * 8, (n4 + 255) / 256);
-  reduce_partials_kernel<<<blocks, 256, 0, st>>>(partial, n_partial, stride, out, n4);
-  return cudaGetLastError();
+  return launch_k(reduce_partials_kernel, dim3(blocks), dim3(256), 0, st, partial, n_partial, stride, out, n4);
 }
 
 // ------------------------------------------------------------------------------ rope_kv_write
@@ -140,6 +149,8 @@ rope_kv_write_kernel(const float *__restrict__ qkv, int n_partial, long long par
                      const float *__restrict__ rope_sin, int n_heads, int n_kv, int d, int page_size) {
   const int t = blockIdx.x;
   const int half = d >> 1, hq = half >> 2;  // hq: units per head
+  pdl_launch_dependents();
+  pdl_wait();
   const int p = pos[t];
   const int nq = n_heads * d, nk = n_kv * d;
   const int ntot = nq + 2 * nk;
@@ -190,9 +201,8 @@ cudaError_t launch_rope_kv_write(const float *qkv, int n_partial, long long part
   const int units = (n_heads + n_kv) * (d / 8) + n_kv * d / 4;
   int threads = (units + 31) / 32 * 32;
   threads = threads > 1024 ? 1024 : threads;
-  rope_kv_write_kernel<<<T, threads, 0, st>>>(qkv, n_partial, partial_stride, q, kv_pool, page_table, max_pages,
-                                              pt_row, pos, rope_cos, rope_sin, n_heads, n_kv, d, page_size);
-  return cudaGetLastError();
+  return launch_k(rope_kv_write_kernel, dim3(T), dim3(threads), 0, st, qkv, n_partial, partial_stride, q, kv_pool, page_table,
+                  max_pages, pt_row, pos, rope_cos, rope_sin, n_heads, n_kv, d, page_size);
 }
 
 // ------------------------------------------------------------------------------ sampler
@@ -234,6 +244,7 @@ sample_kernel(const float *__restrict__ logits, long long ld, int V, const float
   __shared__ float scan[kSampThreads / 32];
   __shared__ int s_tok;
   const int t = blockIdx.x;
+  pdl_wait();
   const float *row = logits + (size_t)t * ld;
   const float temp = temperature ? temperature[t] : 0.f;
 
@@ -338,8 +349,8 @@ cudaError_t launch_sample(const float *logits, long long ld, int T, int V, const
                           const float *top_p, const unsigned long long *seeds, const unsigned long long *steps,
                           uint32_t *out_tokens, int vocab_offset, float *out_val, cudaStream_t st) {
   if (T <= 0) return cudaSuccess;
-  sample_kernel<<<T, kSampThreads, 0, st>>>(logits, ld, V, temperature, top_p, seeds, steps, out_tokens, vocab_offset, out_val);
-  return cudaGetLastError();
+  return launch_k(sample_kernel, dim3(T), dim3(kSampThreads), 0, st, logits, ld, V, temperature, top_p, seeds, steps, out_tokens,
+                  vocab_offset, out_val);
 }
 
 // Final step of a vocab-parallel greedy argmax: cand_val/cand_tok are [tp][T] (all-gathered).

@@ -21,50 +21,11 @@
 #include <cuda.h>
 
 #include "kernels.h"
+#include "ptx.cuh"
 
 namespace dis {
 
-// ------------------------------------------------------------------------------------ PTX wrappers
-__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
-
-__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
-  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
-}
-__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
-  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
-  uint32_t ok;
-  do {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-        "selp.u32 %0, 1, 0, p;\n\t}"
-        : "=r"(ok)
-        : "r"(bar), "r"(parity)
-        : "memory");
-  } while (!ok);
-}
-__device__ __forceinline__ void fence_barrier_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
-__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
-__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
-
-__device__ __forceinline__ void tma_prefetch_desc(const void *map) {
-  asm volatile("prefetch.tensormap [%0];" ::"l"(map) : "memory");
-}
-// 2-D tile load: coordinates {c0 = element offset along the contiguous dim, c1 = row}
-__device__ __forceinline__ void tma_load_2d(uint32_t dst, const void *map, int c0, int c1, uint32_t bar,
-                                            uint64_t policy) {
-  asm volatile(
-      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint"
-      " [%0], [%1, {%3, %4}], [%2], %5;"
-      ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1), "l"(policy)
-      : "memory");
-}
-constexpr uint64_t kEvictFirst = 0x12F0000000000000ull;  // stream-once data (weights)
-constexpr uint64_t kEvictLast = 0x14F0000000000000ull;   // data every CTA re-reads (activations)
-
+// (mbarrier / TMA / PDL wrappers: ptx.cuh)
 template <int kCols>
 __device__ __forceinline__ void tmem_alloc(uint32_t dst_smem) {
   asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(dst_smem), "n"(kCols) : "memory");
@@ -172,12 +133,23 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_cons
   uint32_t tmem_base;
   asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
 
+  pdl_launch_dependents();  // the next kernel may start its own prologue / weight prefetch
   if (warp == 0) {
     // ===== TMA producer =====
     if (lane == 0) {
-      int s = 0;
-      uint32_t phase = 0;
-      for (int kb = kb0; kb < kb1; kb++) {
+      // Weights do not depend on the previous kernel: fill the ring with weight tiles first, and only
+      // then wait for the producer of the activations (programmatic dependent launch).
+      const int pre = min(kb1 - kb0, Cfg::kStages);
+      for (int i = 0; i < pre; i++) {
+        mbar_expect_tx(full_bar(i), Cfg::kStageBytes);
+        tma_load_2d(a_tile(i), &w_map, (kb0 + i) * kBK, w_row0 + n0, full_bar(i), kEvictFirst);
+        if (kDual) tma_load_2d(a2_tile(i), &w_map, (kb0 + i) * kBK, w_row0 + up_row_off + n0, full_bar(i), kEvictFirst);
+      }
+      pdl_wait();
+      for (int i = 0; i < pre; i++) tma_load_2d(b_tile(i), &x_map, (kb0 + i) * kBK, t0, full_bar(i), kEvictLast);
+      int s = pre == Cfg::kStages ? 0 : pre;
+      uint32_t phase = pre == Cfg::kStages ? 1u : 0u;
+      for (int kb = kb0 + pre; kb < kb1; kb++) {
         mbar_wait(empty_bar(s), phase ^ 1u);
         mbar_expect_tx(full_bar(s), Cfg::kStageBytes);
         tma_load_2d(a_tile(s), &w_map, kb * kBK, w_row0 + n0, full_bar(s), kEvictFirst);
@@ -211,6 +183,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_cons
     // ===== epilogue: TMEM -> registers -> global =====
     mbar_wait(tmem_full_bar, 0);
     tc_fence_after();
+    pdl_wait();  // global writes only after every prerequisite grid has completed
     const int quarter = warp & 3;  // a warp may only touch TMEM lanes [32*(warp%4), +32)
     const int n = n0 + quarter * 32 + lane;
     const uint32_t lane_addr = tmem_base + ((uint32_t)(quarter * 32) << 16);
@@ -313,10 +286,8 @@ static cudaError_t gemm_launch(const TmaMap &w_map, const TmaMap &x_map, float *
   const int per = (num_kb + split_k - 1) / split_k;
   if ((num_kb + per - 1) / per != split_k) { set_last_error("gemm: split_k leaves an empty K slice; use gemm_pick_split_k"); return cudaErrorInvalidValue; }
   dim3 grid((N + kBM - 1) / kBM, (T + BN - 1) / BN, split_k);
-  kern<<<grid, kGemmThreads, Cfg::kSmemBytes, st>>>(*reinterpret_cast<const CUtensorMap *>(&w_map),
-                                                    *reinterpret_cast<const CUtensorMap *>(&x_map), out, act, T, N, K,
-                                                    w_row0, up_off, per);
-  return cudaGetLastError();
+  return launch_k(kern, grid, dim3(kGemmThreads), Cfg::kSmemBytes, st, *reinterpret_cast<const CUtensorMap *>(&w_map),
+                  *reinterpret_cast<const CUtensorMap *>(&x_map), out, act, T, N, K, w_row0, up_off, per);
 }
 
 cudaError_t launch_gemm_partial(const TmaMap &w_map, const TmaMap &x_map, float *out, int T, int N, int K,

@@ -3,6 +3,7 @@
 // fp32 accumulate, one warp per pair of output rows, warp-shuffle reduction.
 // Algorithmic bytes per launch: 2*N*K (weights) + 2*T*K (activations, L1/L2 resident) + 4*T*N.
 #include "kernels.h"
+#include "ptx.cuh"
 
 namespace dis {
 
@@ -25,6 +26,8 @@ gemv_kernel(const uint16_t *__restrict__ X, const uint16_t *__restrict__ W, floa
             uint16_t *__restrict__ act, int N, int K) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int n0 = (blockIdx.x * kGemvWarps + warp) * kGemvRows;
+  pdl_launch_dependents();
+  pdl_wait();
   if (n0 >= N) return;
   constexpr int kW = kSilu ? 2 * kGemvRows : kGemvRows;  // weight rows streamed per warp
   const uint16_t *wrow[kW];
@@ -85,10 +88,10 @@ static cudaError_t gemv_dispatch(const uint16_t *X, const uint16_t *W, float *ou
     float *o = out ? out + (size_t)t0 * N : nullptr;
     uint16_t *a = act ? act + (size_t)t0 * N : nullptr;
     switch (tn) {
-      case 1: gemv_kernel<1, kSilu><<<blocks, kGemvWarps * 32, 0, st>>>(x, W, o, a, N, K); break;
-      case 2: gemv_kernel<2, kSilu><<<blocks, kGemvWarps * 32, 0, st>>>(x, W, o, a, N, K); break;
-      case 3: gemv_kernel<3, kSilu><<<blocks, kGemvWarps * 32, 0, st>>>(x, W, o, a, N, K); break;
-      default: gemv_kernel<4, kSilu><<<blocks, kGemvWarps * 32, 0, st>>>(x, W, o, a, N, K); break;
+      case 1: DIS_CUDA_TRY(launch_k(gemv_kernel<1, kSilu>, dim3(blocks), dim3(kGemvWarps * 32), 0, st, x, W, o, a, N, K)); break;
+      case 2: DIS_CUDA_TRY(launch_k(gemv_kernel<2, kSilu>, dim3(blocks), dim3(kGemvWarps * 32), 0, st, x, W, o, a, N, K)); break;
+      case 3: DIS_CUDA_TRY(launch_k(gemv_kernel<3, kSilu>, dim3(blocks), dim3(kGemvWarps * 32), 0, st, x, W, o, a, N, K)); break;
+      default: DIS_CUDA_TRY(launch_k(gemv_kernel<4, kSilu>, dim3(blocks), dim3(kGemvWarps * 32), 0, st, x, W, o, a, N, K)); break;
     }
     DIS_CUDA_TRY(cudaGetLastError());
   }

@@ -4,6 +4,9 @@
 
 namespace dis {
 
+// A 2-D bf16 row-major [rows][cols] tensor map with a {64, box_rows} box and 128-byte swizzle.
+struct TmaMap { alignas(64) unsigned char bytes[128]; };
+
 // k_elementwise.cu
 cudaError_t launch_add_rmsnorm(float *x, const uint32_t *tokens, const uint16_t *embed, const float *partial,
                                int n_partial, long long partial_stride, const float *gain, uint16_t *xn,
@@ -32,13 +35,14 @@ cudaError_t launch_gemv_silu(const uint16_t *X, const uint16_t *Wgu, uint16_t *a
 
 // k_attn_paged.cu
 size_t attn_scratch_elems(int T, int n_heads, int d, int n_splits);
-cudaError_t launch_attn_paged(const uint16_t *q, const uint16_t *kv_pool, const int *page_table, int max_pages,
-                              const int *pt_row, const int *ctx, uint16_t *out, float *scratch, int n_splits,
-                              int T, int n_heads, int n_kv, int d, int page_size, cudaStream_t st);
+// kv_map: make_kv_map over a pool of d-element rows [..][page][2][n_kv][page_size]; row0 = first row of the
+// layer to read (the engine keeps one map over all layers).
+cudaError_t make_kv_map(TmaMap *out, const uint16_t *pool, long long total_rows, int d, int page_size);
+cudaError_t launch_attn_paged(const TmaMap &kv_map, long long row0, const uint16_t *q, const int *page_table,
+                              int max_pages, const int *pt_row, const int *ctx, uint16_t *out, float *scratch,
+                              int n_splits, int T, int n_heads, int n_kv, int d, int page_size, cudaStream_t st);
 
 // k_gemm_tcgen05.cu
-// A 2-D bf16 row-major [rows][cols] tensor map with a {64, box_rows} box and 128-byte swizzle.
-struct TmaMap { alignas(64) unsigned char bytes[128]; };
 cudaError_t make_tma_map_2d(TmaMap *out, const void *base, uint64_t rows, uint64_t cols, uint32_t box_rows);
 int gemm_token_tile(int T);  // 32 / 64 / 128: the UMMA N used for T tokens
 // out[S][T][N] fp32 partials.  w_row0: first row of W's map to use (stacked per-layer weights).

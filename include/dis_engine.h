@@ -73,6 +73,7 @@ typedef struct dis_model_config {
  * accumulate only. */
 #define DIS_FLAG_NO_GRAPH 1u   /* do not capture the decode step in a CUDA graph */
 #define DIS_FLAG_FORCE_GEMV 2u /* debugging: run every projection through the GEMV kernel */
+#define DIS_FLAG_NO_PDL 4u     /* launch the kernels of a step without programmatic dependent launch */
 typedef struct dis_engine_config {
   dis_model_config model;
   int32_t device;              /* CUDA ordinal (WorkerConfig.gpu_layers has no meaning here) */
@@ -223,9 +224,10 @@ DIS_API int dis_k_rope_kv_write(const float *qkv, int32_t n_partial, int64_t par
                                 int32_t d, int32_t page_size, void *stream);
 /* Attention of each query token over its paged history (ctx[t] tokens, causal by construction).
  * out bf16 [T][nh*d].  n_splits > 1 uses `scratch` (fp32, dis_k_attn_scratch_elems()) for the
- * split-KV partials and a combine pass. */
+ * split-KV partials and a combine pass.  kv_pool holds n_pages pages (the TMA map is bounded by it);
+ * rows of a page that lie past ctx[t] must hold finite values (zero-fill the pool once). */
 DIS_API size_t dis_k_attn_scratch_elems(int32_t T, int32_t n_heads, int32_t d, int32_t n_splits);
-DIS_API int dis_k_attn_paged(const uint16_t *q, const uint16_t *kv_pool, const int32_t *page_table,
+DIS_API int dis_k_attn_paged(const uint16_t *q, const uint16_t *kv_pool, int64_t n_pages, const int32_t *page_table,
                              int32_t max_pages, const int32_t *pt_row, const int32_t *ctx, uint16_t *out,
                              float *scratch, int32_t n_splits, int32_t T, int32_t n_heads, int32_t n_kv,
                              int32_t d, int32_t page_size, void *stream);

@@ -135,7 +135,7 @@ def _paged_setup(rng, n_seq, ctx_lens, n_kv, d, page_size, n_pages):
     return pt, max_pages
 
 
-@pytest.mark.parametrize("d,nh,nkv", [(128, 8, 2), (64, 8, 2), (128, 4, 4), (64, 4, 2), (128, 8, 1)])
+@pytest.mark.parametrize("d,nh,nkv", [(128, 8, 2), (64, 8, 2), (128, 4, 4), (64, 4, 2), (128, 8, 1), (64, 16, 2)])
 def test_rope_kv_write_and_attention(d, nh, nkv):
     rng = np.random.default_rng(d + nh + nkv)
     page_size, n_pages, max_ctx = 16, 64, 256
@@ -190,11 +190,12 @@ def test_rope_kv_write_and_attention(d, nh, nkv):
         out = torch.empty((n_seq, nq), dtype=torch.bfloat16, device=DEV)
         n_scr = lib().dis_k_attn_scratch_elems(n_seq, nh, d, splits)
         scr = torch.empty(max(n_scr, 1), dtype=torch.float32, device=DEV)
-        check(lib().dis_k_attn_paged(ptr(dq), ptr(pool), ptr(dpt), max_pages, ptr(dev_i32(np.arange(n_seq))),
+        check(lib().dis_k_attn_paged(ptr(dq), ptr(pool), n_pages, ptr(dpt), max_pages, ptr(dev_i32(np.arange(n_seq))),
                                      ptr(dev_i32(ctx_lens)), ptr(out), ptr(scr), splits, n_seq, nh, nkv, d, page_size, None))
         sync()
         got = host(out)
-        assert np.abs(got - ref).max() <= BF16_ULP * np.abs(ref).max() * 1.05 + 1e-5, (splits, np.abs(got - ref).max())
+        # P is rounded to bf16 for the P.V tensor-core MMA: allow two bf16 ulps of the output scale
+        assert np.abs(got - ref).max() <= 2 * BF16_ULP * np.abs(ref).max() + 1e-5, (splits, np.abs(got - ref).max())
 
 
 def test_attention_long_context_tiles():
@@ -215,10 +216,10 @@ def test_attention_long_context_tiles():
     for splits in (1, 2, 5):
         out = torch.empty((1, nh * d), dtype=torch.bfloat16, device=DEV)
         scr = torch.empty(max(lib().dis_k_attn_scratch_elems(1, nh, d, splits), 1), dtype=torch.float32, device=DEV)
-        check(lib().dis_k_attn_paged(ptr(dev_bf16(q)), ptr(dpool), ptr(dev_i32(pt)), max_pages, ptr(dev_i32([0])),
+        check(lib().dis_k_attn_paged(ptr(dev_bf16(q)), ptr(dpool), n_pages, ptr(dev_i32(pt)), max_pages, ptr(dev_i32([0])),
                                      ptr(dev_i32([ctx])), ptr(out), ptr(scr), splits, 1, nh, nkv, d, page_size, None))
         sync()
-        assert np.abs(host(out)[0] - ref).max() <= BF16_ULP * np.abs(ref).max() * 1.05 + 1e-5
+        assert np.abs(host(out)[0] - ref).max() <= 2 * BF16_ULP * np.abs(ref).max() + 1e-5
 
 
 def test_sampler_argmax_and_ties():
