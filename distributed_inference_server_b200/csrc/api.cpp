@@ -136,10 +136,11 @@ static int gemm_common(const uint16_t *X, const uint16_t *W, float *out, uint16_
   if (int rc = need_gpu()) return rc;
   dis::TmaMap wm, xm;
   const int bn = dis::gemm_token_tile(T);
-  cudaError_t e = dis::make_tma_map_2d(&wm, W, (uint64_t)(silu ? 2 * N : N), (uint64_t)K, 128);
+  const int rows = silu ? dis::gemm_pick_tile_rows(N) : 128;
+  cudaError_t e = dis::make_tma_map_2d(&wm, W, (uint64_t)(silu ? 2 * N : N), (uint64_t)K, (uint32_t)rows);
   if (e == cudaSuccess) e = dis::make_tma_map_2d(&xm, X, (uint64_t)T, (uint64_t)K, (uint32_t)bn);
   if (e != cudaSuccess) return k_ret(e);
-  if (silu) return k_ret(dis::launch_gemm_silu(wm, xm, act, T, N, K, 0, st));
+  if (silu) return k_ret(dis::launch_gemm_silu(wm, xm, act, T, N, K, 0, rows, st));
   return k_ret(dis::launch_gemm_partial(wm, xm, out, T, N, K, 0, split, st));
 }
 int dis_k_gemm(const uint16_t *X, const uint16_t *W, float *out, int32_t T, int32_t N, int32_t K, int32_t split_k,

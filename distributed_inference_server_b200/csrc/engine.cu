@@ -6,6 +6,7 @@
 
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 
 namespace dis {
@@ -106,11 +107,22 @@ int Engine::init(const dis_engine_config *c) {
   ENG_CUDA(dev_alloc(&attn_norm, L * H, &bytes_allocated));
   ENG_CUDA(dev_alloc(&mlp_norm, L * H, &bytes_allocated));
   ENG_CUDA(dev_alloc(&final_norm, H, &bytes_allocated));
+  if (getenv("DIS_GEMM_TILED_FAKE")) {
+    // bandwidth experiment only (results are garbage): every weight box is a contiguous 16 KB block
+    gemm_tiled_flag() = 1;
+    const uint32_t gr = (uint32_t)gemm_pick_tile_rows(inter_l);
+    ENG_CUDA(make_tma_map_2d(&wqkv_map, wqkv, L * nqkv_l * H / 64, 64, 128));
+    ENG_CUDA(make_tma_map_2d(&wo_map, wo, L * H * qd_l / 64, 64, 128));
+    ENG_CUDA(make_tma_map_2d(&wgu_map, wgu, L * 2 * inter_l * H / 64, 64, gr));
+    ENG_CUDA(make_tma_map_2d(&wdown_map, wdown, L * H * inter_l / 64, 64, 128));
+    ENG_CUDA(make_tma_map_2d(&lm_map, lm_head, (size_t)vocab_l * H / 64, 64, 128));
+  } else {
   ENG_CUDA(make_tma_map_2d(&wqkv_map, wqkv, L * nqkv_l, H, 128));
   ENG_CUDA(make_tma_map_2d(&wo_map, wo, L * H, qd_l, 128));
-  ENG_CUDA(make_tma_map_2d(&wgu_map, wgu, L * 2 * inter_l, H, 128));
+  ENG_CUDA(make_tma_map_2d(&wgu_map, wgu, L * 2 * inter_l, H, (uint32_t)gemm_pick_tile_rows(inter_l)));
   ENG_CUDA(make_tma_map_2d(&wdown_map, wdown, L * H, inter_l, 128));
   ENG_CUDA(make_tma_map_2d(&lm_map, lm_head, vocab_l, H, 128));
+  }
   // ---- activations
   const size_t cap = cap_tokens;
   const size_t widest = std::max<size_t>(nqkv_l, H);
@@ -523,7 +535,7 @@ cudaError_t Engine::enqueue_layers(int T, int n_splits) {
       RET_CUDA(launch_gemv_silu(xn, wgu + (size_t)l * 2 * inter_l * H, act, T, inter_l, H, stream));
       kernel_launches += (uint64_t)((T + kGemvMaxT - 1) / kGemvMaxT);
     } else {
-      RET_CUDA(launch_gemm_silu(wgu_map, xn_map[tile_index(T)], act, T, inter_l, H, l * 2 * inter_l, stream));
+      RET_CUDA(launch_gemm_silu(wgu_map, xn_map[tile_index(T)], act, T, inter_l, H, l * 2 * inter_l, gemm_pick_tile_rows(inter_l), stream));
       kernel_launches++;
     }
     int s_d = 1;

@@ -97,7 +97,7 @@ template <int BN, bool kDual>
 __global__ void __launch_bounds__(kGemmThreads)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_constant__ CUtensorMap x_map,
                     float *__restrict__ out_partial, uint16_t *__restrict__ out_act, int T, int N, int K,
-                    int w_row0, int up_row_off, int kb_per_split) {
+                    int w_row0, int up_row_off, int kb_per_split, int tile_rows, int w_tiled) {
   using Cfg = GemmCfg<BN, kDual>;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -112,7 +112,15 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_cons
   auto b_tile = [&](int s) { return a_tile(s) + (kDual ? 2 : 1) * Cfg::kABytes; };
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int n0 = blockIdx.x * kBM;
+  // tile_rows (<= 128, the weight map's box height) output features per CTA: a 128-row MMA runs on a
+  // partly filled A tile; lanes >= tile_rows compute on stale shared memory and are never stored.
+  const int n0 = blockIdx.x * tile_rows;
+  const int num_kb_all = (K + kBK - 1) / kBK;
+  // w_tiled: the weight is stored tile-major, [row tile][k-block][tile_rows][64] (each TMA box is one contiguous
+  // block of DRAM); the map then is [rows][64] and a box is addressed by its block index.
+  auto a_c0 = [&](int kb) { return w_tiled ? 0 : kb * kBK; };
+  auto a_c1 = [&](int kb, int row_base) { return w_tiled ? ((row_base / tile_rows) * num_kb_all + kb) * tile_rows : row_base; };
+  const uint32_t stage_tx = (uint32_t)((kDual ? 2 : 1) * tile_rows * kBK * 2 + Cfg::kBBytes);
   const int t0 = blockIdx.y * BN;
   const int num_kb = (K + kBK - 1) / kBK;
   const int kb0 = blockIdx.z * kb_per_split;
@@ -141,9 +149,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_cons
       // then wait for the producer of the activations (programmatic dependent launch).
       const int pre = min(kb1 - kb0, Cfg::kStages);
       for (int i = 0; i < pre; i++) {
-        mbar_expect_tx(full_bar(i), Cfg::kStageBytes);
-        tma_load_2d(a_tile(i), &w_map, (kb0 + i) * kBK, w_row0 + n0, full_bar(i), kEvictFirst);
-        if (kDual) tma_load_2d(a2_tile(i), &w_map, (kb0 + i) * kBK, w_row0 + up_row_off + n0, full_bar(i), kEvictFirst);
+        mbar_expect_tx(full_bar(i), stage_tx);
+        tma_load_2d(a_tile(i), &w_map, a_c0(kb0 + i), a_c1(kb0 + i, w_row0 + n0), full_bar(i), kEvictFirst);
+        if (kDual) tma_load_2d(a2_tile(i), &w_map, a_c0(kb0 + i), a_c1(kb0 + i, w_row0 + up_row_off + n0), full_bar(i), kEvictFirst);
       }
       pdl_wait();
       for (int i = 0; i < pre; i++) tma_load_2d(b_tile(i), &x_map, (kb0 + i) * kBK, t0, full_bar(i), kEvictLast);
@@ -151,9 +159,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_cons
       uint32_t phase = pre == Cfg::kStages ? 1u : 0u;
       for (int kb = kb0 + pre; kb < kb1; kb++) {
         mbar_wait(empty_bar(s), phase ^ 1u);
-        mbar_expect_tx(full_bar(s), Cfg::kStageBytes);
-        tma_load_2d(a_tile(s), &w_map, kb * kBK, w_row0 + n0, full_bar(s), kEvictFirst);
-        if (kDual) tma_load_2d(a2_tile(s), &w_map, kb * kBK, w_row0 + up_row_off + n0, full_bar(s), kEvictFirst);
+        mbar_expect_tx(full_bar(s), stage_tx);
+        tma_load_2d(a_tile(s), &w_map, a_c0(kb), a_c1(kb, w_row0 + n0), full_bar(s), kEvictFirst);
+        if (kDual) tma_load_2d(a2_tile(s), &w_map, a_c0(kb), a_c1(kb, w_row0 + up_row_off + n0), full_bar(s), kEvictFirst);
         tma_load_2d(b_tile(s), &x_map, kb * kBK, t0, full_bar(s), kEvictLast);
         if (++s == Cfg::kStages) { s = 0; phase ^= 1u; }
       }
@@ -185,7 +193,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_cons
     tc_fence_after();
     pdl_wait();  // global writes only after every prerequisite grid has completed
     const int quarter = warp & 3;  // a warp may only touch TMEM lanes [32*(warp%4), +32)
-    const int n = n0 + quarter * 32 + lane;
+    const int n = (quarter * 32 + lane < tile_rows) ? n0 + quarter * 32 + lane : N;  // N = masked
     const uint32_t lane_addr = tmem_base + ((uint32_t)(quarter * 32) << 16);
 #pragma unroll 1
     for (int c = 0; c < BN; c += 32) {
@@ -256,6 +264,8 @@ cudaError_t make_tma_map_2d(TmaMap *out, const void *base, uint64_t rows, uint64
   return cudaSuccess;
 }
 
+int &gemm_tiled_flag() { static int f = 0; return f; }
+
 int gemm_token_tile(int T) { return T <= 32 ? 32 : (T <= 64 ? 64 : 128); }
 
 // Split-K factor: enough CTAs to keep every SM streaming (two CTAs per SM), each with >= 4 k-blocks.
@@ -274,7 +284,7 @@ int gemm_pick_split_k(int T, int N, int K) {
 
 template <int BN, bool kDual>
 static cudaError_t gemm_launch(const TmaMap &w_map, const TmaMap &x_map, float *out, uint16_t *act, int T, int N,
-                               int K, int w_row0, int up_off, int split_k, cudaStream_t st) {
+                               int K, int w_row0, int up_off, int split_k, int tile_rows, cudaStream_t st) {
   using Cfg = GemmCfg<BN, kDual>;
   auto kern = gemm_tcgen05_kernel<BN, kDual>;
   static bool attr_set = false;
@@ -285,9 +295,10 @@ static cudaError_t gemm_launch(const TmaMap &w_map, const TmaMap &x_map, float *
   const int num_kb = (K + kBK - 1) / kBK;
   const int per = (num_kb + split_k - 1) / split_k;
   if ((num_kb + per - 1) / per != split_k) { set_last_error("gemm: split_k leaves an empty K slice; use gemm_pick_split_k"); return cudaErrorInvalidValue; }
-  dim3 grid((N + kBM - 1) / kBM, (T + BN - 1) / BN, split_k);
+  if (tile_rows < 8 || tile_rows > kBM || tile_rows % 8) { set_last_error("gemm: tile_rows must be a multiple of 8 in [8, 128]"); return cudaErrorInvalidValue; }
+  dim3 grid((N + tile_rows - 1) / tile_rows, (T + BN - 1) / BN, split_k);
   return launch_k(kern, grid, dim3(kGemmThreads), Cfg::kSmemBytes, st, *reinterpret_cast<const CUtensorMap *>(&w_map),
-                  *reinterpret_cast<const CUtensorMap *>(&x_map), out, act, T, N, K, w_row0, up_off, per);
+                  *reinterpret_cast<const CUtensorMap *>(&x_map), out, act, T, N, K, w_row0, up_off, per, tile_rows, gemm_tiled_flag());
 }
 
 cudaError_t launch_gemm_partial(const TmaMap &w_map, const TmaMap &x_map, float *out, int T, int N, int K,
@@ -295,19 +306,27 @@ cudaError_t launch_gemm_partial(const TmaMap &w_map, const TmaMap &x_map, float 
   if (T <= 0) return cudaSuccess;
   if (split_k < 1) { set_last_error("gemm: split_k must be >= 1"); return cudaErrorInvalidValue; }
   switch (gemm_token_tile(T)) {
-    case 32: return gemm_launch<32, false>(w_map, x_map, out, nullptr, T, N, K, w_row0, 0, split_k, st);
-    case 64: return gemm_launch<64, false>(w_map, x_map, out, nullptr, T, N, K, w_row0, 0, split_k, st);
-    default: return gemm_launch<128, false>(w_map, x_map, out, nullptr, T, N, K, w_row0, 0, split_k, st);
+    case 32: return gemm_launch<32, false>(w_map, x_map, out, nullptr, T, N, K, w_row0, 0, split_k, kBM, st);
+    case 64: return gemm_launch<64, false>(w_map, x_map, out, nullptr, T, N, K, w_row0, 0, split_k, kBM, st);
+    default: return gemm_launch<128, false>(w_map, x_map, out, nullptr, T, N, K, w_row0, 0, split_k, kBM, st);
   }
 }
 
+// Output features per CTA for the single-pass (no split-K) gate-up projection: as few CTAs as possible
+// with at most one per SM, so that every SM streams the same share of the weight
+// (128-row tiles put 14336 rows on 112 of 148 SMs: measured 76 % of the 148-SM rate).
+int gemm_pick_tile_rows(int N) {
+  int r = ((N + kNumSMs - 1) / kNumSMs + 7) / 8 * 8;
+  return r > kBM ? kBM : (r < 8 ? 8 : r);
+}
+
 cudaError_t launch_gemm_silu(const TmaMap &w_map, const TmaMap &x_map, uint16_t *act, int T, int I, int K,
-                             int w_row0, cudaStream_t st) {
+                             int w_row0, int tile_rows, cudaStream_t st) {
   if (T <= 0) return cudaSuccess;
   switch (gemm_token_tile(T)) {
-    case 32: return gemm_launch<32, true>(w_map, x_map, nullptr, act, T, I, K, w_row0, I, 1, st);
-    case 64: return gemm_launch<64, true>(w_map, x_map, nullptr, act, T, I, K, w_row0, I, 1, st);
-    default: return gemm_launch<128, true>(w_map, x_map, nullptr, act, T, I, K, w_row0, I, 1, st);
+    case 32: return gemm_launch<32, true>(w_map, x_map, nullptr, act, T, I, K, w_row0, I, 1, tile_rows, st);
+    case 64: return gemm_launch<64, true>(w_map, x_map, nullptr, act, T, I, K, w_row0, I, 1, tile_rows, st);
+    default: return gemm_launch<128, true>(w_map, x_map, nullptr, act, T, I, K, w_row0, I, 1, tile_rows, st);
   }
 }
 

@@ -48,9 +48,12 @@ int gemm_token_tile(int T);  // 32 / 64 / 128: the UMMA N used for T tokens
 // out[S][T][N] fp32 partials.  w_row0: first row of W's map to use (stacked per-layer weights).
 cudaError_t launch_gemm_partial(const TmaMap &w_map, const TmaMap &x_map, float *out, int T, int N, int K,
                                 int w_row0, int split_k, cudaStream_t st);
-// act[T][I] = bf16(silu(gate) * up); gate rows at w_row0, up rows at w_row0 + I.
+// act[T][I] = bf16(silu(gate) * up); gate rows at w_row0, up rows at w_row0 + I.  w_map's box height must be
+// tile_rows = gemm_pick_tile_rows(I).
+int gemm_pick_tile_rows(int N);
 cudaError_t launch_gemm_silu(const TmaMap &w_map, const TmaMap &x_map, uint16_t *act, int T, int I, int K,
-                             int w_row0, cudaStream_t st);
+                             int w_row0, int tile_rows, cudaStream_t st);
 int gemm_pick_split_k(int T, int N, int K);
+int &gemm_tiled_flag();  // experiment: weights addressed as tile-major blocks
 
 }  // namespace dis

@@ -131,9 +131,10 @@ def test_ragged_batch_greedy_matches_oracle(flags):
     n_new = 24
     got, _ = greedy(e, prompts, n_new)
     assert_greedy_matches(got, mimic, prompts, n_new, "ragged")
-    # the cache is reusable: a second round in the same engine gives the same tokens
+    # the cache is reusable: a second round in the same engine, in another batch order (stream-K split points
+    # depend on the tile a token lands in, so fp32 summation order -- not the result's validity -- may change)
     got2, _ = greedy(e, prompts[::-1], n_new)
-    assert got2 == got[::-1]
+    assert_greedy_matches(got2, mimic, prompts[::-1], n_new, "ragged-reversed")
     e.close()
 
 

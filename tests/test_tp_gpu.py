@@ -1,0 +1,84 @@
+"""Tensor parallel engine on 2 GPUs (skipped on a single-GPU box): one process per GPU, NCCL all-reduce
+after the O and down projections, vocab-parallel lm_head.  Checked against the oracle and against the
+product's shard plan (each rank's weights are exactly the plan's slice of the synthetic tensors)."""
+import ctypes as C
+import os
+
+import numpy as np
+import pytest
+import torch
+import torch.multiprocessing as mp
+
+from oracle import oracle as O
+
+pytestmark = pytest.mark.gpu
+SHAPE = O.ModelShape(2048, 512, 3, 8, 2, 64, 1408, 256)
+SEED = 21
+
+
+def _rank(rank, world, idq, outq, prompts, n_new, temps):
+    from distributed_inference_server_b200 import Engine, InferenceParams, WorkerConfig, shard_plan as SP
+    from distributed_inference_server_b200 import binding as B
+    from tests._gpu_util import to_engine_shape
+    torch.cuda.set_device(rank)
+    if rank == 0:
+        buf = (C.c_uint8 * 128)()
+        assert B.load().dis_tp_unique_id(buf) == 0, B.load().dis_last_error()
+        for _ in range(world - 1):
+            idq.put(bytes(buf))
+        nccl_id = bytes(buf)
+    else:
+        nccl_id = idq.get(timeout=120)
+    e = Engine(WorkerConfig(to_engine_shape(SHAPE), device=rank, tp_rank=rank, tp_size=world, max_batch=8, kv_pages=64,
+                            page_size=16, max_step_tokens=256, nccl_id=nccl_id))
+    e.load_synthetic(SEED)
+    e.finalize()
+    # each rank holds exactly the plan's slice
+    for kind, layer in [(O.WQ, 1), (O.WK, 0), (O.WV, 2), (O.WO, 1), (O.WGATE, 0), (O.WUP, 2), (O.WDOWN, 1), (O.LM_HEAD, 0), (O.EMBED, 0)]:
+        got = O.from_bf16_bits(e.read_tensor(kind, layer))
+        want = O.synth_tensor(SHAPE, SEED, kind, layer)[SP.shard_slices(SHAPE, kind, rank, world)].reshape(-1)
+        assert np.array_equal(got, want), (rank, kind, layer)
+    slots = [e.seq_add(p, InferenceParams(max_tokens=n_new + 1, temperature=t, top_p=0.9, seed=5)) for p, t in zip(prompts, temps)]
+    toks, _ = e.prefill(slots)
+    out = [[int(t)] for t in toks]
+    logits0 = e.last_logits(len(slots))
+    for _ in range(n_new - 1):
+        toks, _ = e.decode(slots)
+        for i, t in enumerate(toks):
+            out[i].append(int(t))
+    outq.put((rank, out, logits0))
+    e.close()
+
+
+@pytest.mark.skipif(not torch.cuda.is_available() or torch.cuda.device_count() < 2, reason="needs 2 GPUs")
+@pytest.mark.parametrize("sampled", [False, True], ids=["greedy", "sampled"])
+def test_tp2_matches_oracle(sampled):
+    world, n_new = 2, 12
+    rng = np.random.default_rng(2)
+    prompts = [rng.integers(0, SHAPE.vocab, n).tolist() for n in (7, 33, 18)]
+    temps = [0.7, 0.0, 1.1] if sampled else [0.0, 0.0, 0.0]
+    ctx = mp.get_context("spawn")
+    idq, outq = ctx.Queue(), ctx.Queue()
+    procs = [ctx.Process(target=_rank, args=(r, world, idq, outq, prompts, n_new, temps)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = {}
+    for _ in range(world):
+        r, out, lg = outq.get(timeout=300)
+        res[r] = (out, lg)
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert res[0][0] == res[1][0]                       # every rank yields the same tokens
+    assert np.array_equal(res[0][1], res[1][1])         # and the same gathered logits
+    ref = O.Oracle(SHAPE, act_round=False); ref.fill_synthetic(SEED, True)
+    want = ref.generate(prompts, 1, n_logit_steps=1)
+    rel = np.abs(res[0][1] - want["logits"][:, 0]).max() / np.abs(want["logits"]).max()
+    assert rel <= 2e-2, rel
+    if not sampled:
+        mimic = O.Oracle(SHAPE, act_round=True); mimic.fill_synthetic(SEED, True)
+        w = mimic.generate(prompts, n_new, n_logit_steps=n_new)
+        for b in range(len(prompts)):
+            if res[0][0][b] != w["tokens"][b]:
+                i = next(k for k in range(n_new) if res[0][0][b][k] != w["tokens"][b][k])
+                assert w["margins"][b, i] <= 5e-3 * np.abs(w["logits"][b, i]).max(), (b, i)
