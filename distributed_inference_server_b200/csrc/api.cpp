@@ -180,6 +180,17 @@ int dis_k_attn_paged(const uint16_t *q, const uint16_t *kv_pool, int64_t n_pages
   return k_ret(dis::launch_attn_paged(map, 0, q, page_table, max_pages, pt_row, ctx, out, scratch, n_splits, T, n_heads, n_kv,
                                       d, page_size, (cudaStream_t)stream));
 }
+int dis_k_attn_prefill(const uint16_t *q, const uint16_t *kv_pool, int64_t n_pages, const int32_t *page_table,
+                       int32_t max_pages, const int32_t *qb_tok0, const int32_t *qb_len, const int32_t *qb_pos0,
+                       const int32_t *qb_ptrow, uint16_t *out, int32_t n_blocks, int32_t n_heads, int32_t n_kv, int32_t d,
+                       int32_t page_size, void *stream) {
+  if (int rc = need_gpu()) return rc;
+  dis::TmaMap map;
+  cudaError_t e = dis::make_kv_map(&map, kv_pool, (long long)n_pages * 2 * n_kv * page_size, d, page_size);
+  if (e != cudaSuccess) return k_ret(e);
+  return k_ret(dis::launch_attn_prefill(map, 0, q, page_table, max_pages, qb_tok0, qb_len, qb_pos0, qb_ptrow, out, n_blocks,
+                                        n_heads, n_kv, d, page_size, (cudaStream_t)stream));
+}
 int dis_k_sample(const float *logits, int64_t ld, int32_t T, int32_t V, const float *temperature, const float *top_p,
                  const uint64_t *seeds, const uint64_t *steps, uint32_t *out_tokens, void *stream) {
   if (int rc = need_gpu()) return rc;

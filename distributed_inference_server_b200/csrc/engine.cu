@@ -107,22 +107,11 @@ int Engine::init(const dis_engine_config *c) {
   ENG_CUDA(dev_alloc(&attn_norm, L * H, &bytes_allocated));
   ENG_CUDA(dev_alloc(&mlp_norm, L * H, &bytes_allocated));
   ENG_CUDA(dev_alloc(&final_norm, H, &bytes_allocated));
-  if (getenv("DIS_GEMM_TILED_FAKE")) {
-    // bandwidth experiment only (results are garbage): every weight box is a contiguous 16 KB block
-    gemm_tiled_flag() = 1;
-    const uint32_t gr = (uint32_t)gemm_pick_tile_rows(inter_l);
-    ENG_CUDA(make_tma_map_2d(&wqkv_map, wqkv, L * nqkv_l * H / 64, 64, 128));
-    ENG_CUDA(make_tma_map_2d(&wo_map, wo, L * H * qd_l / 64, 64, 128));
-    ENG_CUDA(make_tma_map_2d(&wgu_map, wgu, L * 2 * inter_l * H / 64, 64, gr));
-    ENG_CUDA(make_tma_map_2d(&wdown_map, wdown, L * H * inter_l / 64, 64, 128));
-    ENG_CUDA(make_tma_map_2d(&lm_map, lm_head, (size_t)vocab_l * H / 64, 64, 128));
-  } else {
   ENG_CUDA(make_tma_map_2d(&wqkv_map, wqkv, L * nqkv_l, H, 128));
   ENG_CUDA(make_tma_map_2d(&wo_map, wo, L * H, qd_l, 128));
   ENG_CUDA(make_tma_map_2d(&wgu_map, wgu, L * 2 * inter_l, H, (uint32_t)gemm_pick_tile_rows(inter_l)));
   ENG_CUDA(make_tma_map_2d(&wdown_map, wdown, L * H, inter_l, 128));
   ENG_CUDA(make_tma_map_2d(&lm_map, lm_head, vocab_l, H, 128));
-  }
   // ---- activations
   const size_t cap = cap_tokens;
   const size_t widest = std::max<size_t>(nqkv_l, H);
@@ -169,21 +158,26 @@ int Engine::init(const dis_engine_config *c) {
     ENG_CUDA(cudaMemcpy(rope_cos, cs.data(), cs.size() * 4, cudaMemcpyHostToDevice));
     ENG_CUDA(cudaMemcpy(rope_sin, sn.data(), sn.size() * 4, cudaMemcpyHostToDevice));
   }
-  // ---- step metadata
-  {
-    StepMeta &s = meta;
-    s.cap_tokens = cap_tokens;
+  // ---- step metadata: a small block for decode steps (one H2D copy per step) and a large one for prefill chunks
+  auto make_meta = [&](StepMeta &s, int cap_t) -> cudaError_t {
+    s.cap_tokens = cap_t;
     s.cap_rows = max_batch;
     size_t o = 0;
     auto sec = [&](size_t bytes) { size_t at = o; o = align_up(o + bytes, 16); return at; };
-    s.o_tokens = sec(cap * 4); s.o_pos = sec(cap * 4); s.o_ptrow = sec(cap * 4); s.o_ctx = sec(cap * 4);
+    const size_t ct = (size_t)cap_t;
+    s.o_tokens = sec(ct * 4); s.o_pos = sec(ct * 4); s.o_ptrow = sec(ct * 4); s.o_ctx = sec(ct * 4);
     s.o_rowmap = sec((size_t)max_batch * 4); s.o_temp = sec((size_t)max_batch * 4); s.o_topp = sec((size_t)max_batch * 4);
     s.o_seed = sec((size_t)max_batch * 8); s.o_step = sec((size_t)max_batch * 8);
+    s.o_qb_tok0 = sec(ct * 4); s.o_qb_len = sec(ct * 4); s.o_qb_pos0 = sec(ct * 4); s.o_qb_ptrow = sec(ct * 4);
     s.bytes = o;
-    ENG_CUDA(cudaMallocHost(reinterpret_cast<void **>(&s.host), s.bytes));
-    ENG_CUDA(dev_alloc(&s.dev, s.bytes, &bytes_allocated));
+    cudaError_t e1 = cudaMallocHost(reinterpret_cast<void **>(&s.host), s.bytes);
+    if (e1 != cudaSuccess) return e1;
     memset(s.host, 0, s.bytes);
-  }
+    return dev_alloc(&s.dev, s.bytes, &bytes_allocated);
+  };
+  ENG_CUDA(make_meta(meta_dec, max_batch));
+  ENG_CUDA(make_meta(meta_pre, cap_tokens));
+  cur_meta = &meta_dec;
   // ---- KV pages: [layer][page][2][nkv_l][page_size][d]
   {
     const size_t page_elems = (size_t)2 * nkv_l * page_size * m.head_dim;
@@ -235,11 +229,12 @@ Engine::~Engine() {
   if (comm && nccl) nccl->CommDestroy(comm);
   void *ptrs[] = {embed, wqkv, wo, wgu, wdown, lm_head, attn_norm, mlp_norm, final_norm, x, partial, logits, ar_buf,
                   attn_scratch, full_logits, gather_buf, cand_val, cand_val_all, cand_tok, cand_tok_all, xn, q, attn,
-                  act, d_out_tokens, kv_pool, d_page_table, rope_cos, rope_sin, meta.dev};
+                  act, d_out_tokens, kv_pool, d_page_table, rope_cos, rope_sin, meta_dec.dev, meta_pre.dev};
   for (void *p : ptrs) if (p) cudaFree(p);
   if (h_out_tokens) cudaFreeHost(h_out_tokens);
   if (h_page_table) cudaFreeHost(h_page_table);
-  if (meta.host) cudaFreeHost(meta.host);
+  if (meta_dec.host) cudaFreeHost(meta_dec.host);
+  if (meta_pre.host) cudaFreeHost(meta_pre.host);
   if (ev0) cudaEventDestroy(ev0);
   if (ev1) cudaEventDestroy(ev1);
   if (own_stream && stream) cudaStreamDestroy(stream);
@@ -452,7 +447,7 @@ cudaError_t Engine::upload_step(int T, int R) {
     pt_dirty = false;
   }
   (void)T; (void)R;
-  return cudaMemcpyAsync(meta.dev, meta.host, meta.bytes, cudaMemcpyHostToDevice, stream);
+  return cudaMemcpyAsync(cur_meta->dev, cur_meta->host, cur_meta->bytes, cudaMemcpyHostToDevice, stream);
 }
 
 int Engine::pick_attn_splits(int T, int max_ctx_in_batch) const {
@@ -500,8 +495,8 @@ cudaError_t Engine::enqueue_layers(int T, int n_splits) {
   const float *pend = nullptr;  // projection output waiting to be added to the residual
   int pend_n = 0;
   long long pend_stride = 0;
-  const uint32_t *tokens = meta.d<uint32_t>(meta.o_tokens);
-  const int *pos = meta.d<int>(meta.o_pos), *ptrow = meta.d<int>(meta.o_ptrow), *ctx = meta.d<int>(meta.o_ctx);
+  const uint32_t *tokens = cur_meta->d<uint32_t>(cur_meta->o_tokens);
+  const int *pos = cur_meta->d<int>(cur_meta->o_pos), *ptrow = cur_meta->d<int>(cur_meta->o_ptrow), *ctx = cur_meta->d<int>(cur_meta->o_ctx);
   for (int l = 0; l < m.layers; l++) {
     // x (+)= pending; xn = RMSNorm(x)
     prof_mark(P_NORM);
@@ -518,9 +513,17 @@ cudaError_t Engine::enqueue_layers(int T, int n_splits) {
     RET_CUDA(launch_rope_kv_write(partial, s_qkv, (long long)T * nqkv_l, q, pool, d_page_table, max_pages, ptrow, pos,
                                   rope_cos, rope_sin, T, nh_l, nkv_l, d, page_size, stream));
     prof_mark(P_ATTN);
-    RET_CUDA(launch_attn_paged(kv_map, (long long)l * kv_rows_per_layer, q, d_page_table, max_pages, ptrow, ctx, attn,
-                               attn_scratch, n_splits, T, nh_l, nkv_l, d, page_size, stream));
-    kernel_launches += n_splits > 1 ? 3 : 2;
+    if (n_qblocks > 0) {
+      RET_CUDA(launch_attn_prefill(kv_map, (long long)l * kv_rows_per_layer, q, d_page_table, max_pages,
+                                   cur_meta->d<int>(cur_meta->o_qb_tok0), cur_meta->d<int>(cur_meta->o_qb_len),
+                                   cur_meta->d<int>(cur_meta->o_qb_pos0), cur_meta->d<int>(cur_meta->o_qb_ptrow), attn,
+                                   n_qblocks, nh_l, nkv_l, d, page_size, stream));
+      kernel_launches += 2;
+    } else {
+      RET_CUDA(launch_attn_paged(kv_map, (long long)l * kv_rows_per_layer, q, d_page_table, max_pages, ptrow, ctx, attn,
+                                 attn_scratch, n_splits, T, nh_l, nkv_l, d, page_size, stream));
+      kernel_launches += n_splits > 1 ? 3 : 2;
+    }
     int s_o = 1;
     prof_mark(P_OPROJ);
     RET_CUDA(linear_partial(attn_map, attn, wo_map, wo, l * H, T, H, qd_l, &s_o));
@@ -554,15 +557,15 @@ cudaError_t Engine::enqueue_head(int R, bool all_greedy) {
   const int H = m.hidden;
   prof_mark(P_HEAD_NORM);
   RET_CUDA(launch_add_rmsnorm(x, nullptr, nullptr, pend_ptr, pend_count, pend_str, final_norm, xn,
-                              meta.d<int>(meta.o_rowmap), R, H, m.rms_eps, stream));
+                              cur_meta->d<int>(cur_meta->o_rowmap), R, H, m.rms_eps, stream));
   kernel_launches++;
   const bool gemv = (cfg.flags & DIS_FLAG_FORCE_GEMV) || R <= 2;
   prof_mark(P_LM_HEAD);
   if (gemv) { RET_CUDA(launch_gemv(xn, lm_head, logits, R, vocab_l, H, stream)); kernel_launches += (uint64_t)((R + kGemvMaxT - 1) / kGemvMaxT); }
   else { RET_CUDA(launch_gemm_partial(lm_map, xn_map[tile_index(R)], logits, R, vocab_l, H, 0, 1, stream)); kernel_launches++; }
   prof_mark(P_SAMPLE);
-  const float *temp = meta.d<float>(meta.o_temp), *topp = meta.d<float>(meta.o_topp);
-  const unsigned long long *seed = meta.d<unsigned long long>(meta.o_seed), *step = meta.d<unsigned long long>(meta.o_step);
+  const float *temp = cur_meta->d<float>(cur_meta->o_temp), *topp = cur_meta->d<float>(cur_meta->o_topp);
+  const unsigned long long *seed = cur_meta->d<unsigned long long>(cur_meta->o_seed), *step = cur_meta->d<unsigned long long>(cur_meta->o_step);
   if (tp_size == 1) {
     kernel_launches++;
     return launch_sample(logits, vocab_l, R, vocab_l, temp, topp, seed, step, d_out_tokens, 0, nullptr, stream);
@@ -611,37 +614,48 @@ int Engine::prefill(int n, const int *slots, uint32_t *out_tokens, int *out_fini
   }
   ENG_CUDA(cudaSetDevice(cfg.device));
   ENG_CUDA(cudaEventRecord(ev0, stream));
+  cur_meta = &meta_pre;
+  struct MetaReset { Engine *e; ~MetaReset() { e->cur_meta = &e->meta_dec; e->n_qblocks = 0; } } meta_reset{this};
   // flatten (sequence, position) pairs and cut them into chunks of at most cap_tokens
   int si = 0, sp = 0;  // next sequence index / position inside it
   bool all_greedy = true;
   for (int i = 0; i < n; i++) all_greedy = all_greedy && seqs[(size_t)slots[i]].temperature <= 0.f;
   while (si < n) {
-    int T = 0, R = 0;
+    int T = 0, R = 0, QB = 0;
     std::vector<int> owners;
     while (si < n && T < cap_tokens) {
       Sequence &s = seqs[(size_t)slots[si]];
       const int total = (int)s.prompt.size();
       const int take = std::min(total - sp, cap_tokens - T);
       for (int k = 0; k < take; k++) {
-        meta.h<uint32_t>(meta.o_tokens)[T + k] = s.prompt[(size_t)(sp + k)];
-        meta.h<int>(meta.o_pos)[T + k] = sp + k;
-        meta.h<int>(meta.o_ptrow)[T + k] = slots[si];
-        meta.h<int>(meta.o_ctx)[T + k] = sp + k + 1;
+        cur_meta->h<uint32_t>(cur_meta->o_tokens)[T + k] = s.prompt[(size_t)(sp + k)];
+        cur_meta->h<int>(cur_meta->o_pos)[T + k] = sp + k;
+        cur_meta->h<int>(cur_meta->o_ptrow)[T + k] = slots[si];
+        cur_meta->h<int>(cur_meta->o_ctx)[T + k] = sp + k + 1;
+      }
+      // query blocks of up to 16 consecutive tokens for the prefill attention kernel
+      for (int k = 0; k < take; k += 16) {
+        cur_meta->h<int>(cur_meta->o_qb_tok0)[QB] = T + k;
+        cur_meta->h<int>(cur_meta->o_qb_len)[QB] = std::min(16, take - k);
+        cur_meta->h<int>(cur_meta->o_qb_pos0)[QB] = sp + k;
+        cur_meta->h<int>(cur_meta->o_qb_ptrow)[QB] = slots[si];
+        QB++;
       }
       T += take;
       sp += take;
       if (sp == total) {
-        meta.h<int>(meta.o_rowmap)[R] = T - 1;
-        meta.h<float>(meta.o_temp)[R] = s.temperature;
-        meta.h<float>(meta.o_topp)[R] = s.top_p;
-        meta.h<unsigned long long>(meta.o_seed)[R] = s.seed;
-        meta.h<unsigned long long>(meta.o_step)[R] = 0;
+        cur_meta->h<int>(cur_meta->o_rowmap)[R] = T - 1;
+        cur_meta->h<float>(cur_meta->o_temp)[R] = s.temperature;
+        cur_meta->h<float>(cur_meta->o_topp)[R] = s.top_p;
+        cur_meta->h<unsigned long long>(cur_meta->o_seed)[R] = s.seed;
+        cur_meta->h<unsigned long long>(cur_meta->o_step)[R] = 0;
         owners.push_back(si);
         R++;
         si++;
         sp = 0;
       }
     }
+    n_qblocks = QB;
     ENG_CUDA(upload_step(T, R));
     ENG_CUDA(enqueue_layers(T, 1));
     if (R > 0) {
@@ -691,15 +705,15 @@ int Engine::decode(int n, const int *slots, uint32_t *out_tokens, int *out_finis
     if (s.finish != DIS_FINISH_NONE) { out_finish[i] = s.finish; continue; }
     if (s.len + 1 > m.max_ctx || !ensure_pages(s, slots[i], s.len + 1)) { s.finish = DIS_FINISH_FAILED; out_finish[i] = s.finish; continue; }
     const int r = (int)live.size();
-    meta.h<uint32_t>(meta.o_tokens)[r] = s.last_token;
-    meta.h<int>(meta.o_pos)[r] = s.len;
-    meta.h<int>(meta.o_ptrow)[r] = slots[i];
-    meta.h<int>(meta.o_ctx)[r] = s.len + 1;
-    meta.h<int>(meta.o_rowmap)[r] = r;
-    meta.h<float>(meta.o_temp)[r] = s.temperature;
-    meta.h<float>(meta.o_topp)[r] = s.top_p;
-    meta.h<unsigned long long>(meta.o_seed)[r] = s.seed;
-    meta.h<unsigned long long>(meta.o_step)[r] = (unsigned long long)s.generated;
+    cur_meta->h<uint32_t>(cur_meta->o_tokens)[r] = s.last_token;
+    cur_meta->h<int>(cur_meta->o_pos)[r] = s.len;
+    cur_meta->h<int>(cur_meta->o_ptrow)[r] = slots[i];
+    cur_meta->h<int>(cur_meta->o_ctx)[r] = s.len + 1;
+    cur_meta->h<int>(cur_meta->o_rowmap)[r] = r;
+    cur_meta->h<float>(cur_meta->o_temp)[r] = s.temperature;
+    cur_meta->h<float>(cur_meta->o_topp)[r] = s.top_p;
+    cur_meta->h<unsigned long long>(cur_meta->o_seed)[r] = s.seed;
+    cur_meta->h<unsigned long long>(cur_meta->o_step)[r] = (unsigned long long)s.generated;
     all_greedy = all_greedy && s.temperature <= 0.f;
     max_ctx_b = std::max(max_ctx_b, s.len + 1);
     live.push_back(i);

@@ -50,6 +50,7 @@ struct StepMeta {
   uint8_t *dev = nullptr;
   // sections (offsets in bytes)
   size_t o_tokens, o_pos, o_ptrow, o_ctx, o_rowmap, o_temp, o_topp, o_seed, o_step;
+  size_t o_qb_tok0, o_qb_len, o_qb_pos0, o_qb_ptrow;  // prefill query blocks
   template <class T_> T_ *h(size_t off) { return reinterpret_cast<T_ *>(host + off); }
   template <class T_> T_ *d(size_t off) { return reinterpret_cast<T_ *>(dev + off); }
 };
@@ -93,7 +94,9 @@ struct Engine {
   int *d_page_table = nullptr, *h_page_table = nullptr;
   bool pt_dirty = true;
   float *rope_cos = nullptr, *rope_sin = nullptr;
-  StepMeta meta;
+  StepMeta meta_dec, meta_pre;      // decode steps / prefill chunks
+  StepMeta *cur_meta = &meta_dec;
+  int n_qblocks = 0;                // > 0 while a prefill chunk is being enqueued
   std::vector<Sequence> seqs;
   int last_rows = 0;  // logits rows of the last call
   // decode graphs keyed by (T, n_splits, all_greedy)

@@ -250,6 +250,187 @@ attn_paged_kernel(const __grid_constant__ CUtensorMap kv_map, long long row0, co
   }
 }
 
+// ---------------------------------------------------------------------------------------- prefill
+// Attention of a BLOCK of up to 16 consecutive query tokens of one sequence.
+// One CTA = (query block, kv head); warp w owns query head h0 + w: a 16-row MMA tile whose rows are the
+// block's tokens.  All warps walk the same 64-token K/V tiles (TMA ring shared by the GQA group, so K/V
+// are read once per 16 tokens x G heads), causal mask by position, online softmax per row, P in bf16.
+template <int D, int G>
+__global__ void __launch_bounds__(G * 32)
+attn_prefill_kernel(const __grid_constant__ CUtensorMap kv_map, long long row0, const uint16_t *__restrict__ q,
+                    const int *__restrict__ page_table, int max_pages, const int *__restrict__ qb_tok0,
+                    const int *__restrict__ qb_len, const int *__restrict__ qb_pos0, const int *__restrict__ qb_ptrow,
+                    uint16_t *__restrict__ out, int n_heads, int n_kv, int page_shift) {
+  using Cfg = AttnCfg<D>;
+  constexpr int KS = D / 16, NT = D / 8;
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t bar_base = smem_base + Cfg::kStages * Cfg::kStageBytes;
+  auto full_bar = [&](int s) { return bar_base + 8u * s; };
+
+  const int qb = blockIdx.x, kvh = blockIdx.y;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int g = lane >> 2, tq = lane & 3;
+  const int h = kvh * G + warp;
+
+  if (threadIdx.x == 0) {
+    tma_prefetch_desc(&kv_map);
+    for (int s = 0; s < Cfg::kStages; s++) mbar_init(full_bar(s), 1);
+    fence_barrier_init();
+    fence_proxy_async();
+  }
+  pdl_launch_dependents();
+  pdl_wait();
+  __syncthreads();
+
+  const int tok0 = qb_tok0[qb], len = qb_len[qb], pos0 = qb_pos0[qb];
+  const int *pt = page_table + (size_t)qb_ptrow[qb] * max_pages;
+  const int page_size = 1 << page_shift;
+  const int box_rows = min(page_size, kAttnTile);
+  const int end = pos0 + len;  // keys [0, end)
+  const int n_tiles = (end + kAttnTile - 1) / kAttnTile;
+
+  auto load_tile = [&](int tile, int stage) {  // one thread
+    const int tile0 = tile * kAttnTile;
+    const uint32_t sbase = smem_base + stage * Cfg::kStageBytes;
+    mbar_expect_tx(full_bar(stage), Cfg::kStageBytes);
+    for (int r = 0; r < kAttnTile; r += box_rows) {
+      const int pos = tile0 + r;
+      const long long page = pt[min(pos >> page_shift, max_pages - 1)];
+      const long long krow = row0 + ((page * 2 + 0) * n_kv + kvh) * page_size + (pos & (page_size - 1));
+      const long long vrow = krow + (long long)n_kv * page_size;
+#pragma unroll
+      for (int hh = 0; hh < Cfg::kHalves; hh++) {
+        tma_load_2d(sbase + hh * Cfg::kHalfBytes + r * 128, &kv_map, hh * 64, (int)krow, full_bar(stage), kEvictLast);
+        tma_load_2d(sbase + (Cfg::kHalves + hh) * Cfg::kHalfBytes + r * 128, &kv_map, hh * 64, (int)vrow, full_bar(stage), kEvictLast);
+      }
+    }
+  };
+  if (threadIdx.x == 0)
+    for (int s = 0; s < Cfg::kStages - 1; s++)
+      if (s < n_tiles) load_tile(s, s);
+
+  // ---- Q fragments: rows g and g+8 are tokens tok0+g, tok0+g+8 of head h
+  uint32_t qa[KS][4];
+  {
+    const bool v0 = g < len, v1 = g + 8 < len;
+    const uint16_t *q0 = q + ((size_t)(tok0 + g) * n_heads + h) * D + tq * 2;
+    const uint16_t *q1 = q + ((size_t)(tok0 + g + 8) * n_heads + h) * D + tq * 2;
+#pragma unroll
+    for (int ks = 0; ks < KS; ks++) {
+      qa[ks][0] = v0 ? *reinterpret_cast<const uint32_t *>(q0 + ks * 16) : 0u;
+      qa[ks][1] = v1 ? *reinterpret_cast<const uint32_t *>(q1 + ks * 16) : 0u;
+      qa[ks][2] = v0 ? *reinterpret_cast<const uint32_t *>(q0 + ks * 16 + 8) : 0u;
+      qa[ks][3] = v1 ? *reinterpret_cast<const uint32_t *>(q1 + ks * 16 + 8) : 0u;
+    }
+  }
+  const float scale_log2 = rsqrtf((float)D) * 1.4426950408889634f;
+  float oacc[NT][4];
+#pragma unroll
+  for (int n = 0; n < NT; n++) { oacc[n][0] = 0.f; oacc[n][1] = 0.f; oacc[n][2] = 0.f; oacc[n][3] = 0.f; }
+  float m_run[2] = {-INFINITY, -INFINITY}, l_run[2] = {0.f, 0.f};
+  const int qp0 = pos0 + g, qp1 = pos0 + g + 8;  // query positions of this thread's two rows
+
+  for (int tile = 0; tile < n_tiles; tile++) {
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      const int nt = tile + Cfg::kStages - 1;
+      if (nt < n_tiles) load_tile(nt, nt % Cfg::kStages);
+    }
+    const int stage = tile % Cfg::kStages;
+    mbar_wait(full_bar(stage), (uint32_t)(tile / Cfg::kStages) & 1u);
+    const uint32_t ks_addr = smem_base + stage * Cfg::kStageBytes;
+    const uint32_t vs_addr = ks_addr + Cfg::kHalves * Cfg::kHalfBytes;
+    const int tile0 = tile * kAttnTile;
+
+    // ---- S = Q K^T : 16 rows x 64 keys
+    float sacc[8][4];
+#pragma unroll
+    for (int n = 0; n < 8; n++) { sacc[n][0] = 0.f; sacc[n][1] = 0.f; sacc[n][2] = 0.f; sacc[n][3] = 0.f; }
+    {
+      const int mi = lane >> 3, r = lane & 7;
+#pragma unroll
+      for (int ks = 0; ks < KS; ks++) {
+        const int c = ks * 2 + (mi & 1);
+#pragma unroll
+        for (int np = 0; np < 4; np++) {  // n-tile pairs
+          const int tok = np * 16 + (mi >> 1) * 8 + r;
+          uint32_t b0, b1, b2, b3;
+          ldmatrix_x4(ks_addr + (c >> 3) * Cfg::kHalfBytes + tok * 128 + (((c & 7) ^ (tok & 7)) << 4), b0, b1, b2, b3);
+          mma_bf16_16816(sacc[2 * np], qa[ks][0], qa[ks][1], qa[ks][2], qa[ks][3], b0, b1);
+          mma_bf16_16816(sacc[2 * np + 1], qa[ks][0], qa[ks][1], qa[ks][2], qa[ks][3], b2, b3);
+        }
+      }
+    }
+    // ---- causal mask + online softmax (rows g and g+8)
+    float mx0 = -INFINITY, mx1 = -INFINITY;
+#pragma unroll
+    for (int n = 0; n < 8; n++)
+#pragma unroll
+      for (int e = 0; e < 2; e++) {
+        const int kp = tile0 + n * 8 + tq * 2 + e;
+        const float v0 = kp <= qp0 ? sacc[n][e] * scale_log2 : -INFINITY;
+        const float v1 = kp <= qp1 ? sacc[n][2 + e] * scale_log2 : -INFINITY;
+        sacc[n][e] = v0; sacc[n][2 + e] = v1;
+        mx0 = fmaxf(mx0, v0); mx1 = fmaxf(mx1, v1);
+      }
+    mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 1)); mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 2));
+    mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 1)); mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 2));
+    const float mn0 = fmaxf(m_run[0], mx0), mn1 = fmaxf(m_run[1], mx1);
+    // a row with nothing visible yet keeps m = -inf: use 0 as the reference so exp2(-inf - 0) = 0
+    const float r0 = mn0 == -INFINITY ? 0.f : mn0, r1 = mn1 == -INFINITY ? 0.f : mn1;
+    const float c0 = exp2f(m_run[0] - r0), c1 = exp2f(m_run[1] - r1);
+    m_run[0] = mn0; m_run[1] = mn1;
+    float ps0 = 0.f, ps1 = 0.f;
+    uint32_t pa[4][4];
+#pragma unroll
+    for (int kk = 0; kk < 4; kk++) {
+      const float a0 = exp2f(sacc[2 * kk][0] - r0), a1 = exp2f(sacc[2 * kk][1] - r0);
+      const float b0 = exp2f(sacc[2 * kk][2] - r1), b1 = exp2f(sacc[2 * kk][3] - r1);
+      const float c2 = exp2f(sacc[2 * kk + 1][0] - r0), c3 = exp2f(sacc[2 * kk + 1][1] - r0);
+      const float d0 = exp2f(sacc[2 * kk + 1][2] - r1), d1 = exp2f(sacc[2 * kk + 1][3] - r1);
+      ps0 += a0 + a1 + c2 + c3;
+      ps1 += b0 + b1 + d0 + d1;
+      pa[kk][0] = float2_to_bf16x2(a0, a1); pa[kk][1] = float2_to_bf16x2(b0, b1);
+      pa[kk][2] = float2_to_bf16x2(c2, c3); pa[kk][3] = float2_to_bf16x2(d0, d1);
+    }
+    l_run[0] = l_run[0] * c0 + ps0;
+    l_run[1] = l_run[1] * c1 + ps1;
+#pragma unroll
+    for (int n = 0; n < NT; n++) { oacc[n][0] *= c0; oacc[n][1] *= c0; oacc[n][2] *= c1; oacc[n][3] *= c1; }
+    // ---- O += P V
+    {
+      const int mi = lane >> 3, r = lane & 7;
+#pragma unroll
+      for (int kk = 0; kk < 4; kk++) {
+        const int tok = kk * 16 + (mi & 1) * 8 + r;
+#pragma unroll
+        for (int n = 0; n < NT; n += 2) {
+          const int c = n + (mi >> 1);
+          uint32_t b0, b1, b2, b3;
+          ldmatrix_x4_trans(vs_addr + (c >> 3) * Cfg::kHalfBytes + tok * 128 + (((c & 7) ^ (tok & 7)) << 4), b0, b1, b2, b3);
+          mma_bf16_16816(oacc[n], pa[kk][0], pa[kk][1], pa[kk][2], pa[kk][3], b0, b1);
+          mma_bf16_16816(oacc[n + 1], pa[kk][0], pa[kk][1], pa[kk][2], pa[kk][3], b2, b3);
+        }
+      }
+    }
+  }
+  // ---- normalise and store rows g, g+8
+  l_run[0] += __shfl_xor_sync(0xffffffffu, l_run[0], 1); l_run[0] += __shfl_xor_sync(0xffffffffu, l_run[0], 2);
+  l_run[1] += __shfl_xor_sync(0xffffffffu, l_run[1], 1); l_run[1] += __shfl_xor_sync(0xffffffffu, l_run[1], 2);
+  const float i0 = 1.0f / l_run[0], i1 = 1.0f / l_run[1];
+  if (g < len) {
+    uint16_t *o = out + ((size_t)(tok0 + g) * n_heads + h) * D + tq * 2;
+#pragma unroll
+    for (int n = 0; n < NT; n++) *reinterpret_cast<uint32_t *>(o + n * 8) = float2_to_bf16x2(oacc[n][0] * i0, oacc[n][1] * i0);
+  }
+  if (g + 8 < len) {
+    uint16_t *o = out + ((size_t)(tok0 + g + 8) * n_heads + h) * D + tq * 2;
+#pragma unroll
+    for (int n = 0; n < NT; n++) *reinterpret_cast<uint32_t *>(o + n * 8) = float2_to_bf16x2(oacc[n][2] * i1, oacc[n][3] * i1);
+  }
+}
+
 template <int D>
 __global__ void attn_combine_kernel(const float *__restrict__ scratch, uint16_t *__restrict__ out, int n_splits,
                                     int T, int n_heads) {
@@ -316,6 +497,44 @@ cudaError_t launch_attn_paged(const TmaMap &kv_map, long long row0, const uint16
   DIS_ATTN_CASE(64, 8) DIS_ATTN_CASE(64, 4) DIS_ATTN_CASE(64, 2) DIS_ATTN_CASE(64, 1)
 #undef DIS_ATTN_CASE
   set_last_error("attn_paged: head_dim must be 64 or 128 and the GQA group 1, 2, 4 or 8");
+  return cudaErrorInvalidValue;
+}
+
+template <int D, int G>
+static cudaError_t prefill_launch(const TmaMap &kv_map, long long row0, const uint16_t *q, const int *page_table,
+                                  int max_pages, const int *qb_tok0, const int *qb_len, const int *qb_pos0,
+                                  const int *qb_ptrow, uint16_t *out, int n_blocks, int n_heads, int n_kv,
+                                  int page_shift, cudaStream_t st) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    DIS_CUDA_TRY(cudaFuncSetAttribute(attn_prefill_kernel<D, G>, cudaFuncAttributeMaxDynamicSharedMemorySize, AttnCfg<D>::kSmemBytes));
+    attr_set = true;
+  }
+  return launch_k(attn_prefill_kernel<D, G>, dim3(n_blocks, n_kv), dim3(G * 32), AttnCfg<D>::kSmemBytes, st,
+                  *reinterpret_cast<const CUtensorMap *>(&kv_map), row0, q, page_table, max_pages, qb_tok0, qb_len, qb_pos0,
+                  qb_ptrow, out, n_heads, n_kv, page_shift);
+}
+
+// Query blocks: block b covers tokens [qb_tok0[b], +qb_len[b]) of the flattened batch (qb_len <= 16), which are
+// consecutive positions qb_pos0[b].. of the sequence whose page-table row is qb_ptrow[b].
+cudaError_t launch_attn_prefill(const TmaMap &kv_map, long long row0, const uint16_t *q, const int *page_table,
+                                int max_pages, const int *qb_tok0, const int *qb_len, const int *qb_pos0,
+                                const int *qb_ptrow, uint16_t *out, int n_blocks, int n_heads, int n_kv, int d,
+                                int page_size, cudaStream_t st) {
+  if (n_blocks <= 0) return cudaSuccess;
+  if (n_kv <= 0 || n_heads % n_kv != 0 || n_kv > 65535) { set_last_error("attn_prefill: bad head counts"); return cudaErrorInvalidValue; }
+  if (page_size < 8 || (page_size & (page_size - 1))) { set_last_error("attn_prefill: page_size must be a power of two >= 8"); return cudaErrorInvalidValue; }
+  int page_shift = 0;
+  while ((1 << page_shift) < page_size) page_shift++;
+  const int G = n_heads / n_kv;
+#define DIS_PF_CASE(DD, GG)                                                                                        \
+  if (d == DD && G == GG)                                                                                          \
+    return prefill_launch<DD, GG>(kv_map, row0, q, page_table, max_pages, qb_tok0, qb_len, qb_pos0, qb_ptrow, out, \
+                                  n_blocks, n_heads, n_kv, page_shift, st);
+  DIS_PF_CASE(128, 8) DIS_PF_CASE(128, 4) DIS_PF_CASE(128, 2) DIS_PF_CASE(128, 1)
+  DIS_PF_CASE(64, 8) DIS_PF_CASE(64, 4) DIS_PF_CASE(64, 2) DIS_PF_CASE(64, 1)
+#undef DIS_PF_CASE
+  set_last_error("attn_prefill: head_dim must be 64 or 128 and the GQA group 1, 2, 4 or 8");
   return cudaErrorInvalidValue;
 }
 

@@ -97,7 +97,7 @@ template <int BN, bool kDual>
 __global__ void __launch_bounds__(kGemmThreads)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_constant__ CUtensorMap x_map,
                     float *__restrict__ out_partial, uint16_t *__restrict__ out_act, int T, int N, int K,
-                    int w_row0, int up_row_off, int kb_per_split, int tile_rows, int w_tiled) {
+                    int w_row0, int up_row_off, int kb_per_split, int tile_rows) {
   using Cfg = GemmCfg<BN, kDual>;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -115,11 +115,6 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_cons
   // tile_rows (<= 128, the weight map's box height) output features per CTA: a 128-row MMA runs on a
   // partly filled A tile; lanes >= tile_rows compute on stale shared memory and are never stored.
   const int n0 = blockIdx.x * tile_rows;
-  const int num_kb_all = (K + kBK - 1) / kBK;
-  // w_tiled: the weight is stored tile-major, [row tile][k-block][tile_rows][64] (each TMA box is one contiguous
-  // block of DRAM); the map then is [rows][64] and a box is addressed by its block index.
-  auto a_c0 = [&](int kb) { return w_tiled ? 0 : kb * kBK; };
-  auto a_c1 = [&](int kb, int row_base) { return w_tiled ? ((row_base / tile_rows) * num_kb_all + kb) * tile_rows : row_base; };
   const uint32_t stage_tx = (uint32_t)((kDual ? 2 : 1) * tile_rows * kBK * 2 + Cfg::kBBytes);
   const int t0 = blockIdx.y * BN;
   const int num_kb = (K + kBK - 1) / kBK;
@@ -150,8 +145,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_cons
       const int pre = min(kb1 - kb0, Cfg::kStages);
       for (int i = 0; i < pre; i++) {
         mbar_expect_tx(full_bar(i), stage_tx);
-        tma_load_2d(a_tile(i), &w_map, a_c0(kb0 + i), a_c1(kb0 + i, w_row0 + n0), full_bar(i), kEvictFirst);
-        if (kDual) tma_load_2d(a2_tile(i), &w_map, a_c0(kb0 + i), a_c1(kb0 + i, w_row0 + up_row_off + n0), full_bar(i), kEvictFirst);
+        tma_load_2d(a_tile(i), &w_map, (kb0 + i) * kBK, w_row0 + n0, full_bar(i), kEvictFirst);
+        if (kDual) tma_load_2d(a2_tile(i), &w_map, (kb0 + i) * kBK, w_row0 + up_row_off + n0, full_bar(i), kEvictFirst);
       }
       pdl_wait();
       for (int i = 0; i < pre; i++) tma_load_2d(b_tile(i), &x_map, (kb0 + i) * kBK, t0, full_bar(i), kEvictLast);
@@ -160,8 +155,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_cons
       for (int kb = kb0 + pre; kb < kb1; kb++) {
         mbar_wait(empty_bar(s), phase ^ 1u);
         mbar_expect_tx(full_bar(s), stage_tx);
-        tma_load_2d(a_tile(s), &w_map, a_c0(kb), a_c1(kb, w_row0 + n0), full_bar(s), kEvictFirst);
-        if (kDual) tma_load_2d(a2_tile(s), &w_map, a_c0(kb), a_c1(kb, w_row0 + up_row_off + n0), full_bar(s), kEvictFirst);
+        tma_load_2d(a_tile(s), &w_map, kb * kBK, w_row0 + n0, full_bar(s), kEvictFirst);
+        if (kDual) tma_load_2d(a2_tile(s), &w_map, kb * kBK, w_row0 + up_row_off + n0, full_bar(s), kEvictFirst);
         tma_load_2d(b_tile(s), &x_map, kb * kBK, t0, full_bar(s), kEvictLast);
         if (++s == Cfg::kStages) { s = 0; phase ^= 1u; }
       }
@@ -264,8 +259,6 @@ cudaError_t make_tma_map_2d(TmaMap *out, const void *base, uint64_t rows, uint64
   return cudaSuccess;
 }
 
-int &gemm_tiled_flag() { static int f = 0; return f; }
-
 int gemm_token_tile(int T) { return T <= 32 ? 32 : (T <= 64 ? 64 : 128); }
 
 // Split-K factor: enough CTAs to keep every SM streaming (two CTAs per SM), each with >= 4 k-blocks.
@@ -298,7 +291,7 @@ static cudaError_t gemm_launch(const TmaMap &w_map, const TmaMap &x_map, float *
   if (tile_rows < 8 || tile_rows > kBM || tile_rows % 8) { set_last_error("gemm: tile_rows must be a multiple of 8 in [8, 128]"); return cudaErrorInvalidValue; }
   dim3 grid((N + tile_rows - 1) / tile_rows, (T + BN - 1) / BN, split_k);
   return launch_k(kern, grid, dim3(kGemmThreads), Cfg::kSmemBytes, st, *reinterpret_cast<const CUtensorMap *>(&w_map),
-                  *reinterpret_cast<const CUtensorMap *>(&x_map), out, act, T, N, K, w_row0, up_off, per, tile_rows, gemm_tiled_flag());
+                  *reinterpret_cast<const CUtensorMap *>(&x_map), out, act, T, N, K, w_row0, up_off, per, tile_rows);
 }
 
 cudaError_t launch_gemm_partial(const TmaMap &w_map, const TmaMap &x_map, float *out, int T, int N, int K,

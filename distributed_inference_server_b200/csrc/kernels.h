@@ -42,6 +42,11 @@ cudaError_t launch_attn_paged(const TmaMap &kv_map, long long row0, const uint16
                               int max_pages, const int *pt_row, const int *ctx, uint16_t *out, float *scratch,
                               int n_splits, int T, int n_heads, int n_kv, int d, int page_size, cudaStream_t st);
 
+cudaError_t launch_attn_prefill(const TmaMap &kv_map, long long row0, const uint16_t *q, const int *page_table,
+                                int max_pages, const int *qb_tok0, const int *qb_len, const int *qb_pos0,
+                                const int *qb_ptrow, uint16_t *out, int n_blocks, int n_heads, int n_kv, int d,
+                                int page_size, cudaStream_t st);
+
 // k_gemm_tcgen05.cu
 cudaError_t make_tma_map_2d(TmaMap *out, const void *base, uint64_t rows, uint64_t cols, uint32_t box_rows);
 int gemm_token_tile(int T);  // 32 / 64 / 128: the UMMA N used for T tokens
@@ -54,6 +59,5 @@ int gemm_pick_tile_rows(int N);
 cudaError_t launch_gemm_silu(const TmaMap &w_map, const TmaMap &x_map, uint16_t *act, int T, int I, int K,
                              int w_row0, int tile_rows, cudaStream_t st);
 int gemm_pick_split_k(int T, int N, int K);
-int &gemm_tiled_flag();  // experiment: weights addressed as tile-major blocks
 
 }  // namespace dis

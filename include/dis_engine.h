@@ -231,6 +231,13 @@ DIS_API int dis_k_attn_paged(const uint16_t *q, const uint16_t *kv_pool, int64_t
                              int32_t max_pages, const int32_t *pt_row, const int32_t *ctx, uint16_t *out,
                              float *scratch, int32_t n_splits, int32_t T, int32_t n_heads, int32_t n_kv,
                              int32_t d, int32_t page_size, void *stream);
+/* Prefill attention: query block b is the qb_len[b] (<= 16) consecutive tokens [qb_tok0[b], ..) of the flattened
+ * batch, at positions qb_pos0[b].. of the sequence with page-table row qb_ptrow[b]; causal over keys [0, pos].
+ * The block's own K/V must already be in the pages.  q / out are [tokens][nh*d] bf16. */
+DIS_API int dis_k_attn_prefill(const uint16_t *q, const uint16_t *kv_pool, int64_t n_pages, const int32_t *page_table,
+                               int32_t max_pages, const int32_t *qb_tok0, const int32_t *qb_len,
+                               const int32_t *qb_pos0, const int32_t *qb_ptrow, uint16_t *out, int32_t n_blocks,
+                               int32_t n_heads, int32_t n_kv, int32_t d, int32_t page_size, void *stream);
 /* Sampler over fp32 logits [T][V] (row stride ld): temperature 0 -> argmax, lowest index wins ties;
  * else nucleus sampling as oracle/llama_oracle.c states it.  out_tokens[T]. */
 DIS_API int dis_k_sample(const float *logits, int64_t ld, int32_t T, int32_t V, const float *temperature,

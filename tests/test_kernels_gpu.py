@@ -222,6 +222,44 @@ def test_attention_long_context_tiles():
         assert np.abs(host(out)[0] - ref).max() <= 2 * BF16_ULP * np.abs(ref).max() + 1e-5
 
 
+@pytest.mark.parametrize("d,nh,nkv,page_size", [(128, 8, 2, 64), (64, 8, 2, 16), (128, 8, 1, 32), (64, 2, 2, 64)])
+def test_attention_prefill_blocks(d, nh, nkv, page_size):
+    """Causal attention of 16-token query blocks over the paged cache vs the oracle, ragged sequences."""
+    rng = np.random.default_rng(d + nh + nkv + page_size)
+    seq_lens = [1, 15, 16, 17, 70, 200]
+    n_pages = 32
+    pt, max_pages = _paged_setup(rng, len(seq_lens), seq_lens, nkv, d, page_size, n_pages)
+    pool = np.zeros((n_pages, 2, nkv, page_size, d), np.float32)
+    K = [rand_bf16(rng, (n, nkv * d)) for n in seq_lens]
+    V = [rand_bf16(rng, (n, nkv * d)) for n in seq_lens]
+    Q = [rand_bf16(rng, (n, nh * d)) for n in seq_lens]
+    for s, n in enumerate(seq_lens):
+        for p in range(n):
+            pool[pt[s, p // page_size], 0, :, p % page_size] = K[s][p].reshape(nkv, d)
+            pool[pt[s, p // page_size], 1, :, p % page_size] = V[s][p].reshape(nkv, d)
+    # the second half of the longest sequence only: blocks need not start at position 0 (chunked prefill)
+    starts = [0, 0, 0, 0, 0, 96]
+    q_flat, tok0, qlen, pos0, ptrow, ref = [], [], [], [], [], []
+    t = 0
+    for s, n in enumerate(seq_lens):
+        for p0 in range(starts[s], n, 16):
+            ln = min(16, n - p0)
+            tok0.append(t); qlen.append(ln); pos0.append(p0); ptrow.append(s)
+            for i in range(ln):
+                q_flat.append(Q[s][p0 + i])
+                ref.append(O.attention_one(Q[s][p0 + i], K[s][:p0 + i + 1], V[s][:p0 + i + 1], nh, nkv, d))
+            t += ln
+    q_flat, ref = np.stack(q_flat), np.stack(ref)
+    out = torch.empty((t, nh * d), dtype=torch.bfloat16, device=DEV)
+    check(lib().dis_k_attn_prefill(ptr(dev_bf16(q_flat)), ptr(dev_bf16(pool)), n_pages, ptr(dev_i32(pt)), max_pages,
+                                   ptr(dev_i32(tok0)), ptr(dev_i32(qlen)), ptr(dev_i32(pos0)), ptr(dev_i32(ptrow)), ptr(out),
+                                   len(tok0), nh, nkv, d, page_size, None))
+    sync()
+    got = host(out)
+    assert np.isfinite(got).all()
+    assert np.abs(got - ref).max() <= 2 * BF16_ULP * np.abs(ref).max() + 1e-5, np.abs(got - ref).max()
+
+
 def test_sampler_argmax_and_ties():
     rng = np.random.default_rng(0)
     T, V = 6, 128256
