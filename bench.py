@@ -167,6 +167,7 @@ def workload_config(n_gpus, batch, prompt_len):
     else:
         w = f"BASELINE configs[2]: Llama-3-8B bf16, tensor parallel TP={n_gpus} over NVLink, batch {batch} decode, {prompt_len}-token prompts"
     return {"workload": w, "batch": batch, "prompt_len": prompt_len, "parallelism": f"tp{n_gpus}",
+            "tp_exchange": None if n_gpus == 1 else "fused peer-memory all-reduce (k_tp.cu); NCCL with --nccl-allreduce",
             "l2": "per-step working set (15 GB of weights + KV) is far larger than the 126 MB L2; no explicit flush"}
 
 
@@ -213,6 +214,12 @@ def run_ours(args):
                               flags=(B.FLAG_NO_GRAPH if args.no_graph else 0) | (B.FLAG_NO_PDL if args.no_pdl else 0)))
     eng.load_synthetic(0)
     eng.finalize()
+    if world > 1 and not args.nccl_allreduce:
+        # peer-memory exchange: all-gather the CUDA IPC handles of the symmetric buffers
+        mine = torch.tensor(list(eng.tp_export()), dtype=torch.uint8, device="cuda")
+        every = [torch.zeros_like(mine) for _ in range(world)]
+        dist.all_gather(every, mine)
+        eng.tp_import([bytes(t.cpu().tolist()) for t in every])
 
     rng = np.random.default_rng(1)
     prompts = [rng.integers(0, shape.vocab, args.prompt_len).tolist() for _ in range(batch)]
@@ -337,6 +344,7 @@ def main():
     ap.add_argument("--no-graph", action="store_true", help="run decode steps eagerly (profiling under ncu)")
     ap.add_argument("--ttft-runs", type=int, default=3)
     ap.add_argument("--no-pdl", action="store_true", help="disable programmatic dependent launch (A/B)")
+    ap.add_argument("--nccl-allreduce", action="store_true", help="TP: use NCCL instead of the fused peer-memory exchange (A/B)")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)

@@ -72,6 +72,8 @@ PROTOTYPES = {
     "dis_engine_status": (C.c_int, [vp, C.POINTER(WorkerStatus)]),
     "dis_engine_model_info": (C.c_int, [vp, C.POINTER(ModelConfig)]),
     "dis_tp_unique_id": (C.c_int, [vp]),
+    "dis_engine_tp_export": (C.c_int, [vp, vp]),
+    "dis_engine_tp_import": (C.c_int, [vp, vp]),
     "dis_worker_infer": (C.c_int, [vp, C.c_int32, vp, C.c_int32, vp, C.POINTER(SamplingParams), vp, C.c_int32, vp, vp,
                                    C.POINTER(BatchResult), vp, vp]),
     "dis_k_add_rmsnorm": (C.c_int, [vp, vp, vp, vp, C.c_int32, C.c_int64, vp, vp, vp, C.c_int32, C.c_int32,

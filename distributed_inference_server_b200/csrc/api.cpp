@@ -115,6 +115,17 @@ int dis_tp_unique_id(uint8_t out[128]) {
   return DIS_OK;
 }
 
+int dis_engine_tp_export(dis_engine *e, uint8_t out[64]) {
+  if (int rc = guard_null(e)) return rc;
+  LOCKED(e);
+  return e->eng.tp_export(out);
+}
+int dis_engine_tp_import(dis_engine *e, const uint8_t *handles) {
+  if (int rc = guard_null(e)) return rc;
+  LOCKED(e);
+  return e->eng.tp_import(handles);
+}
+
 // ---- kernel-level entry points -------------------------------------------------------------------
 static int k_ret(cudaError_t e) { return e == cudaSuccess ? DIS_OK : DIS_ERR_INFERENCE_FAILED; }
 static int need_gpu() {

@@ -169,6 +169,7 @@ int Engine::init(const dis_engine_config *c) {
     s.o_rowmap = sec((size_t)max_batch * 4); s.o_temp = sec((size_t)max_batch * 4); s.o_topp = sec((size_t)max_batch * 4);
     s.o_seed = sec((size_t)max_batch * 8); s.o_step = sec((size_t)max_batch * 8);
     s.o_qb_tok0 = sec(ct * 4); s.o_qb_len = sec(ct * 4); s.o_qb_pos0 = sec(ct * 4); s.o_qb_ptrow = sec(ct * 4);
+    s.o_arstep = sec(16);
     s.bytes = o;
     cudaError_t e1 = cudaMallocHost(reinterpret_cast<void **>(&s.host), s.bytes);
     if (e1 != cudaSuccess) return e1;
@@ -217,7 +218,56 @@ int Engine::init(const dis_engine_config *c) {
     const int r = nccl->CommInitRank(&comm, tp_size, id, tp_rank);
     if (r != 0) return fail(DIS_ERR_INFERENCE_FAILED, std::string("ncclCommInitRank: ") + nccl->GetErrorString(r));
   }
+  if (tp_size > 1) {
+    if (tp_size > kTpMaxRanks) return fail(DIS_ERR_INVALID_ARGUMENT, "tp_size > 8");
+    ar_cap_rows = std::min(std::max(max_batch, 128), 256);
+    const size_t data_b = (size_t)2 * tp_size * ar_cap_rows * m.hidden * sizeof(float);
+    const size_t flags_b = align_up((size_t)2 * tp_size * ar_cap_rows * 4, 256);
+    const size_t cand_b = align_up((size_t)2 * tp_size * ar_cap_rows * 2 * 4, 256);
+    sym_bytes = data_b + flags_b + cand_b + 256;
+    ENG_CUDA(dev_alloc(&sym, sym_bytes, &bytes_allocated));
+    ENG_CUDA(cudaMemset(sym, 0, sym_bytes));
+  }
   ENG_CUDA(cudaDeviceSynchronize());
+  return DIS_OK;
+}
+
+// ---- peer-memory exchange set-up: export this rank's symmetric buffer, import everybody's
+int Engine::tp_export(uint8_t out[64]) {
+  if (tp_size <= 1 || !sym) return fail(DIS_ERR_INVALID_ARGUMENT, "tp_export: engine is not tensor parallel");
+  ENG_CUDA(cudaSetDevice(cfg.device));
+  cudaIpcMemHandle_t hdl;
+  ENG_CUDA(cudaIpcGetMemHandle(&hdl, sym));
+  static_assert(sizeof(hdl) == 64, "cudaIpcMemHandle_t is 64 bytes");
+  memcpy(out, &hdl, 64);
+  return DIS_OK;
+}
+
+int Engine::tp_import(const uint8_t *handles) {
+  if (tp_size <= 1 || !sym || !handles) return fail(DIS_ERR_INVALID_ARGUMENT, "tp_import: engine is not tensor parallel");
+  ENG_CUDA(cudaSetDevice(cfg.device));
+  const size_t data_b = (size_t)2 * tp_size * ar_cap_rows * m.hidden * sizeof(float);
+  const size_t flags_b = align_up((size_t)2 * tp_size * ar_cap_rows * 4, 256);
+  const size_t cand_b = align_up((size_t)2 * tp_size * ar_cap_rows * 2 * 4, 256);
+  for (int r = 0; r < tp_size; r++) {
+    uint8_t *base = sym;
+    if (r != tp_rank) {
+      cudaIpcMemHandle_t hdl;
+      memcpy(&hdl, handles + (size_t)r * 64, 64);
+      void *p = nullptr;
+      ENG_CUDA(cudaIpcOpenMemHandle(&p, hdl, cudaIpcMemLazyEnablePeerAccess));
+      peer_base[r] = p;
+      base = static_cast<uint8_t *>(p);
+    }
+    peers.data[r] = reinterpret_cast<float *>(base);
+    peers.flags[r] = reinterpret_cast<uint32_t *>(base + data_b);
+    peers.cand[r] = reinterpret_cast<uint32_t *>(base + data_b + flags_b);
+    peers.cand_flags[r] = reinterpret_cast<uint32_t *>(base + data_b + flags_b + cand_b);
+  }
+  peers.rank = tp_rank;
+  peers.tp = tp_size;
+  peers.cap_rows = ar_cap_rows;
+  tp_custom = true;
   return DIS_OK;
 }
 
@@ -227,9 +277,10 @@ Engine::~Engine() {
   for (auto &g : graphs) cudaGraphExecDestroy(g.second);
   for (auto ev : prof_events) cudaEventDestroy(ev);
   if (comm && nccl) nccl->CommDestroy(comm);
+  for (int r = 0; r < kTpMaxRanks; r++) if (peer_base[r]) cudaIpcCloseMemHandle(peer_base[r]);
   void *ptrs[] = {embed, wqkv, wo, wgu, wdown, lm_head, attn_norm, mlp_norm, final_norm, x, partial, logits, ar_buf,
                   attn_scratch, full_logits, gather_buf, cand_val, cand_val_all, cand_tok, cand_tok_all, xn, q, attn,
-                  act, d_out_tokens, kv_pool, d_page_table, rope_cos, rope_sin, meta_dec.dev, meta_pre.dev};
+                  act, d_out_tokens, kv_pool, d_page_table, rope_cos, rope_sin, meta_dec.dev, meta_pre.dev, sym};
   for (void *p : ptrs) if (p) cudaFree(p);
   if (h_out_tokens) cudaFreeHost(h_out_tokens);
   if (h_page_table) cudaFreeHost(h_page_table);
@@ -447,6 +498,8 @@ cudaError_t Engine::upload_step(int T, int R) {
     pt_dirty = false;
   }
   (void)T; (void)R;
+  cur_meta->h<uint32_t>(cur_meta->o_arstep)[0] = ++ar_step;
+  ar_idx = 0;
   return cudaMemcpyAsync(cur_meta->dev, cur_meta->host, cur_meta->bytes, cudaMemcpyHostToDevice, stream);
 }
 
@@ -489,22 +542,56 @@ cudaError_t Engine::allreduce_partials(int split, int T) {
   return cudaSuccess;
 }
 
+// x (+)= the pending projection output (summed over split-K slices and, under tensor parallelism, over the
+// ranks); xn = bf16(RMSNorm(x) * gain).  With row_map only `rows` gathered rows are normalised (logits rows).
+cudaError_t Engine::consume_pending(const float *gain, const int *row_map, int rows, int T) {
+  const int H = m.hidden;
+  if (pend_needs_ar) {
+    // fused exchange over peer memory: split-K reduce + all-reduce + residual + norm in one kernel
+    const int idx = ar_idx++;
+    RET_CUDA(launch_tp_add_rmsnorm(peers, x, pend_ptr, pend_count, pend_str, gain, xn,
+                                   cur_meta->d<uint32_t>(cur_meta->o_arstep), (uint32_t)idx, idx & 1, T, H, m.rms_eps, stream));
+    kernel_launches++;
+    pend_needs_ar = false; pend_ptr = nullptr; pend_count = 0;
+    if (!row_map) return cudaSuccess;
+    kernel_launches++;  // x is complete: gather the rows that need logits
+    return launch_add_rmsnorm(x, nullptr, nullptr, nullptr, 0, 0, gain, xn, row_map, rows, H, m.rms_eps, stream);
+  }
+  kernel_launches++;
+  const cudaError_t r = launch_add_rmsnorm(x, nullptr, nullptr, pend_ptr, pend_count, pend_str, gain, xn, row_map, rows, H,
+                                           m.rms_eps, stream);
+  pend_ptr = nullptr; pend_count = 0;
+  return r;
+}
+
 cudaError_t Engine::enqueue_layers(int T, int n_splits) {
   const int H = m.hidden, d = m.head_dim;
   const bool gemv = (cfg.flags & DIS_FLAG_FORCE_GEMV) || T <= 2;
-  const float *pend = nullptr;  // projection output waiting to be added to the residual
-  int pend_n = 0;
-  long long pend_stride = 0;
+  const bool fused_ar = tp_size > 1 && tp_custom && T <= ar_cap_rows;  // exchange over peer memory, no NCCL kernel
+  const bool pdl_ok = use_pdl && !profiling && (tp_size == 1 || fused_ar);
+  pend_ptr = nullptr; pend_count = 0; pend_str = 0; pend_needs_ar = false;
   const uint32_t *tokens = cur_meta->d<uint32_t>(cur_meta->o_tokens);
   const int *pos = cur_meta->d<int>(cur_meta->o_pos), *ptrow = cur_meta->d<int>(cur_meta->o_ptrow), *ctx = cur_meta->d<int>(cur_meta->o_ctx);
+  // a projection output becomes "pending": the next norm kernel adds it to the residual
+  auto set_pending = [&](int split) -> cudaError_t {
+    pend_ptr = partial; pend_count = split; pend_str = (long long)T * H;
+    if (tp_size > 1) {
+      if (fused_ar) pend_needs_ar = true;
+      else { RET_CUDA(allreduce_partials(split, T)); pend_ptr = ar_buf; pend_count = 1; pend_str = 0; }
+    }
+    return cudaSuccess;
+  };
   for (int l = 0; l < m.layers; l++) {
-    // x (+)= pending; xn = RMSNorm(x)
     prof_mark(P_NORM);
-    pdl_enabled() = use_pdl && !profiling && tp_size == 1 && l > 0;  // the step's first kernel follows a memcpy
-    RET_CUDA(launch_add_rmsnorm(x, l == 0 ? tokens : nullptr, embed, pend, pend_n, pend_stride, attn_norm + (size_t)l * H,
-                                xn, nullptr, T, H, m.rms_eps, stream));
-    kernel_launches++;
-    pdl_enabled() = use_pdl && !profiling && tp_size == 1;
+    if (l == 0) {
+      pdl_enabled() = false;  // the step's first kernel follows a memcpy
+      RET_CUDA(launch_add_rmsnorm(x, tokens, embed, nullptr, 0, 0, attn_norm, xn, nullptr, T, H, m.rms_eps, stream));
+      kernel_launches++;
+    } else {
+      pdl_enabled() = pdl_ok;
+      RET_CUDA(consume_pending(attn_norm + (size_t)l * H, nullptr, T, T));
+    }
+    pdl_enabled() = pdl_ok;
     int s_qkv = 1;
     prof_mark(P_QKV);
     RET_CUDA(linear_partial(xn_map, xn, wqkv_map, wqkv, l * nqkv_l, T, nqkv_l, H, &s_qkv));
@@ -527,12 +614,9 @@ cudaError_t Engine::enqueue_layers(int T, int n_splits) {
     int s_o = 1;
     prof_mark(P_OPROJ);
     RET_CUDA(linear_partial(attn_map, attn, wo_map, wo, l * H, T, H, qd_l, &s_o));
-    if (tp_size > 1) { RET_CUDA(allreduce_partials(s_o, T)); pend = ar_buf; pend_n = 1; pend_stride = 0; }
-    else { pend = partial; pend_n = s_o; pend_stride = (long long)T * H; }
+    RET_CUDA(set_pending(s_o));
     prof_mark(P_NORM);
-    RET_CUDA(launch_add_rmsnorm(x, nullptr, nullptr, pend, pend_n, pend_stride, mlp_norm + (size_t)l * H, xn, nullptr, T,
-                                H, m.rms_eps, stream));
-    kernel_launches++;
+    RET_CUDA(consume_pending(mlp_norm + (size_t)l * H, nullptr, T, T));
     prof_mark(P_GATEUP);
     if (gemv) {
       RET_CUDA(launch_gemv_silu(xn, wgu + (size_t)l * 2 * inter_l * H, act, T, inter_l, H, stream));
@@ -544,10 +628,8 @@ cudaError_t Engine::enqueue_layers(int T, int n_splits) {
     int s_d = 1;
     prof_mark(P_DOWN);
     RET_CUDA(linear_partial(act_map, act, wdown_map, wdown, l * H, T, H, inter_l, &s_d));
-    if (tp_size > 1) { RET_CUDA(allreduce_partials(s_d, T)); pend = ar_buf; pend_n = 1; pend_stride = 0; }
-    else { pend = partial; pend_n = s_d; pend_stride = (long long)T * H; }
+    RET_CUDA(set_pending(s_d));
   }
-  pend_ptr = pend; pend_count = pend_n; pend_str = pend_stride;
   pdl_enabled() = false;
   return cudaSuccess;
 }
@@ -556,9 +638,7 @@ cudaError_t Engine::enqueue_layers(int T, int n_splits) {
 cudaError_t Engine::enqueue_head(int R, bool all_greedy) {
   const int H = m.hidden;
   prof_mark(P_HEAD_NORM);
-  RET_CUDA(launch_add_rmsnorm(x, nullptr, nullptr, pend_ptr, pend_count, pend_str, final_norm, xn,
-                              cur_meta->d<int>(cur_meta->o_rowmap), R, H, m.rms_eps, stream));
-  kernel_launches++;
+  RET_CUDA(consume_pending(final_norm, rowmap_identity ? nullptr : cur_meta->d<int>(cur_meta->o_rowmap), R, last_T));
   const bool gemv = (cfg.flags & DIS_FLAG_FORCE_GEMV) || R <= 2;
   prof_mark(P_LM_HEAD);
   if (gemv) { RET_CUDA(launch_gemv(xn, lm_head, logits, R, vocab_l, H, stream)); kernel_launches += (uint64_t)((R + kGemvMaxT - 1) / kGemvMaxT); }
@@ -569,6 +649,12 @@ cudaError_t Engine::enqueue_head(int R, bool all_greedy) {
   if (tp_size == 1) {
     kernel_launches++;
     return launch_sample(logits, vocab_l, R, vocab_l, temp, topp, seed, step, d_out_tokens, 0, nullptr, stream);
+  }
+  if (all_greedy && tp_custom) {
+    // vocab-parallel argmax: local (value, id), exchanged and merged over peer memory in one kernel
+    RET_CUDA(launch_sample(logits, vocab_l, R, vocab_l, nullptr, nullptr, nullptr, nullptr, cand_tok, vocab_off, cand_val, stream));
+    kernel_launches += 2;
+    return launch_tp_argmax_merge(peers, cand_val, cand_tok, cur_meta->d<uint32_t>(cur_meta->o_arstep), R, d_out_tokens, stream);
   }
   if (all_greedy) {
     // vocab-parallel argmax: local (value, id) -> all-gather -> merge
@@ -656,6 +742,8 @@ int Engine::prefill(int n, const int *slots, uint32_t *out_tokens, int *out_fini
       }
     }
     n_qblocks = QB;
+    last_T = T;
+    rowmap_identity = false;
     ENG_CUDA(upload_step(T, R));
     ENG_CUDA(enqueue_layers(T, 1));
     if (R > 0) {
@@ -721,6 +809,8 @@ int Engine::decode(int n, const int *slots, uint32_t *out_tokens, int *out_finis
   const int T = (int)live.size();
   if (T == 0) { last_rows = 0; return DIS_OK; }
   const int n_splits = pick_attn_splits(T, max_ctx_b);
+  last_T = T;
+  rowmap_identity = true;
   ENG_CUDA(cudaEventRecord(ev0, stream));
   ENG_CUDA(upload_step(T, T));
   if ((cfg.flags & DIS_FLAG_NO_GRAPH) || profiling) {

@@ -51,6 +51,7 @@ struct StepMeta {
   // sections (offsets in bytes)
   size_t o_tokens, o_pos, o_ptrow, o_ctx, o_rowmap, o_temp, o_topp, o_seed, o_step;
   size_t o_qb_tok0, o_qb_len, o_qb_pos0, o_qb_ptrow;  // prefill query blocks
+  size_t o_arstep;                                     // forward-pass counter (epoch of the peer-memory exchange)
   template <class T_> T_ *h(size_t off) { return reinterpret_cast<T_ *>(host + off); }
   template <class T_> T_ *d(size_t off) { return reinterpret_cast<T_ *>(dev + off); }
 };
@@ -116,6 +117,21 @@ struct Engine {
   // tensor parallel
   NcclApi *nccl = nullptr;
   void *comm = nullptr;
+  // peer-memory exchange (k_tp.cu): one symmetric allocation per rank, mapped into every peer through CUDA IPC
+  uint8_t *sym = nullptr;
+  size_t sym_bytes = 0;
+  void *peer_base[kTpMaxRanks] = {};
+  TpPeers peers{};
+  bool tp_custom = false;   // peers imported: all-reduce fused into the norm kernels
+  int ar_cap_rows = 0;
+  uint32_t ar_step = 0;
+  bool pend_needs_ar = false;
+  int ar_idx = 0;           // index of the next all-reduce inside the current forward pass
+  int last_T = 0;           // tokens of the forward pass being enqueued
+  bool rowmap_identity = true;  // decode: logits row i is token i
+  int tp_export(uint8_t out[64]);
+  int tp_import(const uint8_t *handles);
+  cudaError_t consume_pending(const float *gain, const int *row_map, int rows, int T);
 
   ~Engine();
   int fail(int code, const std::string &msg);

@@ -1,0 +1,177 @@
+// k_tp.cu -- tensor-parallel exchange fused with the compute around it, over NVLink peer memory
+// (no reference counterpart: the reference specifies replicas only, requirements.md:100-110).
+//
+//   tp_add_rmsnorm : split-K reduce of this rank's O/down projection slices
+//                    -> row PUSHED into every peer's symmetric buffer over NVLink (P2P stores), then a
+//                       release flag (system scope) per (source rank, row)
+//                    -> each rank polls its OWN memory for the peers' flags and reads the peers' rows locally
+//                    -> summed IN RANK ORDER (every rank computes bit-identical results)
+//                    -> residual add + RMSNorm -> bf16 GEMM input.        One kernel, one CTA per token row.
+//   tp_argmax_merge: vocab-parallel greedy sampling: (max, id) candidates exchanged the same way.
+//
+// This is a one-shot all-reduce: every rank sends (tp-1) * T * H * 4 bytes; no NVLink round trip is on the
+// critical path (stores are fire-and-forget, polling and reads are local).  Synchronisation is per ROW (a
+// CTA only waits for the same row of each peer), so there is no grid-wide barrier and no CTA ever waits for
+// another CTA of its own GPU.  Buffers are double-buffered by all-reduce parity: a rank can only reach
+// all-reduce k+2 after every peer has finished all-reduce k (it needed their k+1 rows).
+#include "kernels.h"
+#include "ptx.cuh"
+
+namespace dis {
+
+__device__ __forceinline__ void st_release_sys(uint32_t *p, uint32_t v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t *p) {
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ float4 ld_volatile_f4(const float *p) {
+  float4 v;
+  asm volatile("ld.volatile.global.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
+  return v;
+}
+
+template <int kThreadsUnused = 0>
+__device__ __forceinline__ float tp_block_sum(float v, float *sm) {
+  v = warp_sum(v);
+  const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+  const int nw = (int)(blockDim.x >> 5);
+  __syncthreads();
+  if (l == 0) sm[w] = v;
+  __syncthreads();
+  float r = (l < nw) ? sm[l] : 0.f;
+  return warp_sum(r);
+}
+
+__global__ void __launch_bounds__(1024)
+tp_add_rmsnorm_kernel(TpPeers peers, float *__restrict__ x, const float *__restrict__ partial, int n_partial,
+                      long long partial_stride, const float *__restrict__ gain, uint16_t *__restrict__ xn,
+                      const uint32_t *__restrict__ step_ptr, uint32_t idx, int parity, int H, float eps) {
+  __shared__ float red[32];
+  extern __shared__ float row[];  // [2][H] (own contribution, running total) when a thread owns > 1 float4
+  const int t = blockIdx.x;
+  pdl_launch_dependents();
+  pdl_wait();
+  const uint32_t epoch = *step_ptr * 256u + idx;
+  const int step = blockDim.x * 4;
+  const bool single = H <= step;
+  const int me = peers.rank, tp = peers.tp;
+  // slot of source rank r inside a rank's buffer: [parity][r][row t]
+  const size_t slot_me = (((size_t)parity * tp + me) * peers.cap_rows + t) * (size_t)H;
+  const size_t flag_me = ((size_t)parity * tp + me) * peers.cap_rows + t;
+
+  // ---- local split-K reduce, pushed to every peer
+  float4 keep = make_float4(0.f, 0.f, 0.f, 0.f);
+  for (int i = threadIdx.x * 4; i < H; i += step) {
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    const float *pp = partial + (size_t)t * H + i;
+#pragma unroll 4
+    for (int s = 0; s < n_partial; s++) {
+      const float4 p = *reinterpret_cast<const float4 *>(pp + (size_t)s * partial_stride);
+      v.x += p.x; v.y += p.y; v.z += p.z; v.w += p.w;
+    }
+    for (int r = 0; r < tp; r++)
+      if (r != me) *reinterpret_cast<float4 *>(peers.data[r] + slot_me + i) = v;  // NVLink store
+    if (single) keep = v; else *reinterpret_cast<float4 *>(row + i) = v;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x < tp && threadIdx.x != me) st_release_sys(peers.flags[threadIdx.x] + flag_me, epoch);
+  // ---- wait for every peer's row (flags live in THIS rank's memory), one polling thread per source
+  if (threadIdx.x < tp && threadIdx.x != me) {
+    const uint32_t *f = peers.flags[me] + ((size_t)parity * tp + threadIdx.x) * peers.cap_rows + t;
+    while (ld_acquire_sys(f) != epoch) { }
+  }
+  __syncthreads();
+  // ---- sum in rank order, add the residual
+  float ss = 0.f;
+  for (int i = threadIdx.x * 4; i < H; i += step) {
+    float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int r = 0; r < tp; r++) {
+      float4 v;
+      if (r == me) v = single ? keep : *reinterpret_cast<const float4 *>(row + i);
+      else v = ld_volatile_f4(peers.data[me] + (((size_t)parity * tp + r) * peers.cap_rows + t) * (size_t)H + i);
+      a.x += v.x; a.y += v.y; a.z += v.z; a.w += v.w;
+    }
+    const float4 xv = *reinterpret_cast<const float4 *>(x + (size_t)t * H + i);
+    a.x += xv.x; a.y += xv.y; a.z += xv.z; a.w += xv.w;
+    *reinterpret_cast<float4 *>(x + (size_t)t * H + i) = a;
+    if (single) keep = a; else *reinterpret_cast<float4 *>(row + H + i) = a;
+    ss += a.x * a.x + a.y * a.y + a.z * a.z + a.w * a.w;
+  }
+  ss = tp_block_sum(ss, red);
+  const float inv = rsqrtf(ss / (float)H + eps);
+  for (int i = threadIdx.x * 4; i < H; i += step) {
+    const float4 v = single ? keep : *reinterpret_cast<const float4 *>(row + H + i);
+    const float4 g = *reinterpret_cast<const float4 *>(gain + i);
+    uint2 o;
+    o.x = float2_to_bf16x2(v.x * inv * g.x, v.y * inv * g.y);
+    o.y = float2_to_bf16x2(v.z * inv * g.z, v.w * inv * g.w);
+    *reinterpret_cast<uint2 *>(xn + (size_t)t * H + i) = o;
+  }
+}
+
+cudaError_t launch_tp_add_rmsnorm(const TpPeers &peers, float *x, const float *partial, int n_partial,
+                                  long long partial_stride, const float *gain, uint16_t *xn, const uint32_t *step_ptr,
+                                  uint32_t idx, int parity, int T, int H, float eps, cudaStream_t st) {
+  if (T <= 0) return cudaSuccess;
+  if (T > peers.cap_rows) { set_last_error("tp_add_rmsnorm: more rows than the symmetric buffer holds"); return cudaErrorInvalidValue; }
+  if (H % 4 != 0) { set_last_error("tp_add_rmsnorm: H must be a multiple of 4"); return cudaErrorInvalidValue; }
+  int threads = (H / 4 + 31) / 32 * 32;
+  threads = threads > 1024 ? 1024 : threads;
+  const size_t smem = H <= threads * 4 ? 0 : (size_t)2 * H * sizeof(float);
+  if (smem > 48 * 1024) DIS_CUDA_TRY(cudaFuncSetAttribute(tp_add_rmsnorm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  return launch_k(tp_add_rmsnorm_kernel, dim3(T), dim3(threads), smem, st, peers, x, partial, n_partial, partial_stride, gain,
+                  xn, step_ptr, idx, parity, H, eps);
+}
+
+// One CTA.  Candidates are pushed into every peer's cand area: [parity][source rank][cap_rows][2] words.
+__global__ void __launch_bounds__(1024)
+tp_argmax_merge_kernel(TpPeers peers, const float *__restrict__ val, const uint32_t *__restrict__ tok,
+                       const uint32_t *__restrict__ step_ptr, int T, uint32_t *__restrict__ out) {
+  pdl_wait();
+  const uint32_t epoch = *step_ptr * 256u + 255u;
+  const int parity = (int)(*step_ptr & 1u);  // one merge per forward pass: consecutive passes alternate
+  const int t = threadIdx.x, me = peers.rank, tp = peers.tp;
+  const size_t base_me = ((size_t)parity * tp + me) * peers.cap_rows;
+  if (t < T) {
+    const uint32_t vb = __float_as_uint(val[t]), k = tok[t];
+    for (int r = 0; r < tp; r++)
+      if (r != me) { peers.cand[r][(base_me + t) * 2 + 0] = vb; peers.cand[r][(base_me + t) * 2 + 1] = k; }
+  }
+  __syncthreads();
+  if (t == 0) __threadfence_system();
+  __syncthreads();
+  if (t < tp && t != me) {
+    st_release_sys(peers.cand_flags[t] + parity * tp + me, epoch);
+    while (ld_acquire_sys(peers.cand_flags[me] + parity * tp + t) != epoch) { }
+  }
+  __syncthreads();
+  if (t < T) {
+    float bv = -INFINITY;
+    uint32_t bt = 0xffffffffu;
+    for (int r = 0; r < tp; r++) {
+      uint32_t vb, k;
+      if (r == me) { vb = __float_as_uint(val[t]); k = tok[t]; }
+      else {
+        const volatile uint32_t *c = peers.cand[me] + (((size_t)parity * tp + r) * peers.cap_rows + t) * 2;
+        vb = c[0]; k = c[1];
+      }
+      const float v = __uint_as_float(vb);
+      if (v > bv || (v == bv && k < bt)) { bv = v; bt = k; }
+    }
+    out[t] = bt;
+  }
+}
+
+cudaError_t launch_tp_argmax_merge(const TpPeers &peers, const float *val, const uint32_t *tok, const uint32_t *step_ptr,
+                                   int T, uint32_t *out, cudaStream_t st) {
+  if (T <= 0) return cudaSuccess;
+  if (T > 1024 || T > peers.cap_rows) { set_last_error("tp_argmax_merge: too many rows"); return cudaErrorInvalidValue; }
+  return launch_k(tp_argmax_merge_kernel, dim3(1), dim3((T + 31) / 32 * 32), 0, st, peers, val, tok, step_ptr, T, out);
+}
+
+}  // namespace dis

@@ -27,6 +27,23 @@ cudaError_t launch_synth_bf16(uint16_t *dst, size_t n, unsigned long long seed, 
                               cudaStream_t st);
 cudaError_t launch_bf16_to_f32(const uint16_t *src, float *dst, size_t n, cudaStream_t st);
 
+// k_tp.cu : exchange over peer memory.  Every rank owns one symmetric allocation:
+//   data [2 parities][tp sources][cap_rows][H] fp32 | flags [2][tp][cap_rows] u32 | cand [2][tp][cap_rows][2] u32 |
+//   cand_flags [2][tp] u32     (peers PUSH into the slot of their own rank; the owner polls and reads locally)
+constexpr int kTpMaxRanks = 8;
+struct TpPeers {
+  float *data[kTpMaxRanks];
+  uint32_t *flags[kTpMaxRanks];
+  uint32_t *cand[kTpMaxRanks];
+  uint32_t *cand_flags[kTpMaxRanks];
+  int rank, tp, cap_rows;
+};
+cudaError_t launch_tp_add_rmsnorm(const TpPeers &peers, float *x, const float *partial, int n_partial,
+                                  long long partial_stride, const float *gain, uint16_t *xn, const uint32_t *step_ptr,
+                                  uint32_t idx, int parity, int T, int H, float eps, cudaStream_t st);
+cudaError_t launch_tp_argmax_merge(const TpPeers &peers, const float *val, const uint32_t *tok, const uint32_t *step_ptr,
+                                   int T, uint32_t *out, cudaStream_t st);
+
 // k_gemv.cu : out[t][n] = sum_k X[t][k] W[n][k]  (T <= kGemvMaxT per launch; launcher loops)
 constexpr int kGemvMaxT = 4;
 cudaError_t launch_gemv(const uint16_t *X, const uint16_t *W, float *out, int T, int N, int K, cudaStream_t st);

@@ -203,6 +203,18 @@ class Engine:
         self._check(self.lib.dis_engine_read_tensor(self.h, kind, layer, out.ctypes.data, C.byref(n)))
         return out
 
+    def tp_export(self) -> bytes:
+        """64-byte CUDA IPC handle of this rank's symmetric exchange buffer."""
+        buf = (C.c_uint8 * 64)()
+        self._check(self.lib.dis_engine_tp_export(self.h, buf))
+        return bytes(buf)
+
+    def tp_import(self, handles):
+        """handles: the tp_size exported handles in rank order; switches the all-reduce to peer memory."""
+        blob = b"".join(handles)
+        arr = (C.c_uint8 * len(blob)).from_buffer_copy(blob)
+        self._check(self.lib.dis_engine_tp_import(self.h, arr))
+
     def finalize(self):
         self._check(self.lib.dis_engine_finalize(self.h))
 

@@ -168,6 +168,12 @@ DIS_API int dis_engine_model_info(dis_engine *e, dis_model_config *out);
 /* ---- tensor parallel bootstrap (no reference counterpart: the reference specifies replicas only,
  * requirements.md:100-110; north_star asks for Megatron TP) ------------------------------------- */
 DIS_API int dis_tp_unique_id(uint8_t out[128]);
+/* Peer-memory exchange: every rank exports a 64-byte CUDA IPC handle of its symmetric buffer, the host
+ * all-gathers them (rank order) and hands all tp_size handles to every rank.  After the import the all-reduce
+ * after the O and down projections is fused into the residual + RMSNorm kernel (P2P loads over NVLink, flag
+ * signalling) and the greedy candidates are merged the same way; without it the engine uses NCCL. */
+DIS_API int dis_engine_tp_export(dis_engine *e, uint8_t out[64]);
+DIS_API int dis_engine_tp_import(dis_engine *e, const uint8_t *handles /* [tp_size][64] */);
 
 /* ---- InferenceWorker::infer as one blocking call (design.md:338,345-360) ------------------------ *
  * The C++ InferenceWorker mirror (csrc/worker.hpp) exported for non-C++ hosts.  input_ids is the

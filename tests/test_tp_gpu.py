@@ -16,7 +16,7 @@ SHAPE = O.ModelShape(2048, 512, 3, 8, 2, 64, 1408, 256)
 SEED = 21
 
 
-def _rank(rank, world, idq, outq, prompts, n_new, temps):
+def _rank(rank, world, idq, outq, prompts, n_new, temps, hq, custom):
     from distributed_inference_server_b200 import Engine, InferenceParams, WorkerConfig, shard_plan as SP
     from distributed_inference_server_b200 import binding as B
     from tests._gpu_util import to_engine_shape
@@ -33,6 +33,16 @@ def _rank(rank, world, idq, outq, prompts, n_new, temps):
                             page_size=16, max_step_tokens=256, nccl_id=nccl_id))
     e.load_synthetic(SEED)
     e.finalize()
+    if custom:  # fused all-reduce over peer memory: exchange the CUDA IPC handles of the symmetric buffers
+        mine = e.tp_export()
+        for r in range(world):
+            if r != rank:
+                hq[r].put((rank, mine))
+        handles = {rank: mine}
+        while len(handles) < world:
+            r, hdl = hq[rank].get(timeout=120)
+            handles[r] = hdl
+        e.tp_import([handles[r] for r in range(world)])
     # each rank holds exactly the plan's slice
     for kind, layer in [(O.WQ, 1), (O.WK, 0), (O.WV, 2), (O.WO, 1), (O.WGATE, 0), (O.WUP, 2), (O.WDOWN, 1), (O.LM_HEAD, 0), (O.EMBED, 0)]:
         got = O.from_bf16_bits(e.read_tensor(kind, layer))
@@ -51,15 +61,17 @@ def _rank(rank, world, idq, outq, prompts, n_new, temps):
 
 
 @pytest.mark.skipif(not torch.cuda.is_available() or torch.cuda.device_count() < 2, reason="needs 2 GPUs")
+@pytest.mark.parametrize("custom", [True, False], ids=["peer-memory", "nccl"])
 @pytest.mark.parametrize("sampled", [False, True], ids=["greedy", "sampled"])
-def test_tp2_matches_oracle(sampled):
+def test_tp2_matches_oracle(sampled, custom):
     world, n_new = 2, 12
     rng = np.random.default_rng(2)
     prompts = [rng.integers(0, SHAPE.vocab, n).tolist() for n in (7, 33, 18)]
     temps = [0.7, 0.0, 1.1] if sampled else [0.0, 0.0, 0.0]
     ctx = mp.get_context("spawn")
     idq, outq = ctx.Queue(), ctx.Queue()
-    procs = [ctx.Process(target=_rank, args=(r, world, idq, outq, prompts, n_new, temps)) for r in range(world)]
+    hq = [ctx.Queue() for _ in range(world)]
+    procs = [ctx.Process(target=_rank, args=(r, world, idq, outq, prompts, n_new, temps, hq, custom)) for r in range(world)]
     for p in procs:
         p.start()
     res = {}
