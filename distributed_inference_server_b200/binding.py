@@ -88,6 +88,8 @@ PROTOTYPES = {
     "dis_k_attn_scratch_elems": (C.c_size_t, [C.c_int32, C.c_int32, C.c_int32, C.c_int32]),
     "dis_k_attn_paged": (C.c_int, [vp, vp, C.c_int64, vp, C.c_int32, vp, vp, vp, vp, C.c_int32, C.c_int32, C.c_int32,
                                    C.c_int32, C.c_int32, C.c_int32, vp]),
+    "dis_k_attn_paged_static": (C.c_int, [vp, vp, C.c_int64, vp, C.c_int32, vp, vp, vp, C.c_int32, C.c_int32, C.c_int32, C.c_int32,
+                                          C.c_int32, C.c_int32, vp]),
     "dis_k_attn_prefill": (C.c_int, [vp, vp, C.c_int64, vp, C.c_int32, vp, vp, vp, vp, vp, C.c_int32, C.c_int32, C.c_int32,
                                      C.c_int32, C.c_int32, vp]),
     "dis_k_sample": (C.c_int, [vp, C.c_int64, C.c_int32, C.c_int32, vp, vp, vp, vp, vp, vp]),

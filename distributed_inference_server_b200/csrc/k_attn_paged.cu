@@ -13,6 +13,9 @@
 //
 // With n_splits > 1 every split writes (m, l, unnormalised o) to scratch and a combine pass merges
 // them (flash-decoding); that keeps all 148 SMs busy at batch 1.
+#include <mutex>
+
+#include "../../include/dis_engine.h"
 #include "kernels.h"
 #include "ptx.cuh"
 
@@ -538,4 +541,72 @@ cudaError_t launch_attn_prefill(const TmaMap &kv_map, long long row0, const uint
   return cudaErrorInvalidValue;
 }
 
+// ---------------------------------------------------------------------------------------------------
+// dis_k_attn_paged_static: the split-KV attention above for hosts that must not allocate.
+//
+// Who needs it: a serving process that has already handed every free byte of HBM to its KV-page pool (this
+// engine does exactly that with kv_mem_fraction) has nothing left for cudaMalloc to give, and a request
+// loop that must stay free of cudaMalloc/cudaFree -- both synchronise the whole device and stall every
+// other stream -- cannot afford the call even when memory is available.  Such a host still wants the
+// split-KV path (it is what keeps all SMs busy at small batch), which needs room for the per-split
+// (m, l, o) partials.  Here that room is a fixed array inside the library image instead of a buffer the
+// caller provides.
+namespace {
+constexpr size_t kStaticScratchFloats = DIS_ATTN_STATIC_SCRATCH_FLOATS;
+// Lives in every CUDA context that loads this library, from module load until the process exits.
+static __device__ __align__(256) float g_attn_static_scratch[kStaticScratchFloats];
+
+// In host code the array's name is only a handle for the runtime, not a device address: the address each
+// device gave its own copy has to be asked for, once per device, while that device is current.
+cudaError_t static_scratch_of_current_device(float **out) {
+  static std::mutex mu;
+  static float *ptrs[64] = {};
+  int dev = -1;
+  DIS_CUDA_TRY(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64) { set_last_error("attn_paged_static: device ordinal out of range"); return cudaErrorInvalidDevice; }
+  std::lock_guard<std::mutex> lk(mu);
+  if (!ptrs[dev]) {
+    float *p = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress(reinterpret_cast<void **>(&p), g_attn_static_scratch);
+    if (e != cudaSuccess || !p) {
+      set_last_error(std::string("attn_paged_static: cudaGetSymbolAddress failed: ") + cudaGetErrorString(e));
+      return e != cudaSuccess ? e : cudaErrorUnknown;
+    }
+    ptrs[dev] = p;
+  }
+  *out = ptrs[dev];
+  return cudaSuccess;
+}
+}  // namespace
+
 }  // namespace dis
+
+extern "C" DIS_API int dis_k_attn_paged_static(const uint16_t *q, const uint16_t *kv_pool, int64_t n_pages,
+                                               const int32_t *page_table, int32_t max_pages, const int32_t *pt_row,
+                                               const int32_t *ctx, uint16_t *out, int32_t n_splits, int32_t T,
+                                               int32_t n_heads, int32_t n_kv, int32_t d, int32_t page_size, void *stream) {
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+    dis::set_last_error("no CUDA device: there is no CPU fallback");
+    return DIS_ERR_INFERENCE_FAILED;
+  }
+  if (T <= 0 || n_splits < 1) { dis::set_last_error("attn_paged_static: T and n_splits must be positive"); return DIS_ERR_INVALID_ARGUMENT; }
+  const size_t need = dis::attn_scratch_elems(T, n_heads, d, n_splits);
+  if (need > dis::kStaticScratchFloats) {
+    dis::set_last_error("attn_paged_static: T*n_heads*n_splits*(2+d) = " + std::to_string(need) +
+                        " floats of split-KV partials do not fit the built-in scratch of " +
+                        std::to_string(dis::kStaticScratchFloats) + " floats (DIS_ATTN_STATIC_SCRATCH_FLOATS); use fewer "
+                        "splits or tokens per call, or dis_k_attn_paged with your own buffer");
+    return DIS_ERR_INVALID_ARGUMENT;
+  }
+  float *scratch = nullptr;
+  if (dis::static_scratch_of_current_device(&scratch) != cudaSuccess) return DIS_ERR_INFERENCE_FAILED;
+  dis::TmaMap map;  // encoded on the host stack; no device allocation
+  if (dis::make_kv_map(&map, kv_pool, (long long)n_pages * 2 * n_kv * page_size, d, page_size) != cudaSuccess)
+    return DIS_ERR_INFERENCE_FAILED;
+  // Nothing in the scratch has to start at zero: every (m, l, o) slot the combine pass reads is written by a
+  // split CTA of this same call first, so whatever the previous call left behind is never observed.
+  const cudaError_t e = dis::launch_attn_paged(map, 0, q, page_table, max_pages, pt_row, ctx, out, n_splits > 1 ? scratch : nullptr,
+                                               n_splits, T, n_heads, n_kv, d, page_size, static_cast<cudaStream_t>(stream));
+  return e == cudaSuccess ? DIS_OK : DIS_ERR_INFERENCE_FAILED;
+}

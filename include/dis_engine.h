@@ -237,6 +237,23 @@ DIS_API int dis_k_attn_paged(const uint16_t *q, const uint16_t *kv_pool, int64_t
                              int32_t max_pages, const int32_t *pt_row, const int32_t *ctx, uint16_t *out,
                              float *scratch, int32_t n_splits, int32_t T, int32_t n_heads, int32_t n_kv,
                              int32_t d, int32_t page_size, void *stream);
+/* dis_k_attn_paged without a scratch argument, for callers that cannot allocate device memory: a server
+ * that has already given all free HBM to its KV pages, or a request loop that must never run into the
+ * device-wide synchronisation of cudaMalloc / cudaFree.  It has no counterpart in the reference.
+ * The split-KV partials go to an array built into the library (DIS_ATTN_STATIC_SCRATCH_FLOATS floats =
+ * 8 MiB, present on every GPU that loads the library until the process exits).  A call needing more than
+ * that -- dis_k_attn_scratch_elems(T, n_heads, d, n_splits) -- is refused with DIS_ERR_INVALID_ARGUMENT and a
+ * message naming both numbers.  The entry point itself performs no cudaMalloc, cudaFree or other allocation.
+ * The first call on each device looks up that device's copy of the array (a one-time runtime query made
+ * with the caller's current device); make that first call before any stream capture begins.
+ * All calls share the one array: two calls whose kernels can overlap on the GPU (different streams, or
+ * different host threads without ordering) race on it and corrupt each other's result -- order them.
+ * Nothing in it needs clearing between calls: each call overwrites every slot it later reads. */
+#define DIS_ATTN_STATIC_SCRATCH_FLOATS (2u << 20)
+DIS_API int dis_k_attn_paged_static(const uint16_t *q, const uint16_t *kv_pool, int64_t n_pages,
+                                    const int32_t *page_table, int32_t max_pages, const int32_t *pt_row,
+                                    const int32_t *ctx, uint16_t *out, int32_t n_splits, int32_t T, int32_t n_heads,
+                                    int32_t n_kv, int32_t d, int32_t page_size, void *stream);
 /* Prefill attention: query block b is the qb_len[b] (<= 16) consecutive tokens [qb_tok0[b], ..) of the flattened
  * batch, at positions qb_pos0[b].. of the sequence with page-table row qb_ptrow[b]; causal over keys [0, pos].
  * The block's own K/V must already be in the pages.  q / out are [tokens][nh*d] bf16. */
