@@ -110,11 +110,12 @@ int Engine::init(const dis_engine_config *c) {
   ENG_CUDA(make_tma_map_2d(&wqkv_map, wqkv, L * nqkv_l, H, 128));
   ENG_CUDA(make_tma_map_2d(&wo_map, wo, L * H, qd_l, 128));
   ENG_CUDA(make_tma_map_2d(&wgu_map, wgu, L * 2 * inter_l, H, (uint32_t)gemm_pick_tile_rows(inter_l)));
+  ENG_CUDA(make_tma_map_2d(&wgu_map128, wgu, L * 2 * inter_l, H, 128));
   ENG_CUDA(make_tma_map_2d(&wdown_map, wdown, L * H, inter_l, 128));
   ENG_CUDA(make_tma_map_2d(&lm_map, lm_head, vocab_l, H, 128));
   // ---- activations
   const size_t cap = cap_tokens;
-  const size_t widest = std::max<size_t>(nqkv_l, H);
+  const size_t widest = std::max<size_t>(std::max<size_t>(nqkv_l, H), inter_l <= 4096 ? (size_t)2 * inter_l : 0);
   partial_elems = std::max(cap * widest, (size_t)16 * 128 * widest);
   ENG_CUDA(dev_alloc(&x, cap * H, &bytes_allocated));
   ENG_CUDA(dev_alloc(&xn, cap * H, &bytes_allocated));
@@ -136,8 +137,8 @@ int Engine::init(const dis_engine_config *c) {
     ENG_CUDA(dev_alloc(&cand_val_all, (size_t)max_batch * tp_size, &bytes_allocated));
     ENG_CUDA(dev_alloc(&cand_tok_all, (size_t)max_batch * tp_size, &bytes_allocated));
   }
-  const uint32_t boxes[3] = {32, 64, 128};
-  for (int i = 0; i < 3; i++) {
+  const uint32_t boxes[4] = {32, 64, 128, 256};
+  for (int i = 0; i < 4; i++) {
     ENG_CUDA(make_tma_map_2d(&xn_map[i], xn, cap, H, boxes[i]));
     ENG_CUDA(make_tma_map_2d(&attn_map[i], attn, cap, qd_l, boxes[i]));
     ENG_CUDA(make_tma_map_2d(&act_map[i], act, cap, inter_l, boxes[i]));
@@ -513,7 +514,7 @@ int Engine::pick_attn_splits(int T, int max_ctx_in_batch) const {
   return std::max(want, 1);
 }
 
-static int tile_index(int T) { const int t = gemm_token_tile(T); return t == 32 ? 0 : (t == 64 ? 1 : 2); }
+static int tile_index(int T) { const int t = gemm_token_tile(T); return t == 32 ? 0 : (t == 64 ? 1 : (t == 128 ? 2 : 3)); }
 
 // out = partial[S][T][N] of  X[T][K] * W[w_row0 : w_row0+N][K]^T
 cudaError_t Engine::linear_partial(const TmaMap *xmaps, const uint16_t *xptr, const TmaMap &wmap, const uint16_t *wptr,
@@ -621,6 +622,17 @@ cudaError_t Engine::enqueue_layers(int T, int n_splits) {
     if (gemv) {
       RET_CUDA(launch_gemv_silu(xn, wgu + (size_t)l * 2 * inter_l * H, act, T, inter_l, H, stream));
       kernel_launches += (uint64_t)((T + kGemvMaxT - 1) / kGemvMaxT);
+    } else if (gemm_token_tile(T) >= 128) {
+      // prefill is tensor-bound: full 128-row tiles (the balanced, shorter tiles would idle MMA rows)
+      RET_CUDA(launch_gemm_silu(wgu_map128, xn_map[tile_index(T)], act, T, inter_l, H, l * 2 * inter_l, 128, stream));
+      kernel_launches++;
+    } else if (inter_l <= 4096 && T <= 64 && (size_t)8 * T * 2 * inter_l <= partial_elems) {
+      // small tensor-parallel shard: a single-pass SiLU-fused GEMM would leave each CTA a long, thin K loop;
+      // split-K over the fused [2I][K] weight instead, SiLU-gate applied while the slices are summed
+      const int sgu = gemm_pick_split_k(T, 2 * inter_l, H);
+      RET_CUDA(launch_gemm_partial(wgu_map128, xn_map[tile_index(T)], partial, T, 2 * inter_l, H, l * 2 * inter_l, sgu, stream));
+      RET_CUDA(launch_silu_mul_reduce(partial, sgu, (long long)T * 2 * inter_l, act, T, inter_l, stream));
+      kernel_launches += 2;
     } else {
       RET_CUDA(launch_gemm_silu(wgu_map, xn_map[tile_index(T)], act, T, inter_l, H, l * 2 * inter_l, gemm_pick_tile_rows(inter_l), stream));
       kernel_launches++;

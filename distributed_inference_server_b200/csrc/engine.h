@@ -76,14 +76,14 @@ struct Engine {
   // weights
   uint16_t *embed = nullptr, *wqkv = nullptr, *wo = nullptr, *wgu = nullptr, *wdown = nullptr, *lm_head = nullptr;
   float *attn_norm = nullptr, *mlp_norm = nullptr, *final_norm = nullptr;
-  TmaMap wqkv_map, wo_map, wgu_map, wdown_map, lm_map;
+  TmaMap wqkv_map, wo_map, wgu_map, wgu_map128, wdown_map, lm_map;  // wgu_map: balanced tile height, wgu_map128: 128-row boxes
   // activations
   float *x = nullptr, *partial = nullptr, *logits = nullptr, *ar_buf = nullptr, *attn_scratch = nullptr;
   float *full_logits = nullptr, *gather_buf = nullptr, *cand_val = nullptr, *cand_val_all = nullptr;
   uint32_t *cand_tok = nullptr, *cand_tok_all = nullptr;
   uint16_t *xn = nullptr, *q = nullptr, *attn = nullptr, *act = nullptr;
   size_t partial_elems = 0, attn_scratch_elems = 0;
-  TmaMap xn_map[3], attn_map[3], act_map[3];  // box rows 32 / 64 / 128
+  TmaMap xn_map[4], attn_map[4], act_map[4];  // box rows 32 / 64 / 128 / 256
   uint32_t *d_out_tokens = nullptr, *h_out_tokens = nullptr;
   // KV
   uint16_t *kv_pool = nullptr;

@@ -128,6 +128,41 @@ cudaError_t launch_reduce_partials(const float *partial, int n_partial, long lon
   return launch_k(reduce_partials_kernel, dim3(blocks), dim3(256), 0, st, partial, n_partial, stride, out, n4);
 }
 
+// ------------------------------------------------------------------------------ silu_mul_reduce
+// act[t][i] = bf16(silu(sum_s p[s][t][i]) * sum_s p[s][t][I + i]) for a split-K gate-up projection whose
+// shard is too small to fill the GPU without split-K (tensor parallel ranks).
+__global__ void silu_mul_reduce_kernel(const float *__restrict__ partial, int n_partial, long long stride,
+                                       uint16_t *__restrict__ act, int T, int I) {
+  pdl_launch_dependents();
+  pdl_wait();
+  const long long n4 = (long long)T * I / 4;
+  for (long long j = blockIdx.x * (long long)blockDim.x + threadIdx.x; j < n4; j += (long long)gridDim.x * blockDim.x) {
+    const long long t = (j * 4) / I, i = (j * 4) - t * I;
+    const float *g = partial + (size_t)t * 2 * I + i;
+    float4 a = make_float4(0.f, 0.f, 0.f, 0.f), b = a;
+#pragma unroll 4
+    for (int s = 0; s < n_partial; s++) {
+      const float4 pg = *reinterpret_cast<const float4 *>(g + (size_t)s * stride);
+      const float4 pu = *reinterpret_cast<const float4 *>(g + (size_t)s * stride + I);
+      a.x += pg.x; a.y += pg.y; a.z += pg.z; a.w += pg.w;
+      b.x += pu.x; b.y += pu.y; b.z += pu.z; b.w += pu.w;
+    }
+    uint2 o;
+    o.x = float2_to_bf16x2((a.x / (1.0f + expf(-a.x))) * b.x, (a.y / (1.0f + expf(-a.y))) * b.y);
+    o.y = float2_to_bf16x2((a.z / (1.0f + expf(-a.z))) * b.z, (a.w / (1.0f + expf(-a.w))) * b.w);
+    *reinterpret_cast<uint2 *>(act + (size_t)t * I + i) = o;
+  }
+}
+
+cudaError_t launch_silu_mul_reduce(const float *partial, int n_partial, long long stride, uint16_t *act, int T, int I,
+                                   cudaStream_t st) {
+  if (T <= 0) return cudaSuccess;
+  if (I % 4 != 0) { set_last_error("silu_mul_reduce: I must be a multiple of 4"); return cudaErrorInvalidValue; }
+  const long long n4 = (long long)T * I / 4;
+  const int blocks = (int)min((long long)kNumSMs * 4, (n4 + 255) / 256);
+  return launch_k(silu_mul_reduce_kernel, dim3(blocks), dim3(256), 0, st, partial, n_partial, stride, act, T, I);
+}
+
 // ------------------------------------------------------------------------------ rope_kv_write
 // One CTA per token.  A work unit is four adjacent rotate-half pairs (i..i+3, i+d/2..i+d/2+3) of a q
 // or k head, or four adjacent v elements: two (one) float4 loads per split-K slice, all independent.

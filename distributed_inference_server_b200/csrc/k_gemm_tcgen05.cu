@@ -26,59 +26,8 @@
 namespace dis {
 
 // (mbarrier / TMA / PDL wrappers: ptx.cuh)
-template <int kCols>
-__device__ __forceinline__ void tmem_alloc(uint32_t dst_smem) {
-  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(dst_smem), "n"(kCols) : "memory");
-  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
-}
-template <int kCols>
-__device__ __forceinline__ void tmem_dealloc(uint32_t taddr) {
-  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "n"(kCols) : "memory");
-}
-// D[tmem] (+)= A[smem] * B[smem]^T, bf16 x bf16 -> fp32
-__device__ __forceinline__ void umma_bf16(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc,
-                                          uint32_t accumulate) {
-  asm volatile(
-      "{\n\t.reg .pred p;\n\t"
-      "setp.ne.b32 p, %4, 0;\n\t"
-      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
-      ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
-      : "memory");
-}
-// mbarrier arrives once all MMAs issued so far by this thread have completed
-__device__ __forceinline__ void umma_commit(uint32_t bar) {
-  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
-}
-// 32 lanes x 32 consecutive fp32 columns -> 32 registers per thread (thread = lane = accumulator row)
-__device__ __forceinline__ void tmem_ld_32x32(uint32_t taddr, uint32_t (&r)[32]) {
-  asm volatile(
-      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
-      "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,"
-      "%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
-      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
-        "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
-        "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
-        "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
-      : "r"(taddr)
-      : "memory");
-}
-__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
-
-// Shared-memory matrix descriptor, K-major operand in the canonical 128B-swizzle layout
-// (rows of 64 bf16 = 128 B, 8-row groups 1024 B apart): start>>4 | LBO=1 | SBO=64 | version=1 | SW128.
-__device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t smem_addr) {
-  return (uint64_t)((smem_addr >> 4) & 0x3FFFu) | (1ull << 16) | (64ull << 32) | (1ull << 46) | (2ull << 61);
-}
-// Instruction descriptor: D=f32, A=B=bf16, both K-major, M=128, N=kN.
-template <int kN>
-__host__ __device__ constexpr uint32_t umma_idesc() {
-  return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(kN >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
-}
-
+// (tcgen05 / TMEM wrappers and the UMMA descriptors: ptx.cuh)
 // ------------------------------------------------------------------------------------ tile config
-constexpr int kBM = 128;  // output features per CTA (TMEM lanes)
-constexpr int kBK = 64;   // bf16 per 128-byte swizzle row
-constexpr int kGemmThreads = 192;  // warp 0 TMA, warp 1 MMA + TMEM alloc, warps 2-5 epilogue
 
 template <int BN, bool kDual>
 struct GemmCfg {
@@ -259,7 +208,9 @@ cudaError_t make_tma_map_2d(TmaMap *out, const void *base, uint64_t rows, uint64
   return cudaSuccess;
 }
 
-int gemm_token_tile(int T) { return T <= 32 ? 32 : (T <= 64 ? 64 : 128); }
+// UMMA N (token tile): 32 / 64 for decode batches (HBM-bound), 128 and 256 for prefill (the wider the token tile,
+// the fewer bytes per flop cross the L2 -> SM fabric, which is what bounds the 128-wide tile)
+int gemm_token_tile(int T) { return T <= 32 ? 32 : (T <= 64 ? 64 : (T <= 128 ? 128 : 256)); }
 
 // Split-K factor: enough CTAs to keep every SM streaming (two CTAs per SM), each with >= 4 k-blocks.
 int gemm_pick_split_k(int T, int N, int K) {
@@ -301,7 +252,8 @@ cudaError_t launch_gemm_partial(const TmaMap &w_map, const TmaMap &x_map, float 
   switch (gemm_token_tile(T)) {
     case 32: return gemm_launch<32, false>(w_map, x_map, out, nullptr, T, N, K, w_row0, 0, split_k, kBM, st);
     case 64: return gemm_launch<64, false>(w_map, x_map, out, nullptr, T, N, K, w_row0, 0, split_k, kBM, st);
-    default: return gemm_launch<128, false>(w_map, x_map, out, nullptr, T, N, K, w_row0, 0, split_k, kBM, st);
+    case 128: return gemm_launch<128, false>(w_map, x_map, out, nullptr, T, N, K, w_row0, 0, split_k, kBM, st);
+    default: return gemm_launch<256, false>(w_map, x_map, out, nullptr, T, N, K, w_row0, 0, split_k, kBM, st);
   }
 }
 
@@ -319,7 +271,8 @@ cudaError_t launch_gemm_silu(const TmaMap &w_map, const TmaMap &x_map, uint16_t 
   switch (gemm_token_tile(T)) {
     case 32: return gemm_launch<32, true>(w_map, x_map, nullptr, act, T, I, K, w_row0, I, 1, tile_rows, st);
     case 64: return gemm_launch<64, true>(w_map, x_map, nullptr, act, T, I, K, w_row0, I, 1, tile_rows, st);
-    default: return gemm_launch<128, true>(w_map, x_map, nullptr, act, T, I, K, w_row0, I, 1, tile_rows, st);
+    case 128: return gemm_launch<128, true>(w_map, x_map, nullptr, act, T, I, K, w_row0, I, 1, tile_rows, st);
+    default: return gemm_launch<256, true>(w_map, x_map, nullptr, act, T, I, K, w_row0, I, 1, tile_rows, st);
   }
 }
 

@@ -13,6 +13,8 @@ cudaError_t launch_add_rmsnorm(float *x, const uint32_t *tokens, const uint16_t 
                                const int *row_map, int T, int H, float eps, cudaStream_t st);
 cudaError_t launch_reduce_partials(const float *partial, int n_partial, long long stride, float *out, long long n,
                                    cudaStream_t st);
+cudaError_t launch_silu_mul_reduce(const float *partial, int n_partial, long long stride, uint16_t *act, int T, int I,
+                                   cudaStream_t st);
 cudaError_t launch_rope_kv_write(const float *qkv, int n_partial, long long partial_stride, uint16_t *q,
                                  uint16_t *kv_pool, const int *page_table, int max_pages, const int *pt_row,
                                  const int *pos, const float *rope_cos, const float *rope_sin, int T,
