@@ -342,6 +342,53 @@ def run_ours(args):
     return 0
 
 
+def run_serving(args):
+    """BASELINE configs[4]: continuous batching, 256 concurrent requests, prompt lengths log-uniform in [128, 8192]
+    (seed 2), 128 new tokens each, through the admission queue + continuous batcher (dis_serving_*)."""
+    import torch
+    from distributed_inference_server_b200 import ContinuousBatcher, Engine, InferenceParams, LLAMA3_8B, ModelShape, WorkerConfig
+    from distributed_inference_server_b200 import binding as B
+    torch.cuda.set_device(0)
+    shape = LLAMA3_8B
+    if args.layers:
+        shape = ModelShape(shape.vocab, shape.hidden, args.layers, shape.n_heads, shape.n_kv_heads, shape.head_dim,
+                           shape.inter, shape.max_ctx, shape.rope_theta, shape.rms_eps)
+    n_req, new = args.requests, args.new_tokens
+    rng = np.random.default_rng(2)
+    lens = np.exp(rng.uniform(np.log(128), np.log(8192 - new - 1), n_req)).astype(int)
+    prompts = [rng.integers(0, shape.vocab, int(n)).tolist() for n in lens]
+    page = 64
+    pages = int(sum((n + new) // page + 2 for n in lens))
+    eng = Engine(WorkerConfig(shape, device=0, max_batch=n_req, max_step_tokens=args.prefill_chunk, page_size=page,
+                              kv_pages=pages, context_size=8192, stream=torch.cuda.current_stream().cuda_stream))
+    eng.load_synthetic(0); eng.finalize()
+    cb = ContinuousBatcher(eng, max_active=n_req, high_watermark=4 * n_req, low_watermark=2 * n_req, max_queue_size=8 * n_req,
+                           request_timeout_s=3600.0)
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for i, p in enumerate(prompts):
+        cb.submit(i, p, InferenceParams(new, 0.0))
+    res = cb.run_until_idle()
+    torch.cuda.synchronize()
+    wall = time.perf_counter() - t0
+    gen = sum(len(r["tokens"]) for r in res.values())
+    ttft = sorted(r["ttft_ms"] for r in res.values() if r["ttft_ms"] is not None)
+    st = eng.status()
+    line = {"metric": "aggregate decode tokens/s, continuous batching", "value": gen / wall, "unit": "tokens/s", "n_gpus": 1,
+            "higher_is_better": True, "dtype": "bf16", "data": "synthetic",
+            "config": {"workload": f"BASELINE configs[4]: Llama-3-8B bf16, continuous batching, {n_req} concurrent requests, "
+                                   f"prompt lengths log-uniform in [128, 8192] (mean {int(lens.mean())}), {new} new tokens each"
+                                   + (f" [REDUCED DEPTH {args.layers} layers]" if args.layers else "")},
+            "requests": n_req, "completed": sum(1 for r in res.values() if r["finish"] == B.FINISH_LENGTH),
+            "generated_tokens": gen, "prompt_tokens": int(lens.sum()), "wall_s": wall,
+            "ttft_ms_p50": ttft[len(ttft) // 2] if ttft else None, "ttft_ms_max": ttft[-1] if ttft else None,
+            "total_tokens_per_s_incl_prompt": (gen + int(lens.sum())) / wall, "kv_pages": st.kv_pages_total,
+            "gpu_launches": int(st.kernel_launches)}
+    print(json.dumps(line))
+    cb.close(); eng.close()
+    return 0
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -358,9 +405,14 @@ def main():
     ap.add_argument("--ttft-runs", type=int, default=3)
     ap.add_argument("--no-pdl", action="store_true", help="disable programmatic dependent launch (A/B)")
     ap.add_argument("--nccl-allreduce", action="store_true", help="TP: use NCCL instead of the fused peer-memory exchange (A/B)")
+    ap.add_argument("--workload", default="decode", choices=["decode", "serving"], help="serving = BASELINE configs[4]")
+    ap.add_argument("--requests", type=int, default=256)
+    ap.add_argument("--new-tokens", type=int, default=128)
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
+    if args.workload == "serving":
+        return run_serving(args)
     return run_ours(args)
 
 

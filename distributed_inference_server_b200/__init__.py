@@ -6,5 +6,5 @@ binding.py is the ctypes binding; worker.py mirrors the reference's spec'd Infer
 """
 from . import binding  # noqa: F401
 from .worker import (BatchResult, BatchedRequest, FinishReason, InferenceBatch, InferenceParams,  # noqa: F401
-                     InferenceWorker, RequestResult, WorkerConfig, WorkerError, WorkerStatus, Engine,
+                     InferenceWorker, RequestResult, WorkerConfig, WorkerError, WorkerStatus, Engine, ContinuousBatcher, QueueFull,
                      LLAMA3_8B, LLAMA3_70B, TINYLLAMA, ModelShape)

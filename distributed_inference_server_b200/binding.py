@@ -9,7 +9,9 @@ import os
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libdis_engine.so")
 
-OK, ERR_MODEL_NOT_LOADED, ERR_INFERENCE_FAILED, ERR_SHUTDOWN, ERR_OUT_OF_MEMORY, ERR_INVALID_ARGUMENT = range(6)
+OK, ERR_MODEL_NOT_LOADED, ERR_INFERENCE_FAILED, ERR_SHUTDOWN, ERR_OUT_OF_MEMORY, ERR_INVALID_ARGUMENT, ERR_QUEUE_FULL = range(7)
+PRIORITY_LOW, PRIORITY_NORMAL, PRIORITY_HIGH = 0, 1, 2
+EVENT_TOKEN, EVENT_DONE, EVENT_EXPIRED = 0, 1, 2
 FINISH_NONE, FINISH_STOP, FINISH_LENGTH, FINISH_STOP_SEQUENCE, FINISH_FAILED = range(5)
 (T_EMBED, T_ATTN_NORM, T_WQ, T_WK, T_WV, T_WO, T_MLP_NORM, T_WGATE, T_WUP, T_WDOWN, T_FINAL_NORM,
  T_LM_HEAD) = range(12)
@@ -47,6 +49,20 @@ class BatchResult(C.Structure):
     _fields_ = [("inference_ms", C.c_double), ("ttft_ms", C.c_double), ("tokens_generated", C.c_uint64)]
 
 
+class QueueConfig(C.Structure):
+    _fields_ = [("high_watermark", C.c_int32), ("low_watermark", C.c_int32), ("max_queue_size", C.c_int32),
+                ("request_timeout_s", C.c_double)]
+
+
+class QueueDepth(C.Structure):
+    _fields_ = [(n, C.c_int32) for n in ("high", "normal", "low", "total", "accepting", "active")]
+
+
+class ServingEvent(C.Structure):
+    _fields_ = [("request_id", C.c_uint64), ("kind", C.c_int32), ("token", C.c_uint32), ("index", C.c_int32),
+                ("finish_reason", C.c_int32), ("prompt_tokens", C.c_int32), ("waited_ms", C.c_double)]
+
+
 TOKEN_CALLBACK = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int32, C.c_uint32, C.c_int32, C.c_int32)
 
 u16p, u32p, i32p, f32p, u64p, vp = (C.POINTER(C.c_uint16), C.POINTER(C.c_uint32), C.POINTER(C.c_int32),
@@ -76,6 +92,15 @@ PROTOTYPES = {
     "dis_engine_tp_import": (C.c_int, [vp, vp]),
     "dis_worker_infer": (C.c_int, [vp, C.c_int32, vp, C.c_int32, vp, C.POINTER(SamplingParams), vp, C.c_int32, vp, vp,
                                    C.POINTER(BatchResult), vp, vp]),
+    "dis_serving_create": (C.c_int, [vp, C.POINTER(QueueConfig), C.c_int32, C.POINTER(vp)]),
+    "dis_serving_destroy": (C.c_int, [vp]),
+    "dis_serving_last_error": (C.c_char_p, [vp]),
+    "dis_serving_submit": (C.c_int, [vp, C.c_uint64, vp, C.c_int32, C.POINTER(SamplingParams), C.c_int32]),
+    "dis_serving_submit_at": (C.c_int, [vp, C.c_uint64, vp, C.c_int32, C.POINTER(SamplingParams), C.c_int32, C.c_double]),
+    "dis_serving_step": (C.c_int, [vp, C.POINTER(ServingEvent), C.c_int32, i32p]),
+    "dis_serving_step_at": (C.c_int, [vp, C.c_double, C.POINTER(ServingEvent), C.c_int32, i32p]),
+    "dis_serving_depth": (C.c_int, [vp, C.POINTER(QueueDepth)]),
+    "dis_serving_debug_pop": (C.c_int, [vp, C.c_int32, vp, i32p]),
     "dis_k_add_rmsnorm": (C.c_int, [vp, vp, vp, vp, C.c_int32, C.c_int64, vp, vp, vp, C.c_int32, C.c_int32,
                                     C.c_float, vp]),
     "dis_k_gemm": (C.c_int, [vp, vp, vp, C.c_int32, C.c_int32, C.c_int32, C.c_int32, vp]),

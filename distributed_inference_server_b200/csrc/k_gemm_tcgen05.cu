@@ -29,42 +29,50 @@ namespace dis {
 // (tcgen05 / TMEM wrappers and the UMMA descriptors: ptx.cuh)
 // ------------------------------------------------------------------------------------ tile config
 
+// The ring is sized at launch: a stage holds (1 or 2) weight tiles of tile_rows x 64 bf16 and one token tile, so a
+// short weight tile (tensor-parallel shard, balanced gate-up tile) buys MORE stages -- the k-loop of a weight-
+// streaming GEMM advances one k-block per (memory latency / stages), whatever the stage holds.
+constexpr int kMaxStages = 12;
+constexpr int kMaxDynSmem = 227 * 1024;
+
 template <int BN, bool kDual>
 struct GemmCfg {
-  static constexpr int kABytes = kBM * kBK * 2;
   static constexpr int kBBytes = BN * kBK * 2;
-  static constexpr int kStageBytes = (kDual ? 2 : 1) * kABytes + kBBytes;
-  static constexpr bool kTwoPerSM = kStageBytes * 3 <= 110 * 1024;
-  static constexpr int kStagesRaw = (kTwoPerSM ? 110 * 1024 : 220 * 1024) / kStageBytes;
-  static constexpr int kStages = kStagesRaw > 8 ? 8 : kStagesRaw;
   static constexpr int kAccCols = (kDual ? 2 : 1) * BN;
   static constexpr int kTmemCols = kAccCols <= 32 ? 32 : kAccCols <= 64 ? 64 : kAccCols <= 128 ? 128 : kAccCols <= 256 ? 256 : 512;
-  static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*barriers*/;
+  static int stage_bytes(int tile_rows) { return (kDual ? 2 : 1) * tile_rows * kBK * 2 + kBBytes; }
+  // The MMA always reads a 128-row A tile: behind a shorter tile it reads (and ignores) whatever follows, so the
+  // allocation is padded to keep the last stage's 16 KB read inside the CTA's shared memory.
+  static int smem_bytes(int stages, int tile_rows) {
+    return stages * stage_bytes(tile_rows) + 1024 /*align slack*/ + 256 /*barriers*/ + (tile_rows < kBM ? kBM * kBK * 2 : 0);
+  }
 };
 
 template <int BN, bool kDual>
 __global__ void __launch_bounds__(kGemmThreads)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_constant__ CUtensorMap x_map,
                     float *__restrict__ out_partial, uint16_t *__restrict__ out_act, int T, int N, int K,
-                    int w_row0, int up_row_off, int kb_per_split, int tile_rows) {
+                    int w_row0, int up_row_off, int kb_per_split, int tile_rows, int n_stages) {
   using Cfg = GemmCfg<BN, kDual>;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
-  const uint32_t bar_base = smem_base + Cfg::kStages * Cfg::kStageBytes;
-  // barriers: full[kStages], empty[kStages], tmem_full, then the TMEM base address word
+  const uint32_t a_bytes = (uint32_t)tile_rows * kBK * 2;  // a multiple of 1024 (tile_rows % 8 == 0): swizzle atoms stay aligned
+  const uint32_t stage_bytes = (kDual ? 2u : 1u) * a_bytes + Cfg::kBBytes;
+  const uint32_t bar_base = smem_base + (uint32_t)n_stages * stage_bytes;
+  // barriers: full[n_stages], empty[n_stages], tmem_full, then the TMEM base address word
   auto full_bar = [&](int s) { return bar_base + 8u * s; };
-  auto empty_bar = [&](int s) { return bar_base + 8u * (Cfg::kStages + s); };
-  const uint32_t tmem_full_bar = bar_base + 8u * (2 * Cfg::kStages);
+  auto empty_bar = [&](int s) { return bar_base + 8u * (n_stages + s); };
+  const uint32_t tmem_full_bar = bar_base + 8u * (2 * n_stages);
   const uint32_t tmem_slot = tmem_full_bar + 8u;
-  auto a_tile = [&](int s) { return smem_base + s * Cfg::kStageBytes; };
-  auto a2_tile = [&](int s) { return a_tile(s) + Cfg::kABytes; };
-  auto b_tile = [&](int s) { return a_tile(s) + (kDual ? 2 : 1) * Cfg::kABytes; };
+  auto a_tile = [&](int s) { return smem_base + s * stage_bytes; };
+  auto a2_tile = [&](int s) { return a_tile(s) + a_bytes; };
+  auto b_tile = [&](int s) { return a_tile(s) + (kDual ? 2u : 1u) * a_bytes; };
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   // tile_rows (<= 128, the weight map's box height) output features per CTA: a 128-row MMA runs on a
   // partly filled A tile; lanes >= tile_rows compute on stale shared memory and are never stored.
   const int n0 = blockIdx.x * tile_rows;
-  const uint32_t stage_tx = (uint32_t)((kDual ? 2 : 1) * tile_rows * kBK * 2 + Cfg::kBBytes);
+  const uint32_t stage_tx = stage_bytes;
   const int t0 = blockIdx.y * BN;
   const int num_kb = (K + kBK - 1) / kBK;
   const int kb0 = blockIdx.z * kb_per_split;
@@ -73,7 +81,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_cons
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&w_map);
     tma_prefetch_desc(&x_map);
-    for (int s = 0; s < Cfg::kStages; s++) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
+    for (int s = 0; s < n_stages; s++) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
     mbar_init(tmem_full_bar, 1);
     fence_barrier_init();
     fence_proxy_async();
@@ -91,7 +99,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_cons
     if (lane == 0) {
       // Weights do not depend on the previous kernel: fill the ring with weight tiles first, and only
       // then wait for the producer of the activations (programmatic dependent launch).
-      const int pre = min(kb1 - kb0, Cfg::kStages);
+      const int pre = min(kb1 - kb0, n_stages);
       for (int i = 0; i < pre; i++) {
         mbar_expect_tx(full_bar(i), stage_tx);
         tma_load_2d(a_tile(i), &w_map, (kb0 + i) * kBK, w_row0 + n0, full_bar(i), kEvictFirst);
@@ -99,15 +107,15 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_cons
       }
       pdl_wait();
       for (int i = 0; i < pre; i++) tma_load_2d(b_tile(i), &x_map, (kb0 + i) * kBK, t0, full_bar(i), kEvictLast);
-      int s = pre == Cfg::kStages ? 0 : pre;
-      uint32_t phase = pre == Cfg::kStages ? 1u : 0u;
+      int s = pre == n_stages ? 0 : pre;
+      uint32_t phase = pre == n_stages ? 1u : 0u;
       for (int kb = kb0 + pre; kb < kb1; kb++) {
         mbar_wait(empty_bar(s), phase ^ 1u);
         mbar_expect_tx(full_bar(s), stage_tx);
         tma_load_2d(a_tile(s), &w_map, kb * kBK, w_row0 + n0, full_bar(s), kEvictFirst);
         if (kDual) tma_load_2d(a2_tile(s), &w_map, kb * kBK, w_row0 + up_row_off + n0, full_bar(s), kEvictFirst);
         tma_load_2d(b_tile(s), &x_map, kb * kBK, t0, full_bar(s), kEvictLast);
-        if (++s == Cfg::kStages) { s = 0; phase ^= 1u; }
+        if (++s == n_stages) { s = 0; phase ^= 1u; }
       }
     }
   } else if (warp == 1) {
@@ -127,7 +135,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_cons
           if (kDual) umma_bf16(tmem_base + BN, umma_desc_sw128(a2_tile(s) + k * 32), bd, idesc, acc);
         }
         umma_commit(empty_bar(s));  // slot reusable once these MMAs have read it
-        if (++s == Cfg::kStages) { s = 0; phase ^= 1u; }
+        if (++s == n_stages) { s = 0; phase ^= 1u; }
       }
       umma_commit(tmem_full_bar);  // accumulator complete
     }
@@ -233,7 +241,7 @@ static cudaError_t gemm_launch(const TmaMap &w_map, const TmaMap &x_map, float *
   auto kern = gemm_tcgen05_kernel<BN, kDual>;
   static bool attr_set = false;
   if (!attr_set) {
-    DIS_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
+    DIS_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxDynSmem));
     attr_set = true;
   }
   const int num_kb = (K + kBK - 1) / kBK;
@@ -241,8 +249,17 @@ static cudaError_t gemm_launch(const TmaMap &w_map, const TmaMap &x_map, float *
   if ((num_kb + per - 1) / per != split_k) { set_last_error("gemm: split_k leaves an empty K slice; use gemm_pick_split_k"); return cudaErrorInvalidValue; }
   if (tile_rows < 8 || tile_rows > kBM || tile_rows % 8) { set_last_error("gemm: tile_rows must be a multiple of 8 in [8, 128]"); return cudaErrorInvalidValue; }
   dim3 grid((N + tile_rows - 1) / tile_rows, (T + BN - 1) / BN, split_k);
-  return launch_k(kern, grid, dim3(kGemmThreads), Cfg::kSmemBytes, st, *reinterpret_cast<const CUtensorMap *>(&w_map),
-                  *reinterpret_cast<const CUtensorMap *>(&x_map), out, act, T, N, K, w_row0, up_off, per, tile_rows);
+  // more CTAs than SMs: leave room for two per SM (one CTA's epilogue overlaps the other's stream, and under PDL
+  // the next kernel's CTA can prefetch beside this one); otherwise one CTA per SM gets the whole shared memory
+  const long long ctas = (long long)grid.x * grid.y * grid.z;
+  const int budget = (ctas > kNumSMs && BN <= 128 && Cfg::kTmemCols <= 256) ? 110 * 1024 : 220 * 1024;
+  int stages = (budget - Cfg::smem_bytes(0, tile_rows)) / Cfg::stage_bytes(tile_rows);
+  stages = stages > kMaxStages ? kMaxStages : (stages < 2 ? 2 : stages);
+  stages = stages > per ? (per < 2 ? 2 : per) : stages;  // never more stages than k-blocks
+  const int smem = Cfg::smem_bytes(stages, tile_rows);
+  if (smem > kMaxDynSmem) { set_last_error("gemm: tile does not fit shared memory"); return cudaErrorInvalidValue; }
+  return launch_k(kern, grid, dim3(kGemmThreads), (size_t)smem, st, *reinterpret_cast<const CUtensorMap *>(&w_map),
+                  *reinterpret_cast<const CUtensorMap *>(&x_map), out, act, T, N, K, w_row0, up_off, per, tile_rows, stages);
 }
 
 cudaError_t launch_gemm_partial(const TmaMap &w_map, const TmaMap &x_map, float *out, int T, int N, int K,

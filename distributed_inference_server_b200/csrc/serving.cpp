@@ -1,0 +1,278 @@
+// serving.cpp -- the callers either side of the hot path, host side, above the C ABI:
+//
+//   RequestQueue       three FIFO lanes drained High -> Normal -> Low, admission refused while the queue is over
+//                      capacity or in back-pressure, hysteresis between a high and a low watermark, expiry of
+//                      requests that waited too long.  Behaviour restated from the reference's
+//                      PriorityQueueManager (crates/core/src/queue.rs:103-126 enqueue, :130-158 dequeue_batch,
+//                      :198-226 remove_expired, :235-249 watermarks; defaults :24-33) -- a new implementation,
+//                      with an explicit clock so that it can be tested without sleeping.
+//   ContinuousBatcher  the scheduler the reference only has as a window batcher in its spec (design.md:227-267,
+//                      requirements.md:45-48): between decode steps it admits queued requests into free
+//                      engine slots (KV pages permitting), prefills the newcomers, decodes everybody, retires
+//                      finished sequences and reports one event per token (TokenEvent, models.rs:268-288).
+#include <algorithm>
+#include <chrono>
+#include <cstring>
+#include <deque>
+#include <mutex>
+#include <string>
+#include <unordered_map>
+#include <vector>
+
+#include "../../include/dis_engine.h"
+
+namespace {
+
+struct Queued {
+  uint64_t id;
+  int priority;
+  double enqueued_at;
+  std::vector<uint32_t> prompt;
+  dis_sampling_params params;
+  std::vector<uint32_t> stop_tokens;
+  std::vector<int32_t> stop_lens;
+};
+
+class RequestQueue {
+ public:
+  explicit RequestQueue(const dis_queue_config &c) : cfg_(c) {}
+
+  // queue.rs:103-126: refused while back-pressure is on or the queue is at capacity
+  bool enqueue(Queued &&r) {
+    if (backpressure_ || total() >= (size_t)cfg_.max_queue_size) return false;
+    lane(r.priority).push_back(std::move(r));
+    update();
+    return true;
+  }
+  // queue.rs:130-158: High first, then Normal, then Low, FIFO inside a lane
+  bool pop(Queued *out) {
+    for (int p = DIS_PRIORITY_HIGH; p >= DIS_PRIORITY_LOW; p--) {
+      auto &q = lanes_[p];
+      if (!q.empty()) { *out = std::move(q.front()); q.pop_front(); update(); return true; }
+    }
+    return false;
+  }
+  // a request that could not be admitted yet (no KV pages) goes back to the head of its lane
+  void push_front(Queued &&r) { lane(r.priority).push_front(std::move(r)); update(); }
+  // queue.rs:198-226: everything that waited longer than the timeout leaves the queue
+  void remove_expired(double now, std::vector<Queued> *expired) {
+    for (auto &q : lanes_) {
+      for (size_t i = 0; i < q.size();) {
+        if (now - q[i].enqueued_at > cfg_.request_timeout_s) { expired->push_back(std::move(q[i])); q.erase(q.begin() + (long)i); }
+        else i++;
+      }
+    }
+    update();
+  }
+  size_t total() const { return lanes_[0].size() + lanes_[1].size() + lanes_[2].size(); }
+  size_t depth(int p) const { return lanes_[p].size(); }
+  bool accepting() const { return !backpressure_; }
+
+ private:
+  std::deque<Queued> &lane(int p) { return lanes_[p < 0 ? 0 : (p > 2 ? 2 : p)]; }
+  // queue.rs:235-249: on above the high watermark, off only once below the low watermark
+  void update() {
+    const size_t t = total();
+    if (backpressure_) { if (t < (size_t)cfg_.low_watermark) backpressure_ = false; }
+    else if (t > (size_t)cfg_.high_watermark) backpressure_ = true;
+  }
+  dis_queue_config cfg_;
+  std::deque<Queued> lanes_[3];
+  bool backpressure_ = false;
+};
+
+double steady_now() {
+  return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count();
+}
+
+struct Active {
+  uint64_t id;
+  int32_t slot;
+  int32_t produced;
+  int32_t prompt_tokens;
+  double enqueued_at;
+};
+
+}  // namespace
+
+struct dis_serving {
+  dis_engine *eng = nullptr;
+  dis_queue_config cfg{};
+  RequestQueue queue;
+  std::vector<Active> active;
+  std::deque<dis_serving_event> pending;
+  std::mutex mu;
+  int32_t max_active = 0;
+  int32_t prefill_budget = 8192;  // prompt tokens admitted per scheduler step
+  bool decode_next = false;       // after a prefill step the running sequences get a decode step before the next admission
+  std::string last_error;
+  explicit dis_serving(const dis_queue_config &c) : cfg(c), queue(c) {}
+};
+
+static void emit(dis_serving *s, uint64_t id, int kind, uint32_t token, int32_t index, int32_t finish, int32_t prompt_tokens,
+                 double waited_ms) {
+  dis_serving_event e;
+  memset(&e, 0, sizeof(e));
+  e.request_id = id; e.kind = kind; e.token = token; e.index = index; e.finish_reason = finish;
+  e.prompt_tokens = prompt_tokens; e.waited_ms = waited_ms;
+  s->pending.push_back(e);
+}
+
+extern "C" {
+
+int dis_serving_create(dis_engine *engine, const dis_queue_config *cfg, int32_t max_active, dis_serving **out) {
+  if (!out) return DIS_ERR_INVALID_ARGUMENT;
+  dis_queue_config c;
+  if (cfg) c = *cfg;
+  else { c.high_watermark = 1000; c.low_watermark = 500; c.max_queue_size = 2000; c.request_timeout_s = 30.0; }  // queue.rs:24-33
+  if (c.low_watermark > c.high_watermark || c.max_queue_size <= 0) return DIS_ERR_INVALID_ARGUMENT;
+  dis_serving *s = new dis_serving(c);
+  s->eng = engine;  // NULL: queue-only (admission control can be exercised without a GPU)
+  s->max_active = max_active > 0 ? max_active : 32;
+  *out = s;
+  return DIS_OK;
+}
+
+int dis_serving_destroy(dis_serving *s) {
+  if (!s) return DIS_ERR_INVALID_ARGUMENT;
+  if (s->eng) for (auto &a : s->active) dis_engine_seq_remove(s->eng, a.slot);
+  delete s;
+  return DIS_OK;
+}
+
+const char *dis_serving_last_error(dis_serving *s) { return s ? s->last_error.c_str() : ""; }
+
+int dis_serving_submit_at(dis_serving *s, uint64_t request_id, const uint32_t *prompt, int32_t n_prompt,
+                          const dis_sampling_params *params, int32_t priority, double now_s) {
+  if (!s || !prompt || n_prompt <= 0 || !params) return DIS_ERR_INVALID_ARGUMENT;
+  std::lock_guard<std::mutex> lk(s->mu);
+  Queued q;
+  q.id = request_id; q.priority = priority; q.enqueued_at = now_s;
+  q.prompt.assign(prompt, prompt + n_prompt);
+  q.params = *params;
+  size_t off = 0;
+  for (int i = 0; i < params->n_stop; i++) {
+    const int len = params->stop_lens ? params->stop_lens[i] : 0;
+    for (int k = 0; k < len; k++) q.stop_tokens.push_back(params->stop_tokens[off + k]);
+    q.stop_lens.push_back(len);
+    off += (size_t)std::max(len, 0);
+  }
+  if (!s->queue.enqueue(std::move(q))) { s->last_error = "queue full"; return DIS_ERR_QUEUE_FULL; }
+  return DIS_OK;
+}
+
+int dis_serving_submit(dis_serving *s, uint64_t request_id, const uint32_t *prompt, int32_t n_prompt,
+                       const dis_sampling_params *params, int32_t priority) {
+  return dis_serving_submit_at(s, request_id, prompt, n_prompt, params, priority, steady_now());
+}
+
+int dis_serving_depth(dis_serving *s, dis_queue_depth *out) {
+  if (!s || !out) return DIS_ERR_INVALID_ARGUMENT;
+  std::lock_guard<std::mutex> lk(s->mu);
+  out->low = (int32_t)s->queue.depth(DIS_PRIORITY_LOW);
+  out->normal = (int32_t)s->queue.depth(DIS_PRIORITY_NORMAL);
+  out->high = (int32_t)s->queue.depth(DIS_PRIORITY_HIGH);
+  out->total = (int32_t)s->queue.total();
+  out->accepting = s->queue.accepting() ? 1 : 0;
+  out->active = (int32_t)s->active.size();
+  return DIS_OK;
+}
+
+// Queue-only helper (tests of the admission order without an engine): pops up to `max` requests in
+// scheduling order and returns their ids.
+int dis_serving_debug_pop(dis_serving *s, int32_t max, uint64_t *ids, int32_t *n) {
+  if (!s || !ids || !n) return DIS_ERR_INVALID_ARGUMENT;
+  std::lock_guard<std::mutex> lk(s->mu);
+  *n = 0;
+  Queued q;
+  while (*n < max && s->queue.pop(&q)) ids[(*n)++] = q.id;
+  return DIS_OK;
+}
+
+static int drain(dis_serving *s, dis_serving_event *events, int32_t cap, int32_t *n_events) {
+  *n_events = 0;
+  while (*n_events < cap && !s->pending.empty()) { events[(*n_events)++] = s->pending.front(); s->pending.pop_front(); }
+  return DIS_OK;
+}
+
+int dis_serving_step_at(dis_serving *s, double now_s, dis_serving_event *events, int32_t cap, int32_t *n_events) {
+  if (!s || !events || !n_events || cap <= 0) return DIS_ERR_INVALID_ARGUMENT;
+  std::lock_guard<std::mutex> lk(s->mu);
+  if (!s->pending.empty()) return drain(s, events, cap, n_events);  // deliver what is owed first
+  // 1. requests that waited too long (ApiError::Timeout -> HTTP 408, crates/core/src/error.rs:46)
+  std::vector<Queued> expired;
+  s->queue.remove_expired(now_s, &expired);
+  for (auto &q : expired) emit(s, q.id, DIS_EVENT_EXPIRED, 0, 0, DIS_FINISH_FAILED, (int32_t)q.prompt.size(), (now_s - q.enqueued_at) * 1e3);
+  if (!s->eng) return drain(s, events, cap, n_events);
+
+  // 2. admission: free slots, High -> Normal -> Low, a bounded number of prompt tokens per step
+  std::vector<Active> fresh;
+  if (!(s->decode_next && !s->active.empty())) {
+    int budget = s->prefill_budget;
+    Queued q;
+    while ((int32_t)(s->active.size() + fresh.size()) < s->max_active && budget > 0 && s->queue.pop(&q)) {
+      dis_sampling_params p = q.params;
+      p.stop_tokens = q.stop_tokens.empty() ? nullptr : q.stop_tokens.data();
+      p.stop_lens = q.stop_lens.empty() ? nullptr : q.stop_lens.data();
+      p.n_stop = (int32_t)q.stop_lens.size();
+      int32_t slot = -1;
+      const int rc = dis_engine_seq_add(s->eng, q.prompt.data(), (int32_t)q.prompt.size(), &p, &slot);
+      if (rc == DIS_ERR_OUT_OF_MEMORY && (!s->active.empty() || !fresh.empty())) {
+        s->queue.push_front(std::move(q));  // wait for running sequences to free KV pages / slots
+        break;
+      }
+      if (rc == DIS_ERR_MODEL_NOT_LOADED || rc == DIS_ERR_SHUTDOWN) { s->queue.push_front(std::move(q)); s->last_error = dis_engine_last_error(s->eng); return rc; }
+      if (rc != DIS_OK) {  // a bad request fails alone (Property 22, design.md:812-816)
+        emit(s, q.id, DIS_EVENT_DONE, 0, 0, DIS_FINISH_FAILED, (int32_t)q.prompt.size(), (now_s - q.enqueued_at) * 1e3);
+        continue;
+      }
+      budget -= (int)q.prompt.size();
+      fresh.push_back(Active{q.id, slot, 0, (int32_t)q.prompt.size(), q.enqueued_at});
+    }
+  }
+  auto retire = [&](std::vector<Active> &set, const std::vector<uint32_t> &toks, const std::vector<int32_t> &fin) {
+    std::vector<Active> keep;
+    for (size_t i = 0; i < set.size(); i++) {
+      Active a = set[i];
+      if (fin[i] == DIS_FINISH_FAILED) {  // produced no token
+        emit(s, a.id, DIS_EVENT_DONE, 0, a.produced, DIS_FINISH_FAILED, a.prompt_tokens, 0.0);
+        dis_engine_seq_remove(s->eng, a.slot);
+        continue;
+      }
+      emit(s, a.id, DIS_EVENT_TOKEN, toks[i], a.produced, fin[i], a.prompt_tokens, a.produced == 0 ? (steady_now() - a.enqueued_at) * 1e3 : 0.0);
+      a.produced++;
+      if (fin[i] != DIS_FINISH_NONE) {
+        emit(s, a.id, DIS_EVENT_DONE, 0, a.produced, fin[i], a.prompt_tokens, 0.0);
+        dis_engine_seq_remove(s->eng, a.slot);
+      } else keep.push_back(a);
+    }
+    set.swap(keep);
+  };
+  if (!fresh.empty()) {
+    // 3. prefill the newcomers: their first token
+    std::vector<int32_t> slots, fin(fresh.size());
+    std::vector<uint32_t> toks(fresh.size());
+    for (auto &a : fresh) slots.push_back(a.slot);
+    const int rc = dis_engine_prefill(s->eng, (int32_t)slots.size(), slots.data(), toks.data(), fin.data());
+    if (rc != DIS_OK) { s->last_error = dis_engine_last_error(s->eng); for (auto &a : fresh) dis_engine_seq_remove(s->eng, a.slot); return rc; }
+    retire(fresh, toks, fin);
+    s->active.insert(s->active.end(), fresh.begin(), fresh.end());
+    s->decode_next = true;
+  } else if (!s->active.empty()) {
+    // 4. one decode step for everybody
+    std::vector<int32_t> slots, fin(s->active.size());
+    std::vector<uint32_t> toks(s->active.size());
+    for (auto &a : s->active) slots.push_back(a.slot);
+    const int rc = dis_engine_decode(s->eng, (int32_t)slots.size(), slots.data(), toks.data(), fin.data());
+    if (rc != DIS_OK) { s->last_error = dis_engine_last_error(s->eng); return rc; }
+    retire(s->active, toks, fin);
+    s->decode_next = false;
+  }
+  return drain(s, events, cap, n_events);
+}
+
+int dis_serving_step(dis_serving *s, dis_serving_event *events, int32_t cap, int32_t *n_events) {
+  return dis_serving_step_at(s, steady_now(), events, cap, n_events);
+}
+
+}  // extern "C"

@@ -369,3 +369,90 @@ class InferenceWorker:
             results.append(RequestResult(reqs[i].id, t, fr.get(int(fin[i]), FinishReason.Length), int(lens[i]), len(t),
                                          failed=int(fin[i]) == B.FINISH_FAILED))
         return BatchResult(batch.id, results, res.inference_ms / 1e3, int(res.tokens_generated), res.ttft_ms / 1e3)
+
+
+class QueueFull(Exception):
+    """QueueError::Full (crates/core/src/error.rs:79-89): the admission queue refuses the request (HTTP 503)."""
+
+
+class ContinuousBatcher:
+    """Admission queue + continuous batching over one engine (dis_serving_*).  `engine=None` gives the queue alone.
+
+    Queue semantics follow crates/core/src/queue.rs (High -> Normal -> Low FIFO lanes, watermark back-pressure,
+    expiry); events follow TokenEvent (crates/core/src/models.rs:268-288)."""
+
+    def __init__(self, engine: Optional[Engine], max_active: int = 32, high_watermark: int = 1000, low_watermark: int = 500,
+                 max_queue_size: int = 2000, request_timeout_s: float = 30.0):
+        self.lib = B.load()
+        self.engine = engine
+        cfg = B.QueueConfig(high_watermark, low_watermark, max_queue_size, request_timeout_s)
+        self.h = C.c_void_p()
+        rc = self.lib.dis_serving_create(engine.h if engine is not None else None, C.byref(cfg), max_active, C.byref(self.h))
+        if rc != B.OK:
+            raise ValueError("dis_serving_create: bad queue configuration")
+        self._events = (B.ServingEvent * 1024)()
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.dis_serving_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def submit(self, request_id: int, prompt: Sequence[int], params: InferenceParams, priority: int = B.PRIORITY_NORMAL,
+               now: Optional[float] = None) -> None:
+        p = np.ascontiguousarray(prompt, dtype=np.uint32)
+        sp, keep = _sampling(params)
+        if now is None:
+            rc = self.lib.dis_serving_submit(self.h, request_id, p.ctypes.data, len(p), C.byref(sp), priority)
+        else:
+            rc = self.lib.dis_serving_submit_at(self.h, request_id, p.ctypes.data, len(p), C.byref(sp), priority, now)
+        if rc == B.ERR_QUEUE_FULL:
+            raise QueueFull()
+        if rc != B.OK:
+            raise WorkerError(_KIND.get(rc, WorkerError.InferenceFailed), "submit")
+
+    def step(self, now: Optional[float] = None):
+        """One scheduler iteration; returns the list of events it produced."""
+        n = C.c_int32(0)
+        if now is None:
+            rc = self.lib.dis_serving_step(self.h, self._events, len(self._events), C.byref(n))
+        else:
+            rc = self.lib.dis_serving_step_at(self.h, now, self._events, len(self._events), C.byref(n))
+        if rc != B.OK:
+            raise WorkerError(_KIND.get(rc, WorkerError.InferenceFailed), self.lib.dis_serving_last_error(self.h).decode())
+        return [(e.request_id, e.kind, e.token, e.index, e.finish_reason, e.prompt_tokens, e.waited_ms)
+                for e in self._events[:n.value]]
+
+    def depth(self) -> B.QueueDepth:
+        d = B.QueueDepth()
+        self.lib.dis_serving_depth(self.h, C.byref(d))
+        return d
+
+    def debug_pop(self, max_count: int):
+        ids = (C.c_uint64 * max_count)()
+        n = C.c_int32(0)
+        self.lib.dis_serving_debug_pop(self.h, max_count, ids, C.byref(n))
+        return list(ids[:n.value])
+
+    def run_until_idle(self, max_steps: int = 1_000_000):
+        """Drive the scheduler until queue and engine are empty; returns {request_id: (tokens, finish_reason)}."""
+        out = {}
+        for _ in range(max_steps):
+            evs = self.step()
+            for rid, kind, tok, idx, fin, ptoks, waited in evs:
+                rec = out.setdefault(rid, {"tokens": [], "finish": None, "ttft_ms": None, "prompt_tokens": ptoks})
+                if kind == B.EVENT_TOKEN:
+                    rec["tokens"].append(tok)
+                    if idx == 0:
+                        rec["ttft_ms"] = waited
+                else:
+                    rec["finish"] = fin if kind == B.EVENT_DONE else "expired"
+            d = self.depth()
+            if d.total == 0 and d.active == 0 and not evs:
+                break
+        return out

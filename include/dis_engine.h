@@ -40,7 +40,8 @@ typedef enum dis_status {
   DIS_ERR_INFERENCE_FAILED = 2, /* WorkerError::InferenceFailed error.rs:121 (message: last_error) */
   DIS_ERR_SHUTDOWN = 3,         /* WorkerError::Shutdown        error.rs:124 */
   DIS_ERR_OUT_OF_MEMORY = 4,    /* WorkerError::OutOfMemory     error.rs:127 */
-  DIS_ERR_INVALID_ARGUMENT = 5  /* caller bug; a Rust shim maps it to InferenceFailed */
+  DIS_ERR_INVALID_ARGUMENT = 5, /* caller bug; a Rust shim maps it to InferenceFailed */
+  DIS_ERR_QUEUE_FULL = 6        /* QueueError::Full (error.rs:79-89) -> ApiError::QueueFull, HTTP 503 (error.rs:42) */
 } dis_status;
 
 /* ---- FinishReason: crates/core/src/models.rs:26-32 (plus "still running") ---------------------- */
@@ -193,6 +194,45 @@ DIS_API int dis_worker_infer(dis_engine *e, int32_t n, const uint32_t *input_ids
                              uint32_t *out_tokens, int32_t max_new_cap, int32_t *out_lens,
                              int32_t *out_finish, dis_batch_result *result, dis_token_callback on_token,
                              void *user);
+
+/* ---- admission queue + continuous batching ------------------------------- *
+ * Host-side callers of the step-wise entry points above.  The queue restates the behaviour of the reference's
+ * PriorityQueueManager (crates/core/src/queue.rs:75-250): three FIFO lanes served High -> Normal -> Low
+ * (Priority, types.rs:17-28), enqueue refused (DIS_ERR_QUEUE_FULL) at max_queue_size or while back-pressure
+ * is on, back-pressure switched on above high_watermark and off below low_watermark, requests older than
+ * request_timeout_s expired; defaults (cfg == NULL) are queue.rs:24-33.  The batcher replaces the spec's
+ * 50 ms window batcher (design.md:227-267): every dis_serving_step admits queued requests into free engine
+ * slots (KV pages permitting) and prefills them, or runs one decode step for all running sequences, and
+ * reports one event per generated token (TokenEvent, models.rs:268-288).  engine == NULL gives a queue-only
+ * object (admission logic without a GPU).  The *_at variants take the clock as an argument. */
+typedef enum dis_priority { DIS_PRIORITY_LOW = 0, DIS_PRIORITY_NORMAL = 1, DIS_PRIORITY_HIGH = 2 } dis_priority;
+typedef struct dis_queue_config {
+  int32_t high_watermark, low_watermark, max_queue_size;
+  double request_timeout_s;
+} dis_queue_config;
+typedef struct dis_queue_depth { int32_t high, normal, low, total, accepting, active; } dis_queue_depth;
+typedef enum dis_event_kind { DIS_EVENT_TOKEN = 0, DIS_EVENT_DONE = 1, DIS_EVENT_EXPIRED = 2 } dis_event_kind;
+typedef struct dis_serving_event {
+  uint64_t request_id;
+  int32_t kind;           /* dis_event_kind */
+  uint32_t token;         /* TOKEN */
+  int32_t index;          /* TOKEN: position in the completion; DONE: completion_tokens (Usage, models.rs:9-23) */
+  int32_t finish_reason;  /* dis_finish_reason; DIS_FINISH_NONE on a token that does not end the request */
+  int32_t prompt_tokens;
+  double waited_ms;       /* first TOKEN: time from submit to first token (TTFT); EXPIRED: time spent queued */
+} dis_serving_event;
+typedef struct dis_serving dis_serving;
+DIS_API int dis_serving_create(dis_engine *engine, const dis_queue_config *cfg, int32_t max_active, dis_serving **out);
+DIS_API int dis_serving_destroy(dis_serving *s);
+DIS_API const char *dis_serving_last_error(dis_serving *s);
+DIS_API int dis_serving_submit(dis_serving *s, uint64_t request_id, const uint32_t *prompt, int32_t n_prompt,
+                               const dis_sampling_params *params, int32_t priority);
+DIS_API int dis_serving_submit_at(dis_serving *s, uint64_t request_id, const uint32_t *prompt, int32_t n_prompt,
+                                  const dis_sampling_params *params, int32_t priority, double now_s);
+DIS_API int dis_serving_step(dis_serving *s, dis_serving_event *events, int32_t cap, int32_t *n_events);
+DIS_API int dis_serving_step_at(dis_serving *s, double now_s, dis_serving_event *events, int32_t cap, int32_t *n_events);
+DIS_API int dis_serving_depth(dis_serving *s, dis_queue_depth *out);
+DIS_API int dis_serving_debug_pop(dis_serving *s, int32_t max, uint64_t *ids, int32_t *n);
 
 /* ---- kernel-level entry points ------------------------------------------------------------------ *
  * One per hand-written kernel, taking DEVICE pointers and a cudaStream_t (NULL = default stream).

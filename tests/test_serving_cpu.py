@@ -1,0 +1,90 @@
+"""Admission queue of the serving layer (dis_serving_*, queue-only mode: no GPU needed) against the behaviour
+the reference's PriorityQueueManager has (crates/core/src/queue.rs) and its spec properties 6-8
+(.kiro/specs/distributed-inference-server/design.md:716-732).  The reference ships no tests for its queue."""
+import pytest
+from hypothesis import given, settings, strategies as st
+
+from distributed_inference_server_b200 import ContinuousBatcher, InferenceParams, QueueFull
+from distributed_inference_server_b200 import binding as B
+
+P = InferenceParams(4, 0.0)
+
+
+def mk(**kw):
+    return ContinuousBatcher(None, **kw)
+
+
+@settings(max_examples=100, deadline=None)
+@given(st.lists(st.integers(0, 2), min_size=0, max_size=60), st.integers(1, 70))
+def test_property6_priority_then_fifo(prios, take):
+    q = mk()
+    for i, p in enumerate(prios):
+        q.submit(i, [1], P, priority=p, now=0.0)
+    got = q.debug_pop(take)
+    want = [i for p in (2, 1, 0) for i, x in enumerate(prios) if x == p][:take]
+    assert got == want
+    assert q.depth().total == len(prios) - len(got)
+
+
+@settings(max_examples=100, deadline=None)
+@given(st.lists(st.one_of(st.just("push"), st.integers(1, 6)), min_size=1, max_size=120),
+       st.integers(2, 12), st.integers(0, 6))
+def test_property7_backpressure_hysteresis(ops, high, low_gap):
+    low = max(0, high - low_gap)
+    q = mk(high_watermark=high, low_watermark=low, max_queue_size=10 * high)
+    accepting, depth, nid = True, 0, 0
+    for op in ops:
+        if op == "push":
+            nid += 1
+            try:
+                q.submit(nid, [1], P, now=0.0)
+                assert accepting                       # a refused state never accepts
+                depth += 1
+            except QueueFull:
+                assert not accepting
+        else:
+            depth -= len(q.debug_pop(op))
+        # model of queue.rs:235-249
+        if accepting and depth > high:
+            accepting = False
+        elif not accepting and depth < low:
+            accepting = True
+        d = q.depth()
+        assert d.total == depth and bool(d.accepting) == accepting
+        if depth > high:
+            assert not d.accepting
+        if depth < low:
+            assert d.accepting
+
+
+def test_capacity_limit_and_defaults():
+    q = mk(high_watermark=100, low_watermark=50, max_queue_size=5)
+    for i in range(5):
+        q.submit(i, [1], P, now=0.0)
+    with pytest.raises(QueueFull):
+        q.submit(5, [1], P, now=0.0)                   # queue.rs:110-113
+    d = ContinuousBatcher(None)                         # defaults: queue.rs:24-33
+    for i in range(1001):
+        d.submit(i, [1], P, now=0.0)
+    assert not d.depth().accepting                      # 1001 > high watermark 1000
+    d.debug_pop(501)
+    assert not d.depth().accepting                      # 500 is not < 500
+    d.debug_pop(1)
+    assert d.depth().accepting
+    with pytest.raises(ValueError):
+        mk(high_watermark=1, low_watermark=2)
+
+
+@settings(max_examples=50, deadline=None)
+@given(st.lists(st.tuples(st.floats(0, 100), st.integers(0, 2)), min_size=1, max_size=40), st.floats(1, 50), st.floats(0, 200))
+def test_property8_timeout(arrivals, timeout, now):
+    q = mk(request_timeout_s=timeout)
+    for i, (t, p) in enumerate(arrivals):
+        q.submit(i, [1, 2], P, priority=p, now=t)
+    events = q.step(now=now)                            # queue-only object: expiry only
+    expired = sorted(e[0] for e in events if e[1] == B.EVENT_EXPIRED)
+    want = sorted(i for i, (t, _) in enumerate(arrivals) if now - t > timeout)
+    assert expired == want
+    assert q.depth().total == len(arrivals) - len(want)
+    for e in events:
+        assert e[4] == B.FINISH_FAILED and e[5] == 2 and e[6] >= timeout * 1e3 - 1e-6
