@@ -161,7 +161,11 @@ def run_reference(args):
     return 0
 
 
-def workload_config(n_gpus, batch, prompt_len):
+def workload_config(n_gpus, batch, prompt_len, model="8b"):
+    if model == "70b":
+        w = f"BASELINE configs[3]: Llama-3-70B bf16, tensor parallel TP={n_gpus}, batch {batch} decode, {prompt_len}-token prompts, paged KV"
+        return {"workload": w, "batch": batch, "prompt_len": prompt_len, "parallelism": f"tp{n_gpus}",
+                "tp_exchange": "fused peer-memory all-reduce (k_tp.cu)", "l2": "working set far larger than L2; no explicit flush"}
     if n_gpus == 1:
         w = f"BASELINE configs[1]: Llama-3-8B bf16, 1 B200, batch {batch} decode, {prompt_len}-token prompts"
     else:
@@ -198,11 +202,12 @@ def run_ours(args):
         dist.broadcast(idt, 0)
         nccl_id = bytes(idt.cpu().tolist())
 
-    shape = LLAMA3_8B
+    from distributed_inference_server_b200 import LLAMA3_70B
+    shape = LLAMA3_70B if args.model == "70b" else LLAMA3_8B
     if args.layers:
         shape = ModelShape(shape.vocab, shape.hidden, args.layers, shape.n_heads, shape.n_kv_heads, shape.head_dim,
                            shape.inter, shape.max_ctx, shape.rope_theta, shape.rms_eps)
-    batch = args.batch or (32 if world == 1 else 64)
+    batch = args.batch or (32 if (world == 1 or args.model == "70b") else 64)
     n_ttft = max(1, args.ttft_runs)
     total_steps = args.warmup + args.steps + args.profile_steps + 2
     page = 64
@@ -307,10 +312,10 @@ def run_ours(args):
             roof["frac"] = roof["achieved"] / peak
             roof["avg_launch_ms"] = avg_ms
         step_gbs = step_bytes / (ms_per_step * 1e-3) / 1e9
-        line = {"metric": "decode tokens/s Llama-3-8B", "value": value, "unit": "tokens/s", "n_gpus": world,
+        line = {"metric": "decode tokens/s Llama-3-" + args.model.upper(), "value": value, "unit": "tokens/s", "n_gpus": world,
                 "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
                 "scaling": "strong" if world > 1 else "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-                "config": workload_config(world, batch, args.prompt_len),
+                "config": workload_config(world, batch, args.prompt_len, args.model),
                 "roofline": roof,
                 "step_roofline": {"bound": "hbm", "algorithmic_bytes_per_step_per_gpu": step_bytes, "achieved": step_gbs,
                                   "peak": peak, "unit": "GB/s", "frac": step_gbs / peak, "frac_of_nominal_8TBs": step_gbs / 8000.0,
@@ -406,6 +411,7 @@ def main():
     ap.add_argument("--no-pdl", action="store_true", help="disable programmatic dependent launch (A/B)")
     ap.add_argument("--nccl-allreduce", action="store_true", help="TP: use NCCL instead of the fused peer-memory exchange (A/B)")
     ap.add_argument("--workload", default="decode", choices=["decode", "serving"], help="serving = BASELINE configs[4]")
+    ap.add_argument("--model", default="8b", choices=["8b", "70b"], help="70b = BASELINE configs[3] (TP=8, batch 32)")
     ap.add_argument("--requests", type=int, default=256)
     ap.add_argument("--new-tokens", type=int, default=128)
     args = ap.parse_args()
