@@ -207,6 +207,10 @@ def run_ours(args):
     if args.layers:
         shape = ModelShape(shape.vocab, shape.hidden, args.layers, shape.n_heads, shape.n_kv_heads, shape.head_dim,
                            shape.inter, shape.max_ctx, shape.rope_theta, shape.rms_eps)
+    if args.shard_of > 1:  # one rank's shard of a TP=N run, without the exchange: isolates compute from communication
+        n = args.shard_of
+        shape = ModelShape(shape.vocab // n, shape.hidden, shape.layers, shape.n_heads // n, shape.n_kv_heads // n, shape.head_dim,
+                           shape.inter // n, shape.max_ctx, shape.rope_theta, shape.rms_eps)
     batch = args.batch or (32 if (world == 1 or args.model == "70b") else 64)
     n_ttft = max(1, args.ttft_runs)
     total_steps = args.warmup + args.steps + args.profile_steps + 2
@@ -332,6 +336,8 @@ def run_ours(args):
                 "kv_pages": st.kv_pages_total, "device_mem_gb": st.memory_used / 1e9}
         if args.layers:
             line["config"]["workload"] += f" [REDUCED DEPTH {args.layers} layers: not a valid headline number]"
+        if args.shard_of > 1:
+            line["config"]["workload"] += f" [DIAGNOSTIC: one rank's shard of TP={args.shard_of}, no exchange: not a headline number]"
     eng.close()
     if rank == 0 and not args.no_cpu and world >= 1:
         try:
@@ -413,6 +419,7 @@ def main():
     ap.add_argument("--workload", default="decode", choices=["decode", "serving"], help="serving = BASELINE configs[4]")
     ap.add_argument("--model", default="8b", choices=["8b", "70b"], help="70b = BASELINE configs[3] (TP=8, batch 32)")
     ap.add_argument("--requests", type=int, default=256)
+    ap.add_argument("--shard-of", type=int, default=1, help="diagnostic: run one rank's shard of a TP=N model on one GPU, no exchange")
     ap.add_argument("--new-tokens", type=int, default=128)
     args = ap.parse_args()
     if args.impl == "reference":
