@@ -597,20 +597,23 @@ cudaError_t Engine::enqueue_layers(int T, int n_splits) {
     prof_mark(P_QKV);
     RET_CUDA(linear_partial(xn_map, xn, wqkv_map, wqkv, l * nqkv_l, T, nqkv_l, H, &s_qkv));
     uint16_t *pool = kv_pool + (size_t)l * kv_layer_stride;
-    prof_mark(P_ROPE);
-    RET_CUDA(launch_rope_kv_write(partial, s_qkv, (long long)T * nqkv_l, q, pool, d_page_table, max_pages, ptrow, pos,
-                                  rope_cos, rope_sin, T, nh_l, nkv_l, d, page_size, stream));
-    prof_mark(P_ATTN);
     if (n_qblocks > 0) {
+      prof_mark(P_ROPE);
+      RET_CUDA(launch_rope_kv_write(partial, s_qkv, (long long)T * nqkv_l, q, pool, d_page_table, max_pages, ptrow, pos,
+                                    rope_cos, rope_sin, T, nh_l, nkv_l, d, page_size, stream));
+      prof_mark(P_ATTN);
       RET_CUDA(launch_attn_prefill(kv_map, (long long)l * kv_rows_per_layer, q, d_page_table, max_pages,
                                    cur_meta->d<int>(cur_meta->o_qb_tok0), cur_meta->d<int>(cur_meta->o_qb_len),
                                    cur_meta->d<int>(cur_meta->o_qb_pos0), cur_meta->d<int>(cur_meta->o_qb_ptrow), attn,
                                    n_qblocks, nh_l, nkv_l, d, page_size, stream));
       kernel_launches += 2;
     } else {
-      RET_CUDA(launch_attn_paged(kv_map, (long long)l * kv_rows_per_layer, q, d_page_table, max_pages, ptrow, ctx, attn,
-                                 attn_scratch, n_splits, T, nh_l, nkv_l, d, page_size, stream));
-      kernel_launches += n_splits > 1 ? 3 : 2;
+      // decode: RoPE + KV write live inside the attention kernel (one kernel boundary less per layer)
+      prof_mark(P_ATTN);
+      RET_CUDA(launch_attn_decode_fused(kv_map, (long long)l * kv_rows_per_layer, pool, partial, s_qkv, (long long)T * nqkv_l,
+                                        pos, rope_cos, rope_sin, d_page_table, max_pages, ptrow, ctx, attn, attn_scratch,
+                                        n_splits, T, nh_l, nkv_l, d, page_size, stream));
+      kernel_launches += n_splits > 1 ? 2 : 1;
     }
     int s_o = 1;
     prof_mark(P_OPROJ);

@@ -57,9 +57,33 @@ __device__ __forceinline__ void mma_bf16_16816(float (&c)[4], uint32_t a0, uint3
 // are merged once at the end.  P is rounded to bf16 for the P.V MMA (the usual flash-attention choice).
 // Rows past the context inside a box hold stale (finite) cache contents and get probability 0; the
 // engine zero-fills the pool once so that they can never be NaN.
+// Decode steps fuse the RoPE + KV-write stage into this kernel (rope.qkv != nullptr): the CTA sums the split-K
+// slices of the fused QKV projection for its query heads and -- if the new position falls in its split -- for
+// its kv head, rotates q and k, writes the new K/V row to the page pool for later steps and patches it into
+// the shared-memory tile that TMA fetched.  Because nothing but that one row depends on this step, the K/V
+// stream is started BEFORE griddepcontrol.wait: attention's HBM traffic overlaps the QKV projection's tail.
+struct AttnRope {
+  const float *qkv;          // [S][T][(nh + 2 nkv) * d] fp32 split-K slices, or nullptr: q / pages are ready
+  int n_partial;
+  long long stride;
+  const int *pos;            // [T]
+  const float *cos_t, *sin_t;  // [max_ctx][d/2]
+  uint16_t *kv_base;         // this layer's page pool
+};
+
+__device__ __forceinline__ float4 attn_sum_slices(const float *p, int n, long long stride) {
+  float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 4
+  for (int s = 0; s < n; s++) {
+    const float4 v = *reinterpret_cast<const float4 *>(p + (size_t)s * stride);
+    a.x += v.x; a.y += v.y; a.z += v.z; a.w += v.w;
+  }
+  return a;
+}
+
 template <int D, int G>
 __global__ void __launch_bounds__(kAttnThreads, 2)
-attn_paged_kernel(const __grid_constant__ CUtensorMap kv_map, long long row0, const uint16_t *__restrict__ q,
+attn_paged_kernel(const __grid_constant__ CUtensorMap kv_map, long long row0, const AttnRope rope, const uint16_t *__restrict__ q,
                   const int *__restrict__ page_table, int max_pages, const int *__restrict__ pt_row,
                   const int *__restrict__ ctx_len, uint16_t *__restrict__ out, float *__restrict__ scratch,
                   int n_splits, int T, int n_heads, int n_kv, int page_shift) {
@@ -87,7 +111,10 @@ attn_paged_kernel(const __grid_constant__ CUtensorMap kv_map, long long row0, co
     fence_proxy_async();
   }
   pdl_launch_dependents();
-  pdl_wait();  // q, the page table and this step's K/V rows come from the previous kernels
+  const bool fused = rope.qkv != nullptr;
+  __shared__ __align__(16) uint16_t s_q[G][D];
+  __shared__ __align__(16) uint16_t s_kvnew[2][D];
+  if (!fused) pdl_wait();  // q and this step's K/V rows come from the previous kernels
   __syncthreads();
 
   const int page_size = 1 << page_shift;
@@ -123,13 +150,56 @@ attn_paged_kernel(const __grid_constant__ CUtensorMap kv_map, long long row0, co
       if (s < n_tiles) load_tile(s, s);
   }
 
+  const int new_pos = ctx - 1;                               // the position this decode step appends
+  const bool owner = fused && new_pos >= begin && new_pos < end;  // the split that holds it
+  if (fused) {
+    pdl_wait();  // the QKV projection's slices
+    constexpr int HQ = D / 8;  // float4 rotate-half items per head
+    const int nq = n_heads * D, nk = n_kv * D;
+    const float *base = rope.qkv + (size_t)t * (nq + 2 * nk);
+    const float *cs = rope.cos_t + (size_t)new_pos * (D / 2), *sn = rope.sin_t + (size_t)new_pos * (D / 2);
+    for (int item = threadIdx.x; item < (G + 1) * HQ + D / 4; item += kAttnThreads) {
+      if (item < (G + 1) * HQ) {
+        const bool is_q = item < G * HQ;
+        if (!is_q && !owner) continue;
+        const int hh = is_q ? item / HQ : 0, i = (item % HQ) * 4;
+        const int col = is_q ? (h0 + hh) * D + i : nq + kvh * D + i;
+        const float4 a = attn_sum_slices(base + col, rope.n_partial, rope.stride);
+        const float4 b = attn_sum_slices(base + col + D / 2, rope.n_partial, rope.stride);
+        const float4 c = *reinterpret_cast<const float4 *>(cs + i), sv = *reinterpret_cast<const float4 *>(sn + i);
+        uint2 lo, hi;
+        lo.x = float2_to_bf16x2(a.x * c.x - b.x * sv.x, a.y * c.y - b.y * sv.y);
+        lo.y = float2_to_bf16x2(a.z * c.z - b.z * sv.z, a.w * c.w - b.w * sv.w);
+        hi.x = float2_to_bf16x2(b.x * c.x + a.x * sv.x, b.y * c.y + a.y * sv.y);
+        hi.y = float2_to_bf16x2(b.z * c.z + a.z * sv.z, b.w * c.w + a.w * sv.w);
+        uint16_t *dst = is_q ? s_q[hh] : s_kvnew[0];
+        *reinterpret_cast<uint2 *>(dst + i) = lo;
+        *reinterpret_cast<uint2 *>(dst + D / 2 + i) = hi;
+      } else if (owner) {
+        const int i = (item - (G + 1) * HQ) * 4;
+        const float4 a = attn_sum_slices(base + nq + nk + kvh * D + i, rope.n_partial, rope.stride);
+        uint2 o;
+        o.x = float2_to_bf16x2(a.x, a.y);
+        o.y = float2_to_bf16x2(a.z, a.w);
+        *reinterpret_cast<uint2 *>(s_kvnew[1] + i) = o;
+      }
+    }
+    __syncthreads();
+    if (owner && threadIdx.x < 2 * (D / 8)) {  // the new row goes to the page pool for the steps to come
+      const int kv = threadIdx.x / (D / 8), c = threadIdx.x % (D / 8);
+      const long long page = pt[new_pos >> page_shift];
+      uint16_t *dst = rope.kv_base + ((((size_t)page * 2 + kv) * n_kv + kvh) * page_size + (new_pos & (page_size - 1))) * D + c * 8;
+      *reinterpret_cast<uint4 *>(dst) = *reinterpret_cast<const uint4 *>(s_kvnew[kv] + c * 8);
+    }
+  }
+
   // ---- Q as the A operand: row g = head g (g < G), everything else zero
   uint32_t qa[KS][2];
 #pragma unroll
   for (int ks = 0; ks < KS; ks++) {
     qa[ks][0] = 0u; qa[ks][1] = 0u;
     if (g < G) {
-      const uint16_t *qp = q + ((size_t)t * n_heads + h0 + g) * D + ks * 16 + tq * 2;
+      const uint16_t *qp = fused ? s_q[g] + ks * 16 + tq * 2 : q + ((size_t)t * n_heads + h0 + g) * D + ks * 16 + tq * 2;
       qa[ks][0] = *reinterpret_cast<const uint32_t *>(qp);
       qa[ks][1] = *reinterpret_cast<const uint32_t *>(qp + 8);
     }
@@ -153,6 +223,17 @@ attn_paged_kernel(const __grid_constant__ CUtensorMap kv_map, long long row0, co
     const uint32_t ks_addr = smem_base + stage * Cfg::kStageBytes;
     const uint32_t vs_addr = ks_addr + Cfg::kHalves * Cfg::kHalfBytes;
     const int tile_len = min(kAttnTile, end - (begin + tile * kAttnTile));
+    if (owner && tile == n_tiles - 1) {
+      // the tile TMA fetched predates this step's K/V row: patch it in (same 128B swizzle as the TMA boxes)
+      const int r = new_pos - (begin + tile * kAttnTile);
+      if (threadIdx.x < 2 * (D / 8)) {
+        const int kv = threadIdx.x / (D / 8), c = threadIdx.x % (D / 8);
+        const uint32_t dst = (kv ? vs_addr : ks_addr) + (c >> 3) * Cfg::kHalfBytes + r * 128 + (((c & 7) ^ (r & 7)) << 4);
+        const uint4 v = *reinterpret_cast<const uint4 *>(s_kvnew[kv] + c * 8);
+        asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(dst), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+      }
+      __syncthreads();
+    }
     if (wtok >= tile_len) continue;  // warp-uniform: nothing of this tile belongs to this warp
 
     // ---- S = Q K^T for this warp's 16 tokens (two n-tiles of 8)
@@ -459,7 +540,7 @@ size_t attn_scratch_elems(int T, int n_heads, int d, int n_splits) {
 }
 
 template <int D, int G>
-static cudaError_t attn_launch(const TmaMap &kv_map, long long row0, const uint16_t *q, const int *page_table,
+static cudaError_t attn_launch(const TmaMap &kv_map, long long row0, const AttnRope &rope, const uint16_t *q, const int *page_table,
                                int max_pages, const int *pt_row, const int *ctx, uint16_t *out, float *scratch,
                                int n_splits, int T, int n_heads, int n_kv, int page_shift, cudaStream_t st) {
   dim3 grid(n_splits, n_kv, T);
@@ -469,7 +550,7 @@ static cudaError_t attn_launch(const TmaMap &kv_map, long long row0, const uint1
     attr_set = true;
   }
   DIS_CUDA_TRY(launch_k(attn_paged_kernel<D, G>, grid, dim3(kAttnThreads), AttnCfg<D>::kSmemBytes, st,
-                        *reinterpret_cast<const CUtensorMap *>(&kv_map), row0, q, page_table, max_pages, pt_row, ctx, out,
+                        *reinterpret_cast<const CUtensorMap *>(&kv_map), row0, rope, q, page_table, max_pages, pt_row, ctx, out,
                         scratch, n_splits, T, n_heads, n_kv, page_shift));
   if (n_splits > 1)
     DIS_CUDA_TRY(launch_k(attn_combine_kernel<D>, dim3(n_heads, T), dim3(D), 0, st, (const float *)scratch, out, n_splits, T, n_heads));
@@ -481,9 +562,10 @@ cudaError_t make_kv_map(TmaMap *out, const uint16_t *pool, long long total_rows,
   return make_tma_map_2d(out, pool, (uint64_t)total_rows, (uint64_t)d, (uint32_t)(page_size < kAttnTile ? page_size : kAttnTile));
 }
 
-cudaError_t launch_attn_paged(const TmaMap &kv_map, long long row0, const uint16_t *q, const int *page_table,
-                              int max_pages, const int *pt_row, const int *ctx, uint16_t *out, float *scratch,
-                              int n_splits, int T, int n_heads, int n_kv, int d, int page_size, cudaStream_t st) {
+static cudaError_t attn_dispatch(const TmaMap &kv_map, long long row0, const AttnRope &rope, const uint16_t *q,
+                                 const int *page_table, int max_pages, const int *pt_row, const int *ctx, uint16_t *out,
+                                 float *scratch, int n_splits, int T, int n_heads, int n_kv, int d, int page_size,
+                                 cudaStream_t st) {
   if (T <= 0) return cudaSuccess;
   if (n_kv <= 0 || n_heads % n_kv != 0) { set_last_error("attn_paged: n_heads must be a multiple of n_kv"); return cudaErrorInvalidValue; }
   if (n_splits < 1 || (n_splits > 1 && !scratch)) { set_last_error("attn_paged: n_splits > 1 needs scratch"); return cudaErrorInvalidValue; }
@@ -492,15 +574,34 @@ cudaError_t launch_attn_paged(const TmaMap &kv_map, long long row0, const uint16
   int page_shift = 0;
   while ((1 << page_shift) < page_size) page_shift++;
   const int G = n_heads / n_kv;  // query heads per kv head, all handled by one CTA
-#define DIS_ATTN_CASE(DD, GG)                                                                                  \
-  if (d == DD && G == GG)                                                                                      \
-    return attn_launch<DD, GG>(kv_map, row0, q, page_table, max_pages, pt_row, ctx, out, scratch, n_splits, T, \
+#define DIS_ATTN_CASE(DD, GG)                                                                                        \
+  if (d == DD && G == GG)                                                                                            \
+    return attn_launch<DD, GG>(kv_map, row0, rope, q, page_table, max_pages, pt_row, ctx, out, scratch, n_splits, T, \
                                n_heads, n_kv, page_shift, st);
   DIS_ATTN_CASE(128, 8) DIS_ATTN_CASE(128, 4) DIS_ATTN_CASE(128, 2) DIS_ATTN_CASE(128, 1)
   DIS_ATTN_CASE(64, 8) DIS_ATTN_CASE(64, 4) DIS_ATTN_CASE(64, 2) DIS_ATTN_CASE(64, 1)
 #undef DIS_ATTN_CASE
   set_last_error("attn_paged: head_dim must be 64 or 128 and the GQA group 1, 2, 4 or 8");
   return cudaErrorInvalidValue;
+}
+
+cudaError_t launch_attn_paged(const TmaMap &kv_map, long long row0, const uint16_t *q, const int *page_table,
+                              int max_pages, const int *pt_row, const int *ctx, uint16_t *out, float *scratch,
+                              int n_splits, int T, int n_heads, int n_kv, int d, int page_size, cudaStream_t st) {
+  AttnRope none{};
+  return attn_dispatch(kv_map, row0, none, q, page_table, max_pages, pt_row, ctx, out, scratch, n_splits, T, n_heads, n_kv, d,
+                       page_size, st);
+}
+
+// Decode step: RoPE + KV write of the step's new token (position ctx[t] - 1 == pos[t]) fused in.
+cudaError_t launch_attn_decode_fused(const TmaMap &kv_map, long long row0, uint16_t *kv_layer_base, const float *qkv,
+                                     int n_partial, long long partial_stride, const int *pos, const float *rope_cos,
+                                     const float *rope_sin, const int *page_table, int max_pages, const int *pt_row,
+                                     const int *ctx, uint16_t *out, float *scratch, int n_splits, int T, int n_heads,
+                                     int n_kv, int d, int page_size, cudaStream_t st) {
+  AttnRope r{qkv, n_partial, partial_stride, pos, rope_cos, rope_sin, kv_layer_base};
+  return attn_dispatch(kv_map, row0, r, nullptr, page_table, max_pages, pt_row, ctx, out, scratch, n_splits, T, n_heads, n_kv, d,
+                       page_size, st);
 }
 
 template <int D, int G>

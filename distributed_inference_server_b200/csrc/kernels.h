@@ -61,6 +61,11 @@ cudaError_t launch_attn_paged(const TmaMap &kv_map, long long row0, const uint16
                               int max_pages, const int *pt_row, const int *ctx, uint16_t *out, float *scratch,
                               int n_splits, int T, int n_heads, int n_kv, int d, int page_size, cudaStream_t st);
 
+cudaError_t launch_attn_decode_fused(const TmaMap &kv_map, long long row0, uint16_t *kv_layer_base, const float *qkv,
+                                     int n_partial, long long partial_stride, const int *pos, const float *rope_cos,
+                                     const float *rope_sin, const int *page_table, int max_pages, const int *pt_row,
+                                     const int *ctx, uint16_t *out, float *scratch, int n_splits, int T, int n_heads,
+                                     int n_kv, int d, int page_size, cudaStream_t st);
 cudaError_t launch_attn_prefill(const TmaMap &kv_map, long long row0, const uint16_t *q, const int *page_table,
                                 int max_pages, const int *qb_tok0, const int *qb_len, const int *qb_pos0,
                                 const int *qb_ptrow, uint16_t *out, int n_blocks, int n_heads, int n_kv, int d,
