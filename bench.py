@@ -223,6 +223,8 @@ def run_ours(args):
                               flags=(B.FLAG_NO_GRAPH if args.no_graph else 0) | (B.FLAG_NO_PDL if args.no_pdl else 0)))
     eng.load_synthetic(0)
     eng.finalize()
+    if args.tp_exchange != "auto":
+        os.environ["DIS_TP_EXCHANGE"] = args.tp_exchange
     if world > 1 and not args.nccl_allreduce:
         # peer-memory exchange: all-gather the CUDA IPC handles of the symmetric buffers
         mine = torch.tensor(list(eng.tp_export()), dtype=torch.uint8, device="cuda")
@@ -336,6 +338,10 @@ def run_ours(args):
                 "kv_pages": st.kv_pages_total, "device_mem_gb": st.memory_used / 1e9}
         if args.layers:
             line["config"]["workload"] += f" [REDUCED DEPTH {args.layers} layers: not a valid headline number]"
+        if world > 1:
+            line["config"]["tp_exchange"] = "NCCL all-reduce" if args.nccl_allreduce else (
+                "fused peer-memory exchange (k_tp.cu), " + (args.tp_exchange if args.tp_exchange != "auto" else
+                                                           ("twoshot" if world >= 4 else "oneshot")))
         if args.shard_of > 1:
             line["config"]["workload"] += f" [DIAGNOSTIC: one rank's shard of TP={args.shard_of}, no exchange: not a headline number]"
     eng.close()
@@ -416,6 +422,8 @@ def main():
     ap.add_argument("--ttft-runs", type=int, default=3)
     ap.add_argument("--no-pdl", action="store_true", help="disable programmatic dependent launch (A/B)")
     ap.add_argument("--nccl-allreduce", action="store_true", help="TP: use NCCL instead of the fused peer-memory exchange (A/B)")
+    ap.add_argument("--tp-exchange", choices=["auto", "oneshot", "twoshot"], default="auto",
+                    help="TP: peer-memory exchange kernel (auto = one-shot at TP=2, reduce-scatter + all-gather from TP=4)")
     ap.add_argument("--workload", default="decode", choices=["decode", "serving"], help="serving = BASELINE configs[4]")
     ap.add_argument("--model", default="8b", choices=["8b", "70b"], help="70b = BASELINE configs[3] (TP=8, batch 32)")
     ap.add_argument("--requests", type=int, default=256)

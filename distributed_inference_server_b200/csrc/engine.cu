@@ -209,6 +209,7 @@ int Engine::init(const dis_engine_config *c) {
   }
   seqs.resize((size_t)max_batch);
   use_pdl = !(c->flags & DIS_FLAG_NO_PDL);
+  if (const char *g = getenv("DIS_GEMV_MAX_T")) gemv_max_t = std::max(0, std::min(kGemvMaxT, atoi(g)));
   // ---- tensor parallel communicator
   if (tp_size > 1) {
     std::string err;
@@ -223,7 +224,7 @@ int Engine::init(const dis_engine_config *c) {
     if (tp_size > kTpMaxRanks) return fail(DIS_ERR_INVALID_ARGUMENT, "tp_size > 8");
     ar_cap_rows = std::min(std::max(max_batch, 128), 256);
     const size_t data_b = (size_t)2 * tp_size * ar_cap_rows * m.hidden * sizeof(float);
-    const size_t flags_b = align_up((size_t)2 * tp_size * ar_cap_rows * 4, 256);
+    const size_t flags_b = align_up((size_t)2 * 2 * tp_size * ar_cap_rows * 4, 256);  // two hops
     const size_t cand_b = align_up((size_t)2 * tp_size * ar_cap_rows * 2 * 4, 256);
     sym_bytes = data_b + flags_b + cand_b + 256;
     ENG_CUDA(dev_alloc(&sym, sym_bytes, &bytes_allocated));
@@ -248,7 +249,7 @@ int Engine::tp_import(const uint8_t *handles) {
   if (tp_size <= 1 || !sym || !handles) return fail(DIS_ERR_INVALID_ARGUMENT, "tp_import: engine is not tensor parallel");
   ENG_CUDA(cudaSetDevice(cfg.device));
   const size_t data_b = (size_t)2 * tp_size * ar_cap_rows * m.hidden * sizeof(float);
-  const size_t flags_b = align_up((size_t)2 * tp_size * ar_cap_rows * 4, 256);
+  const size_t flags_b = align_up((size_t)2 * 2 * tp_size * ar_cap_rows * 4, 256);  // two hops
   const size_t cand_b = align_up((size_t)2 * tp_size * ar_cap_rows * 2 * 4, 256);
   for (int r = 0; r < tp_size; r++) {
     uint8_t *base = sym;
@@ -268,6 +269,12 @@ int Engine::tp_import(const uint8_t *handles) {
   peers.rank = tp_rank;
   peers.tp = tp_size;
   peers.cap_rows = ar_cap_rows;
+  // one-shot (tp-1)*T*H*4 bytes and one flag hop, or two-shot 2*(tp-1)/tp*T*H*4 bytes and two hops
+  peers.two_shot = tp_size >= 4 && m.hidden % (4 * tp_size) == 0;
+  if (const char *e = getenv("DIS_TP_EXCHANGE")) {
+    if (!strcmp(e, "oneshot")) peers.two_shot = 0;
+    else if (!strcmp(e, "twoshot") && m.hidden % (4 * tp_size) == 0) peers.two_shot = 1;
+  }
   tp_custom = true;
   return DIS_OK;
 }
@@ -519,7 +526,7 @@ static int tile_index(int T) { const int t = gemm_token_tile(T); return t == 32 
 // out = partial[S][T][N] of  X[T][K] * W[w_row0 : w_row0+N][K]^T
 cudaError_t Engine::linear_partial(const TmaMap *xmaps, const uint16_t *xptr, const TmaMap &wmap, const uint16_t *wptr,
                                    int w_row0, int T, int N, int K, int *split_out) {
-  const bool gemv = (cfg.flags & DIS_FLAG_FORCE_GEMV) || T <= 2;
+  const bool gemv = (cfg.flags & DIS_FLAG_FORCE_GEMV) || T <= gemv_max_t;
   if (gemv) {
     *split_out = 1;
     kernel_launches += (uint64_t)((T + kGemvMaxT - 1) / kGemvMaxT);
@@ -567,7 +574,7 @@ cudaError_t Engine::consume_pending(const float *gain, const int *row_map, int r
 
 cudaError_t Engine::enqueue_layers(int T, int n_splits) {
   const int H = m.hidden, d = m.head_dim;
-  const bool gemv = (cfg.flags & DIS_FLAG_FORCE_GEMV) || T <= 2;
+  const bool gemv = (cfg.flags & DIS_FLAG_FORCE_GEMV) || T <= gemv_max_t;
   const bool fused_ar = tp_size > 1 && tp_custom && T <= ar_cap_rows;  // exchange over peer memory, no NCCL kernel
   const bool pdl_ok = use_pdl && !profiling && (tp_size == 1 || fused_ar);
   pend_ptr = nullptr; pend_count = 0; pend_str = 0; pend_needs_ar = false;
@@ -654,7 +661,7 @@ cudaError_t Engine::enqueue_head(int R, bool all_greedy) {
   const int H = m.hidden;
   prof_mark(P_HEAD_NORM);
   RET_CUDA(consume_pending(final_norm, rowmap_identity ? nullptr : cur_meta->d<int>(cur_meta->o_rowmap), R, last_T));
-  const bool gemv = (cfg.flags & DIS_FLAG_FORCE_GEMV) || R <= 2;
+  const bool gemv = (cfg.flags & DIS_FLAG_FORCE_GEMV) || R <= gemv_max_t;
   prof_mark(P_LM_HEAD);
   if (gemv) { RET_CUDA(launch_gemv(xn, lm_head, logits, R, vocab_l, H, stream)); kernel_launches += (uint64_t)((R + kGemvMaxT - 1) / kGemvMaxT); }
   else { RET_CUDA(launch_gemm_partial(lm_map, xn_map[tile_index(R)], logits, R, vocab_l, H, 0, 1, stream)); kernel_launches++; }

@@ -91,6 +91,7 @@ struct Engine {
   long long kv_rows_per_layer = 0;
   TmaMap kv_map;  // the whole pool as [rows][head_dim]
   bool use_pdl = true;  // programmatic dependent launch between the kernels of a step
+  int gemv_max_t = 1;   // steps of at most this many tokens take the GEMV path; from 2 tokens the tcgen05 path is faster (3.03 vs 4.09 ms per step). DIS_GEMV_MAX_T overrides, for A/B runs
   std::vector<int> free_pages;
   int *d_page_table = nullptr, *h_page_table = nullptr;
   bool pt_dirty = true;

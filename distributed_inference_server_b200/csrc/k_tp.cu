@@ -33,6 +33,13 @@ __device__ __forceinline__ float4 ld_volatile_f4(const float *p) {
   return v;
 }
 
+// explicit fma chain: both exchange kernels must round the sum of squares identically (left to the compiler, the
+// contraction of x*x + y*y + ... differed between them and flipped a bf16 rounding once in ~1e5 elements)
+__device__ __forceinline__ float sumsq4(float ss, const float4 &a) {
+  ss = fmaf(a.x, a.x, ss); ss = fmaf(a.y, a.y, ss); ss = fmaf(a.z, a.z, ss); ss = fmaf(a.w, a.w, ss);
+  return ss;
+}
+
 template <int kThreadsUnused = 0>
 __device__ __forceinline__ float tp_block_sum(float v, float *sm) {
   v = warp_sum(v);
@@ -76,9 +83,7 @@ tp_add_rmsnorm_kernel(TpPeers peers, float *__restrict__ x, const float *__restr
       if (r != me) *reinterpret_cast<float4 *>(peers.data[r] + slot_me + i) = v;  // NVLink store
     if (single) keep = v; else *reinterpret_cast<float4 *>(row + i) = v;
   }
-  __syncthreads();
-  if (threadIdx.x == 0) __threadfence_system();
-  __syncthreads();
+  __syncthreads();  // the release below is cumulative over the stores the barrier ordered before it
   if (threadIdx.x < tp && threadIdx.x != me) st_release_sys(peers.flags[threadIdx.x] + flag_me, epoch);
   // ---- wait for every peer's row (flags live in THIS rank's memory), one polling thread per source
   if (threadIdx.x < tp && threadIdx.x != me) {
@@ -100,12 +105,111 @@ tp_add_rmsnorm_kernel(TpPeers peers, float *__restrict__ x, const float *__restr
     a.x += xv.x; a.y += xv.y; a.z += xv.z; a.w += xv.w;
     *reinterpret_cast<float4 *>(x + (size_t)t * H + i) = a;
     if (single) keep = a; else *reinterpret_cast<float4 *>(row + H + i) = a;
-    ss += a.x * a.x + a.y * a.y + a.z * a.z + a.w * a.w;
+    ss = sumsq4(ss, a);
   }
   ss = tp_block_sum(ss, red);
   const float inv = rsqrtf(ss / (float)H + eps);
   for (int i = threadIdx.x * 4; i < H; i += step) {
     const float4 v = single ? keep : *reinterpret_cast<const float4 *>(row + H + i);
+    const float4 g = *reinterpret_cast<const float4 *>(gain + i);
+    uint2 o;
+    o.x = float2_to_bf16x2(v.x * inv * g.x, v.y * inv * g.y);
+    o.y = float2_to_bf16x2(v.z * inv * g.z, v.w * inv * g.w);
+    *reinterpret_cast<uint2 *>(xn + (size_t)t * H + i) = o;
+  }
+}
+
+// Two-shot variant (tp >= 4): rank o OWNS columns [o*H/tp, (o+1)*H/tp) of every row.
+//   hop 1 (reduce-scatter): each rank sums its split-K slices and pushes, per row, the owner's column block
+//          into the owner's RS area; flag1 per (source, row).
+//   the owner adds the tp contributions IN RANK ORDER and then the residual -- the same additions in the same
+//          order as the one-shot kernel, so both variants produce identical bits --
+//   hop 2 (all-gather): and pushes the finished block of x into every peer's AG area; flag2 per (owner, row).
+//   every rank then holds the full new row and runs the RMSNorm.
+// Bytes sent per rank: 2*(tp-1)/tp*T*H*4 instead of (tp-1)*T*H*4 -- 4x less at tp = 8 -- for one more flag hop.
+//   RS area: data + [parity][source][cap_rows][H/tp]       AG area: data + 2*cap_rows*H + [parity][owner][cap_rows][H/tp]
+//   flag1 = flags + [parity][source][cap_rows]              flag2 = flags + 2*tp*cap_rows + [parity][owner][cap_rows]
+__global__ void __launch_bounds__(1024)
+tp_add_rmsnorm2_kernel(TpPeers peers, float *__restrict__ x, const float *__restrict__ partial, int n_partial,
+                       long long partial_stride, const float *__restrict__ gain, uint16_t *__restrict__ xn,
+                       const uint32_t *__restrict__ step_ptr, uint32_t idx, int parity, int H, float eps) {
+  __shared__ float red[32];
+  extern __shared__ float row[];  // [H]: this rank's own column block, later the whole row when a thread owns > 1 float4
+  const int t = blockIdx.x;
+  pdl_launch_dependents();
+  pdl_wait();
+  const uint32_t epoch = *step_ptr * 256u + idx;
+  const int step = blockDim.x * 4;
+  const bool single = H <= step;
+  const int me = peers.rank, tp = peers.tp, cap = peers.cap_rows;
+  const int Hs = H / tp;
+  const size_t ag_base = (size_t)2 * cap * H;
+  const size_t fl2 = (size_t)2 * tp * cap;
+  const size_t blk_me = (((size_t)parity * tp + me) * cap + t) * (size_t)Hs;  // block written by this rank, row t
+  const size_t flag_me = ((size_t)parity * tp + me) * cap + t;
+
+  // ---- hop 1: split-K reduce, each column block goes to its owner
+  float4 keep = make_float4(0.f, 0.f, 0.f, 0.f);
+  for (int i = threadIdx.x * 4; i < H; i += step) {
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    const float *pp = partial + (size_t)t * H + i;
+#pragma unroll 4
+    for (int s = 0; s < n_partial; s++) {
+      const float4 p = *reinterpret_cast<const float4 *>(pp + (size_t)s * partial_stride);
+      v.x += p.x; v.y += p.y; v.z += p.z; v.w += p.w;
+    }
+    const int owner = i / Hs;
+    if (owner != me) *reinterpret_cast<float4 *>(peers.data[owner] + blk_me + (i - owner * Hs)) = v;  // NVLink store
+    else *reinterpret_cast<float4 *>(row + i) = v;
+  }
+  __syncthreads();
+  if (threadIdx.x < tp && threadIdx.x != me) {
+    st_release_sys(peers.flags[threadIdx.x] + flag_me, epoch);
+    const uint32_t *f = peers.flags[me] + ((size_t)parity * tp + threadIdx.x) * cap + t;
+    while (ld_acquire_sys(f) != epoch) { }
+  }
+  __syncthreads();
+  // ---- owner: sum in rank order, add the residual, hop 2: the finished block goes to everybody
+  for (int i = me * Hs + threadIdx.x * 4; i < (me + 1) * Hs; i += step) {
+    const int j = i - me * Hs;
+    float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int r = 0; r < tp; r++) {
+      float4 v;
+      if (r == me) v = *reinterpret_cast<const float4 *>(row + i);
+      else v = ld_volatile_f4(peers.data[me] + (((size_t)parity * tp + r) * cap + t) * (size_t)Hs + j);
+      a.x += v.x; a.y += v.y; a.z += v.z; a.w += v.w;
+    }
+    const float4 xv = *reinterpret_cast<const float4 *>(x + (size_t)t * H + i);
+    a.x += xv.x; a.y += xv.y; a.z += xv.z; a.w += xv.w;
+    for (int r = 0; r < tp; r++)
+      if (r != me) *reinterpret_cast<float4 *>(peers.data[r] + ag_base + blk_me + j) = a;  // NVLink store
+    *reinterpret_cast<float4 *>(row + i) = a;
+  }
+  __syncthreads();
+  if (threadIdx.x < tp && threadIdx.x != me) {
+    st_release_sys(peers.flags[threadIdx.x] + fl2 + flag_me, epoch);
+    const uint32_t *f = peers.flags[me] + fl2 + ((size_t)parity * tp + threadIdx.x) * cap + t;
+    while (ld_acquire_sys(f) != epoch) { }
+  }
+  __syncthreads();
+  // ---- full row: own block from shared memory, the others from the AG area; RMSNorm
+  float ss = 0.f;
+  for (int i = threadIdx.x * 4; i < H; i += step) {
+    const int owner = i / Hs;
+    float4 a;
+    if (owner == me) a = *reinterpret_cast<const float4 *>(row + i);
+    else {
+      a = ld_volatile_f4(peers.data[me] + ag_base + (((size_t)parity * tp + owner) * cap + t) * (size_t)Hs + (i - owner * Hs));
+      if (!single) *reinterpret_cast<float4 *>(row + i) = a;
+    }
+    *reinterpret_cast<float4 *>(x + (size_t)t * H + i) = a;
+    if (single) keep = a;
+    ss = sumsq4(ss, a);
+  }
+  ss = tp_block_sum(ss, red);
+  const float inv = rsqrtf(ss / (float)H + eps);
+  for (int i = threadIdx.x * 4; i < H; i += step) {
+    const float4 v = single ? keep : *reinterpret_cast<const float4 *>(row + i);
     const float4 g = *reinterpret_cast<const float4 *>(gain + i);
     uint2 o;
     o.x = float2_to_bf16x2(v.x * inv * g.x, v.y * inv * g.y);
@@ -122,6 +226,13 @@ cudaError_t launch_tp_add_rmsnorm(const TpPeers &peers, float *x, const float *p
   if (H % 4 != 0) { set_last_error("tp_add_rmsnorm: H must be a multiple of 4"); return cudaErrorInvalidValue; }
   int threads = (H / 4 + 31) / 32 * 32;
   threads = threads > 1024 ? 1024 : threads;
+  if (peers.two_shot) {
+    if (H % (4 * peers.tp) != 0) { set_last_error("tp_add_rmsnorm: two-shot exchange needs H % (4 * tp) == 0"); return cudaErrorInvalidValue; }
+    const size_t smem2 = (size_t)H * sizeof(float);
+    if (smem2 > 48 * 1024) DIS_CUDA_TRY(cudaFuncSetAttribute(tp_add_rmsnorm2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));
+    return launch_k(tp_add_rmsnorm2_kernel, dim3(T), dim3(threads), smem2, st, peers, x, partial, n_partial, partial_stride,
+                    gain, xn, step_ptr, idx, parity, H, eps);
+  }
   const size_t smem = H <= threads * 4 ? 0 : (size_t)2 * H * sizeof(float);
   if (smem > 48 * 1024) DIS_CUDA_TRY(cudaFuncSetAttribute(tp_add_rmsnorm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   return launch_k(tp_add_rmsnorm_kernel, dim3(T), dim3(threads), smem, st, peers, x, partial, n_partial, partial_stride, gain,

@@ -107,7 +107,9 @@ def test_gemm_silu(T, I, K):
     assert np.abs(host(act) - ref).max() <= BF16_ULP * np.abs(ref).max() * 1.05 + 1e-6
 
 
-@pytest.mark.parametrize("T,N,K", [(1, 256, 128), (2, 201, 352), (4, 512, 4096), (7, 64, 256)])
+@pytest.mark.parametrize("T,N,K", [(1, 256, 128), (2, 201, 352), (4, 512, 4096), (7, 64, 256),
+                                   # several row groups per persistent CTA, ragged N and K tails
+                                   (1, 4096, 4096), (1, 3001, 6152), (2, 1500, 14336), (3, 2501, 520)])
 def test_gemv(T, N, K):
     rng = np.random.default_rng(T + N + K)
     X, W = rand_bf16(rng, (T, K)), rand_bf16(rng, (N, K), 0.05)

@@ -17,6 +17,8 @@ SEED = 21
 
 
 def _rank(rank, world, idq, outq, prompts, n_new, temps, hq, custom):
+    if custom:  # "oneshot" / "twoshot": which peer-memory exchange kernel the engine uses (k_tp.cu)
+        os.environ["DIS_TP_EXCHANGE"] = custom
     from distributed_inference_server_b200 import Engine, InferenceParams, WorkerConfig, shard_plan as SP
     from distributed_inference_server_b200 import binding as B
     from tests._gpu_util import to_engine_shape
@@ -60,14 +62,7 @@ def _rank(rank, world, idq, outq, prompts, n_new, temps, hq, custom):
     e.close()
 
 
-@pytest.mark.skipif(not torch.cuda.is_available() or torch.cuda.device_count() < 2, reason="needs 2 GPUs")
-@pytest.mark.parametrize("custom", [True, False], ids=["peer-memory", "nccl"])
-@pytest.mark.parametrize("sampled", [False, True], ids=["greedy", "sampled"])
-def test_tp2_matches_oracle(sampled, custom):
-    world, n_new = 2, 12
-    rng = np.random.default_rng(2)
-    prompts = [rng.integers(0, SHAPE.vocab, n).tolist() for n in (7, 33, 18)]
-    temps = [0.7, 0.0, 1.1] if sampled else [0.0, 0.0, 0.0]
+def _run(prompts, n_new, temps, custom, world=2):
     ctx = mp.get_context("spawn")
     idq, outq = ctx.Queue(), ctx.Queue()
     hq = [ctx.Queue() for _ in range(world)]
@@ -81,6 +76,25 @@ def test_tp2_matches_oracle(sampled, custom):
     for p in procs:
         p.join(timeout=60)
         assert p.exitcode == 0
+    return res
+
+
+needs2 = pytest.mark.skipif(not torch.cuda.is_available() or torch.cuda.device_count() < 2, reason="needs 2 GPUs")
+
+
+def _prompts():
+    rng = np.random.default_rng(2)
+    return [rng.integers(0, SHAPE.vocab, n).tolist() for n in (7, 33, 18)]
+
+
+@needs2
+@pytest.mark.parametrize("custom", ["oneshot", "twoshot", None], ids=["peer-memory", "peer-memory-twoshot", "nccl"])
+@pytest.mark.parametrize("sampled", [False, True], ids=["greedy", "sampled"])
+def test_tp2_matches_oracle(sampled, custom):
+    n_new = 12
+    prompts = _prompts()
+    temps = [0.7, 0.0, 1.1] if sampled else [0.0, 0.0, 0.0]
+    res = _run(prompts, n_new, temps, custom)
     assert res[0][0] == res[1][0]                       # every rank yields the same tokens
     assert np.array_equal(res[0][1], res[1][1])         # and the same gathered logits
     ref = O.Oracle(SHAPE, act_round=False); ref.fill_synthetic(SEED, True)
@@ -94,3 +108,19 @@ def test_tp2_matches_oracle(sampled, custom):
             if res[0][0][b] != w["tokens"][b]:
                 i = next(k for k in range(n_new) if res[0][0][b][k] != w["tokens"][b][k])
                 assert w["margins"][b, i] <= 5e-3 * np.abs(w["logits"][b, i]).max(), (b, i)
+
+
+@needs2
+def test_twoshot_exchange_is_bit_identical_to_oneshot():
+    """Both exchange kernels add the same contributions in the same (rank) order, then the residual: the logits
+    and the greedy tokens must agree bit for bit."""
+    prompts = _prompts()
+    a = _run(prompts, 24, [0.0] * 3, "oneshot")
+    a2 = _run(prompts, 24, [0.0] * 3, "oneshot")
+    assert a[0][0] == a2[0][0] and np.array_equal(a[0][1], a2[0][1]), "the one-shot exchange is not run-to-run deterministic"
+    b = _run(prompts, 24, [0.0] * 3, "twoshot")
+    b2 = _run(prompts, 24, [0.0] * 3, "twoshot")
+    assert b[0][0] == b2[0][0] and np.array_equal(b[0][1], b2[0][1]), "the two-shot exchange is not run-to-run deterministic"
+    diff = np.abs(a[0][1] - b[0][1])
+    assert np.array_equal(a[0][1], b[0][1]), (float(diff.max()), int((diff > 0).sum()), diff.size)
+    assert a[0][0] == b[0][0]
