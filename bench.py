@@ -341,7 +341,8 @@ def run_ours(args):
         if world > 1:
             line["config"]["tp_exchange"] = "NCCL all-reduce" if args.nccl_allreduce else (
                 "fused peer-memory exchange (k_tp.cu), " + (args.tp_exchange if args.tp_exchange != "auto" else
-                                                           ("twoshot" if world >= 4 else "oneshot")))
+                                                           ("twoshot" if world >= 4 and (world - 1) * batch * shape.hidden * 4 >= 5 << 20
+                                                            else "oneshot")))
         if args.shard_of > 1:
             line["config"]["workload"] += f" [DIAGNOSTIC: one rank's shard of TP={args.shard_of}, no exchange: not a headline number]"
     eng.close()

@@ -270,7 +270,11 @@ int Engine::tp_import(const uint8_t *handles) {
   peers.tp = tp_size;
   peers.cap_rows = ar_cap_rows;
   // one-shot (tp-1)*T*H*4 bytes and one flag hop, or two-shot 2*(tp-1)/tp*T*H*4 bytes and two hops
-  peers.two_shot = tp_size >= 4 && m.hidden % (4 * tp_size) == 0;
+  // measured at batch 64, H = 4096: TP=4 (3 MB per rank and exchange) one-shot 2.80 vs two-shot 3.00 ms per step;
+  // TP=8 (7 MB) one-shot 2.88 vs two-shot 2.67 ms -- the second flag hop costs ~3 us, the bytes ~1 us per MB.
+  // The choice is fixed per engine (the two kernels lay the symmetric buffer out differently).
+  const size_t oneshot_bytes = (size_t)(tp_size - 1) * max_batch * m.hidden * sizeof(float);
+  peers.two_shot = tp_size >= 4 && m.hidden % (4 * tp_size) == 0 && oneshot_bytes >= ((size_t)5 << 20);
   if (const char *e = getenv("DIS_TP_EXCHANGE")) {
     if (!strcmp(e, "oneshot")) peers.two_shot = 0;
     else if (!strcmp(e, "twoshot") && m.hidden % (4 * tp_size) == 0) peers.two_shot = 1;
