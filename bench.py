@@ -407,6 +407,57 @@ def run_serving(args):
     return 0
 
 
+def run_prefix(args):
+    """Row f2 (prefix KV reuse): time to first token of one request on an idle engine, cold against a request whose
+    leading tokens are already in the page pool (a shared system prompt).  Not a headline number: it shows what
+    DIS_FLAG_PREFIX_CACHE buys; the decode bench runs with the cache off so that nothing is ever skipped there."""
+    import torch
+    from distributed_inference_server_b200 import Engine, InferenceParams, LLAMA3_8B, ModelShape, WorkerConfig
+    from distributed_inference_server_b200 import binding as B
+    torch.cuda.set_device(0)
+    shape = LLAMA3_8B
+    if args.layers:
+        shape = ModelShape(shape.vocab, shape.hidden, args.layers, shape.n_heads, shape.n_kv_heads, shape.head_dim,
+                           shape.inter, shape.max_ctx, shape.rope_theta, shape.rms_eps)
+    page, runs = 64, 7
+    rng = np.random.default_rng(3)
+    eng = Engine(WorkerConfig(shape, device=0, max_batch=4, max_step_tokens=8192, page_size=page, kv_pages=1024,
+                              context_size=8192, stream=torch.cuda.current_stream().cuda_stream, flags=B.FLAG_PREFIX_CACHE))
+    eng.load_synthetic(0); eng.finalize()
+    P = InferenceParams(max_tokens=4, temperature=0.0)
+    out = {}
+    for total, shared in ((512, 448), (2048, 1920), (8000, 7680)):
+        def ttft(prompt):
+            s = eng.seq_add(prompt, P)
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            eng.prefill([s])
+            torch.cuda.synchronize()
+            dt = (time.perf_counter() - t0) * 1e3
+            eng.seq_remove(s)
+            return dt
+        system = rng.integers(0, shape.vocab, shared).tolist()
+        cold, hit = [], []
+        for _ in range(runs):
+            cold.append(ttft(rng.integers(0, shape.vocab, total).tolist()))          # nothing in common with anything cached
+        ttft(system + rng.integers(0, shape.vocab, total - shared).tolist())         # registers the shared prefix
+        before = eng.prefix_stats()["hit_tokens"]
+        for _ in range(runs):
+            hit.append(ttft(system + rng.integers(0, shape.vocab, total - shared).tolist()))
+        reused = (eng.prefix_stats()["hit_tokens"] - before) // runs
+        out[f"{total}"] = {"prompt_tokens": total, "shared_prefix_tokens": shared, "reused_tokens_per_request": int(reused),
+                           "ttft_cold_ms_p50": statistics.median(cold), "ttft_prefix_hit_ms_p50": statistics.median(hit)}
+    st = eng.prefix_stats()
+    line = {"metric": "TTFT with prefix KV reuse", "value": out["2048"]["ttft_prefix_hit_ms_p50"], "unit": "ms", "n_gpus": 1,
+            "higher_is_better": False, "dtype": "bf16", "data": "synthetic",
+            "config": {"workload": "Llama-3-8B bf16, one request on an idle engine, DIS_FLAG_PREFIX_CACHE, page size 64"
+                                   + (f" [REDUCED DEPTH {args.layers} layers]" if args.layers else "")},
+            "by_prompt_length": out, "prefix_stats": st, "gpu_launches": int(eng.status().kernel_launches)}
+    print(json.dumps(line))
+    eng.close()
+    return 0
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -425,7 +476,7 @@ def main():
     ap.add_argument("--nccl-allreduce", action="store_true", help="TP: use NCCL instead of the fused peer-memory exchange (A/B)")
     ap.add_argument("--tp-exchange", choices=["auto", "oneshot", "twoshot"], default="auto",
                     help="TP: peer-memory exchange kernel (auto = one-shot at TP=2, reduce-scatter + all-gather from TP=4)")
-    ap.add_argument("--workload", default="decode", choices=["decode", "serving"], help="serving = BASELINE configs[4]")
+    ap.add_argument("--workload", default="decode", choices=["decode", "serving", "prefix"], help="serving = BASELINE configs[4]; prefix = TTFT with prefix KV reuse (row f2)")
     ap.add_argument("--model", default="8b", choices=["8b", "70b"], help="70b = BASELINE configs[3] (TP=8, batch 32)")
     ap.add_argument("--requests", type=int, default=256)
     ap.add_argument("--shard-of", type=int, default=1, help="diagnostic: run one rank's shard of a TP=N model on one GPU, no exchange")
@@ -433,6 +484,8 @@ def main():
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
+    if args.workload == "prefix":
+        return run_prefix(args)
     if args.workload == "serving":
         return run_serving(args)
     return run_ours(args)

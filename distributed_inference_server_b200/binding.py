@@ -16,7 +16,7 @@ FINISH_NONE, FINISH_STOP, FINISH_LENGTH, FINISH_STOP_SEQUENCE, FINISH_FAILED = r
 (T_EMBED, T_ATTN_NORM, T_WQ, T_WK, T_WV, T_WO, T_MLP_NORM, T_WGATE, T_WUP, T_WDOWN, T_FINAL_NORM,
  T_LM_HEAD) = range(12)
 F32, BF16 = 0, 1
-FLAG_NO_GRAPH, FLAG_FORCE_GEMV, FLAG_NO_PDL = 1, 2, 4
+FLAG_NO_GRAPH, FLAG_FORCE_GEMV, FLAG_NO_PDL, FLAG_PREFIX_CACHE = 1, 2, 4, 8
 PROF_CLASSES = ("norm", "qkv", "rope", "attn", "oproj", "gateup", "down", "allreduce", "head_norm", "lm_head",
                 "sample")
 
@@ -56,6 +56,11 @@ class QueueConfig(C.Structure):
 
 class QueueDepth(C.Structure):
     _fields_ = [(n, C.c_int32) for n in ("high", "normal", "low", "total", "accepting", "active")]
+
+
+class PrefixStats(C.Structure):
+    _fields_ = [(n, C.c_int64) for n in ("cached_pages", "evictable_pages", "free_pages")] + \
+               [(n, C.c_uint64) for n in ("lookups", "hits", "lookup_tokens", "hit_tokens", "evictions")]
 
 
 class ServingEvent(C.Structure):
@@ -101,6 +106,13 @@ PROTOTYPES = {
     "dis_serving_step_at": (C.c_int, [vp, C.c_double, C.POINTER(ServingEvent), C.c_int32, i32p]),
     "dis_serving_depth": (C.c_int, [vp, C.POINTER(QueueDepth)]),
     "dis_serving_debug_pop": (C.c_int, [vp, C.c_int32, vp, i32p]),
+    "dis_engine_prefix_stats": (C.c_int, [vp, C.POINTER(PrefixStats)]),
+    "dis_prefix_index_create": (C.c_int, [C.c_int32, C.c_int64, C.POINTER(vp)]),
+    "dis_prefix_index_destroy": (C.c_int, [vp]),
+    "dis_prefix_index_admit": (C.c_int, [vp, vp, C.c_int32, vp, C.c_int32, i32p, i32p]),
+    "dis_prefix_index_commit": (C.c_int, [vp, vp, C.c_int32, vp, C.c_int32]),
+    "dis_prefix_index_release": (C.c_int, [vp, vp, C.c_int32]),
+    "dis_prefix_index_stats": (C.c_int, [vp, C.POINTER(PrefixStats)]),
     "dis_k_add_rmsnorm": (C.c_int, [vp, vp, vp, vp, C.c_int32, C.c_int64, vp, vp, vp, C.c_int32, C.c_int32,
                                     C.c_float, vp]),
     "dis_k_gemm": (C.c_int, [vp, vp, vp, C.c_int32, C.c_int32, C.c_int32, C.c_int32, vp]),

@@ -96,6 +96,11 @@ int dis_engine_status(dis_engine *e, dis_worker_status *out) {
   LOCKED(e);
   return e->eng.status(out);
 }
+int dis_engine_prefix_stats(dis_engine *e, dis_prefix_stats *out) {
+  if (int rc = guard_null(e)) return rc;
+  LOCKED(e);
+  return e->eng.prefix_stats(out);
+}
 int dis_engine_model_info(dis_engine *e, dis_model_config *out) {
   if (int rc = guard_null(e)) return rc;
   if (!out) return DIS_ERR_INVALID_ARGUMENT;

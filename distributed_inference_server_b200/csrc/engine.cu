@@ -201,8 +201,7 @@ int Engine::init(const dis_engine_config *c) {
     ENG_CUDA(cudaMemset(kv_pool, 0, kv_layer_stride * L * sizeof(uint16_t)));
     kv_rows_per_layer = (long long)n_pages * 2 * nkv_l * page_size;
     ENG_CUDA(make_kv_map(&kv_map, kv_pool, kv_rows_per_layer * (long long)L, m.head_dim, page_size));
-    free_pages.resize((size_t)n_pages);
-    for (int64_t i = 0; i < n_pages; i++) free_pages[(size_t)i] = (int)(n_pages - 1 - i);
+    pages_ix.init(page_size, n_pages, (c->flags & DIS_FLAG_PREFIX_CACHE) != 0);
     ENG_CUDA(dev_alloc(&d_page_table, (size_t)max_batch * max_pages, &bytes_allocated));
     ENG_CUDA(cudaMallocHost(reinterpret_cast<void **>(&h_page_table), (size_t)max_batch * max_pages * sizeof(int)));
     memset(h_page_table, 0, (size_t)max_batch * max_pages * sizeof(int));
@@ -433,10 +432,10 @@ int Engine::finalize() {
 bool Engine::ensure_pages(Sequence &s, int slot, int n_tokens) {
   const int need = (n_tokens + page_size - 1) / page_size;
   if (need > max_pages) return false;
+  if (need - (int)s.pages.size() > pages_ix.available()) return false;  // nothing is evicted for a request that cannot be admitted
   while ((int)s.pages.size() < need) {
-    if (free_pages.empty()) return false;
-    const int p = free_pages.back();
-    free_pages.pop_back();
+    int p;
+    if (!pages_ix.alloc(&p)) return false;
     h_page_table[(size_t)slot * max_pages + s.pages.size()] = p;
     s.pages.push_back(p);
     pt_dirty = true;
@@ -445,7 +444,7 @@ bool Engine::ensure_pages(Sequence &s, int slot, int n_tokens) {
 }
 
 void Engine::release_pages(Sequence &s) {
-  for (int p : s.pages) free_pages.push_back(p);
+  pages_ix.release(s.pages);
   s.pages.clear();
 }
 
@@ -463,6 +462,12 @@ int Engine::seq_add(const uint32_t *prompt, int n, const dis_sampling_params *p,
   if (slot < 0) return fail(DIS_ERR_OUT_OF_MEMORY, "seq_add: all sequence slots are in use");
   Sequence &s = seqs[(size_t)slot];
   s = Sequence();
+  // prefix reuse (design.md:396 get_prefix, Property 9): the longest registered prefix, in whole pages, is mapped
+  // into this sequence's page table; prefill starts behind it
+  const int hit = pages_ix.match(prompt, n, &s.pages);
+  for (int i = 0; i < hit; i++) h_page_table[(size_t)slot * max_pages + i] = s.pages[(size_t)i];
+  if (hit) pt_dirty = true;
+  s.cached = hit * page_size;
   if (!ensure_pages(s, slot, n + 1)) { release_pages(s); return fail(DIS_ERR_OUT_OF_MEMORY, "seq_add: out of KV pages"); }
   s.used = true;
   s.prompt.assign(prompt, prompt + n);
@@ -482,8 +487,17 @@ int Engine::seq_add(const uint32_t *prompt, int n, const dis_sampling_params *p,
 
 int Engine::seq_remove(int slot) {
   if (slot < 0 || slot >= max_batch || !seqs[(size_t)slot].used) return fail(DIS_ERR_INVALID_ARGUMENT, "seq_remove: no such sequence");
-  release_pages(seqs[(size_t)slot]);
-  seqs[(size_t)slot] = Sequence();
+  Sequence &s = seqs[(size_t)slot];
+  if (pages_ix.enabled() && s.prefilled) {
+    // what this sequence generated becomes reusable too (a follow-up turn that quotes it): tokens whose K/V are
+    // in the cache = prompt + all sampled tokens but the last
+    std::vector<uint32_t> toks(s.prompt);
+    toks.insert(toks.end(), s.gen.begin(), s.gen.end());
+    if ((int)toks.size() > s.len) toks.resize((size_t)s.len);
+    pages_ix.commit(toks.data(), (int)toks.size() / page_size, s.pages);
+  }
+  release_pages(s);
+  s = Sequence();
   return DIS_OK;
 }
 
@@ -491,6 +505,7 @@ void Engine::finish_check(Sequence &s, uint32_t tok) {
   s.generated++;
   tokens_generated++;
   s.last_token = tok;
+  if (pages_ix.enabled()) s.gen.push_back(tok);
   s.tail.push_back(tok);
   size_t longest = 0;
   for (auto &st : s.stop) longest = std::max(longest, st.size());
@@ -729,7 +744,7 @@ int Engine::prefill(int n, const int *slots, uint32_t *out_tokens, int *out_fini
   cur_meta = &meta_pre;
   struct MetaReset { Engine *e; ~MetaReset() { e->cur_meta = &e->meta_dec; e->n_qblocks = 0; } } meta_reset{this};
   // flatten (sequence, position) pairs and cut them into chunks of at most cap_tokens
-  int si = 0, sp = 0;  // next sequence index / position inside it
+  int si = 0, sp = seqs[(size_t)slots[0]].cached;  // next sequence index / position inside it (behind its cached prefix)
   bool all_greedy = true;
   for (int i = 0; i < n; i++) all_greedy = all_greedy && seqs[(size_t)slots[i]].temperature <= 0.f;
   while (si < n) {
@@ -764,7 +779,7 @@ int Engine::prefill(int n, const int *slots, uint32_t *out_tokens, int *out_fini
         owners.push_back(si);
         R++;
         si++;
-        sp = 0;
+        sp = si < n ? seqs[(size_t)slots[si]].cached : 0;
       }
     }
     n_qblocks = QB;
@@ -789,6 +804,7 @@ int Engine::prefill(int n, const int *slots, uint32_t *out_tokens, int *out_fini
     Sequence &s = seqs[(size_t)slots[i]];
     s.len = (int)s.prompt.size();
     s.prefilled = true;
+    pages_ix.commit(s.prompt.data(), s.len / page_size, s.pages);  // full prompt pages become reusable (no-op when off)
     finish_check(s, out_tokens[i]);
     out_finish[i] = s.finish;
   }
@@ -932,6 +948,14 @@ int Engine::last_logits_host(float *host, int rows) {
   return DIS_OK;
 }
 
+void prefix_fill_stats(const PrefixStats &s, dis_prefix_stats *o);  // prefix.cpp
+
+int Engine::prefix_stats(dis_prefix_stats *o) {
+  if (!o) return fail(DIS_ERR_INVALID_ARGUMENT, "prefix_stats: null argument");
+  prefix_fill_stats(pages_ix.stats(), o);
+  return DIS_OK;
+}
+
 int Engine::status(dis_worker_status *o) {
   if (!o) return fail(DIS_ERR_INVALID_ARGUMENT, "status: null output");
   memset(o, 0, sizeof(*o));
@@ -943,7 +967,7 @@ int Engine::status(dis_worker_status *o) {
   size_t free_b = 0, total_b = 0;
   if (cudaSetDevice(cfg.device) == cudaSuccess && cudaMemGetInfo(&free_b, &total_b) == cudaSuccess) o->memory_available = free_b;
   o->kv_pages_total = n_pages;
-  o->kv_pages_free = (int64_t)free_pages.size();
+  o->kv_pages_free = pages_ix.available();  // free + registered pages that no live sequence maps
   o->tokens_generated = tokens_generated;
   o->last_step_ms = last_step_ms;
   o->kernel_launches = kernel_launches;

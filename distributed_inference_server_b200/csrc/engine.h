@@ -8,6 +8,7 @@
 
 #include "../../include/dis_engine.h"
 #include "kernels.h"
+#include "prefix_index.hpp"
 #include "ptx.cuh"
 
 namespace dis {
@@ -30,6 +31,8 @@ struct Sequence {
   bool used = false;
   bool prefilled = false;
   std::vector<uint32_t> prompt;
+  std::vector<uint32_t> gen;  // sampled tokens (kept only while the prefix cache is on)
+  int cached = 0;          // leading prompt tokens whose K/V came from the prefix cache
   int len = 0;             // tokens whose K/V are in the cache
   uint32_t last_token = 0;  // sampled, not yet in the cache
   int generated = 0;
@@ -92,7 +95,7 @@ struct Engine {
   TmaMap kv_map;  // the whole pool as [rows][head_dim]
   bool use_pdl = true;  // programmatic dependent launch between the kernels of a step
   int gemv_max_t = 1;   // steps of at most this many tokens take the GEMV path; from 2 tokens the tcgen05 path is faster (3.03 vs 4.09 ms per step). DIS_GEMV_MAX_T overrides, for A/B runs
-  std::vector<int> free_pages;
+  PrefixIndex pages_ix;  // page allocator; with DIS_FLAG_PREFIX_CACHE also the prefix index (row f2)
   int *d_page_table = nullptr, *h_page_table = nullptr;
   bool pt_dirty = true;
   float *rope_cos = nullptr, *rope_sin = nullptr;
@@ -147,6 +150,7 @@ struct Engine {
   int decode(int n, const int *slots, uint32_t *out_tokens, int *out_finish);
   int last_logits_host(float *host, int rows);
   int status(dis_worker_status *out);
+  int prefix_stats(dis_prefix_stats *out);
 
   // internals
   bool ensure_pages(Sequence &s, int slot, int n_tokens);

@@ -264,6 +264,14 @@ class Engine:
                             s.kv_pages_free, s.tokens_generated, s.last_step_ms, s.kernel_launches)
 
 
+    def prefix_stats(self) -> dict:
+        """CacheStats of the prefix cache (design.md:404-411): pages registered / evictable / free, requests and
+        tokens looked up and reused, evictions."""
+        s = B.PrefixStats()
+        self._check(self.lib.dis_engine_prefix_stats(self.h, C.byref(s)))
+        return {n: int(getattr(s, n)) for n, _ in B.PrefixStats._fields_}
+
+
 def _sampling(p: InferenceParams):
     sp = B.SamplingParams()
     sp.max_tokens, sp.temperature, sp.top_p, sp.seed = int(p.max_tokens), float(p.temperature), float(p.top_p), int(p.seed)

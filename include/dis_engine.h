@@ -75,6 +75,8 @@ typedef struct dis_model_config {
 #define DIS_FLAG_NO_GRAPH 1u   /* do not capture the decode step in a CUDA graph */
 #define DIS_FLAG_FORCE_GEMV 2u /* debugging: run every projection through the GEMV kernel */
 #define DIS_FLAG_NO_PDL 4u     /* launch the kernels of a step without programmatic dependent launch */
+#define DIS_FLAG_PREFIX_CACHE 8u /* keep the full KV pages of finished prompts and map them into later requests that start
+                                   with the same tokens (KVCacheManager::get_prefix, design.md:396; Property 9) */
 typedef struct dis_engine_config {
   dis_model_config model;
   int32_t device;              /* CUDA ordinal (WorkerConfig.gpu_layers has no meaning here) */
@@ -233,6 +235,40 @@ DIS_API int dis_serving_step(dis_serving *s, dis_serving_event *events, int32_t 
 DIS_API int dis_serving_step_at(dis_serving *s, double now_s, dis_serving_event *events, int32_t cap, int32_t *n_events);
 DIS_API int dis_serving_depth(dis_serving *s, dis_queue_depth *out);
 DIS_API int dis_serving_debug_pop(dis_serving *s, int32_t max, uint64_t *ids, int32_t *n);
+
+/* ---- prefix KV reuse -------------------------------------------------------- *
+ * The spec's KVCacheManager (design.md:363-413) caches K/V per token sequence as host Vec<f32> and hands the
+ * longest cached prefix back through get_prefix (Property 9, design.md:734-738), evicting least-recently-used
+ * entries under memory pressure (Property 10).  Here the cache is the device page pool itself: with
+ * DIS_FLAG_PREFIX_CACHE the full pages of a prefilled prompt (and, when the sequence is removed, of what it
+ * generated) stay registered under a hash of the tokens up to and including the page; dis_engine_seq_add maps
+ * the longest registered prefix into the new sequence and dis_engine_prefill computes only the remaining
+ * tokens.  Pages nobody maps are handed back to the allocator in LRU order when it runs dry.
+ * dis_prefix_stats mirrors CacheStats (design.md:404-411). */
+typedef struct dis_prefix_stats {
+  int64_t cached_pages;    /* CacheStats.entries: registered pages (mapped or not) */
+  int64_t evictable_pages; /* registered, mapped by no live sequence */
+  int64_t free_pages;      /* never registered or already evicted */
+  uint64_t lookups;        /* requests looked up */
+  uint64_t hits;           /* CacheStats.hit_count: requests that reused at least one page (miss_count = lookups - hits) */
+  uint64_t lookup_tokens;  /* prompt tokens looked up */
+  uint64_t hit_tokens;     /* prompt tokens whose K/V were reused instead of computed */
+  uint64_t evictions;      /* CacheStats.eviction_count */
+} dis_prefix_stats;
+DIS_API int dis_engine_prefix_stats(dis_engine *e, dis_prefix_stats *out);
+
+/* The same page index without an engine, so that the admission / reuse / eviction rules can be tested
+ * without a GPU: admit = longest-prefix match + allocation of the remaining pages for n_tokens + 1 positions
+ * (all or nothing), commit = register the full pages, release = the sequence is gone. */
+typedef struct dis_prefix_index dis_prefix_index;
+DIS_API int dis_prefix_index_create(int32_t page_size, int64_t n_pages, dis_prefix_index **out);
+DIS_API int dis_prefix_index_destroy(dis_prefix_index *ix);
+DIS_API int dis_prefix_index_admit(dis_prefix_index *ix, const uint32_t *tokens, int32_t n_tokens, int32_t *pages,
+                                   int32_t pages_cap, int32_t *n_pages, int32_t *matched_tokens);
+DIS_API int dis_prefix_index_commit(dis_prefix_index *ix, const uint32_t *tokens, int32_t n_tokens,
+                                    const int32_t *pages, int32_t n_pages);
+DIS_API int dis_prefix_index_release(dis_prefix_index *ix, const int32_t *pages, int32_t n_pages);
+DIS_API int dis_prefix_index_stats(dis_prefix_index *ix, dis_prefix_stats *out);
 
 /* ---- kernel-level entry points ------------------------------------------------------------------ *
  * One per hand-written kernel, taking DEVICE pointers and a cudaStream_t (NULL = default stream).
