@@ -208,6 +208,7 @@ int Engine::init(const dis_engine_config *c) {
   }
   seqs.resize((size_t)max_batch);
   use_pdl = !(c->flags & DIS_FLAG_NO_PDL);
+  if (const char *g = getenv("DIS_GEMM_PERSIST")) use_persist = atoi(g) != 0;
   if (const char *g = getenv("DIS_GEMV_MAX_T")) gemv_max_t = std::max(0, std::min(kGemvMaxT, atoi(g)));
   // ---- tensor parallel communicator
   if (tp_size > 1) {
@@ -555,6 +556,7 @@ cudaError_t Engine::linear_partial(const TmaMap *xmaps, const uint16_t *xptr, co
   if ((size_t)s * T * N > partial_elems) s = 1;
   *split_out = s;
   kernel_launches++;
+  if (s == 1 && use_persist && gemm_use_persist(T, N, false)) return launch_gemm_persist_partial(wmap, xmaps[3], partial, T, N, K, w_row0, stream);
   return launch_gemm_partial(wmap, xmaps[tile_index(T)], partial, T, N, K, w_row0, s, stream);
 }
 
@@ -651,6 +653,9 @@ cudaError_t Engine::enqueue_layers(int T, int n_splits) {
     if (gemv) {
       RET_CUDA(launch_gemv_silu(xn, wgu + (size_t)l * 2 * inter_l * H, act, T, inter_l, H, stream));
       kernel_launches += (uint64_t)((T + kGemvMaxT - 1) / kGemvMaxT);
+    } else if (use_persist && gemm_use_persist(T, inter_l, true)) {
+      RET_CUDA(launch_gemm_persist_silu(wgu_map128, xn_map[2], act, T, inter_l, H, l * 2 * inter_l, stream));
+      kernel_launches++;
     } else if (gemm_token_tile(T) >= 128) {
       // prefill is tensor-bound: full 128-row tiles (the balanced, shorter tiles would idle MMA rows)
       RET_CUDA(launch_gemm_silu(wgu_map128, xn_map[tile_index(T)], act, T, inter_l, H, l * 2 * inter_l, 128, stream));

@@ -94,6 +94,7 @@ struct Engine {
   long long kv_rows_per_layer = 0;
   TmaMap kv_map;  // the whole pool as [rows][head_dim]
   bool use_pdl = true;  // programmatic dependent launch between the kernels of a step
+  bool use_persist = true;  // prefill-sized projections through the persistent GEMM (DIS_GEMM_PERSIST=0: A/B runs)
   int gemv_max_t = 1;   // steps of at most this many tokens take the GEMV path; from 2 tokens the tcgen05 path is faster (3.03 vs 4.09 ms per step). DIS_GEMV_MAX_T overrides, for A/B runs
   PrefixIndex pages_ix;  // page allocator; with DIS_FLAG_PREFIX_CACHE also the prefix index (row f2)
   int *d_page_table = nullptr, *h_page_table = nullptr;

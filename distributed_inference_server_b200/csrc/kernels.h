@@ -82,6 +82,12 @@ cudaError_t launch_gemm_partial(const TmaMap &w_map, const TmaMap &x_map, float 
 // act[T][I] = bf16(silu(gate) * up); gate rows at w_row0, up rows at w_row0 + I.  w_map's box height must be
 // tile_rows = gemm_pick_tile_rows(I).
 int gemm_pick_tile_rows(int N);
+// k_gemm_persist.cu : persistent, TMEM-double-buffered variant for prefill-sized T (no split-K)
+bool gemm_use_persist(int T, int N, bool dual);
+cudaError_t launch_gemm_persist_partial(const TmaMap &w_map128, const TmaMap &x_map256, float *out, int T, int N, int K,
+                                        int w_row0, cudaStream_t st);
+cudaError_t launch_gemm_persist_silu(const TmaMap &w_map128, const TmaMap &x_map128, uint16_t *act, int T, int I, int K,
+                                     int w_row0, cudaStream_t st);
 cudaError_t launch_gemm_silu(const TmaMap &w_map, const TmaMap &x_map, uint16_t *act, int T, int I, int K,
                              int w_row0, int tile_rows, cudaStream_t st);
 int gemm_pick_split_k(int T, int N, int K);

@@ -72,7 +72,9 @@ def test_add_rmsnorm_embedding_and_rowmap():
 
 
 GEMM_SHAPES = [(32, 256, 128), (5, 200, 352), (64, 384, 512), (17, 1000, 1024), (128, 512, 256), (300, 640, 192),
-               (32, 4096, 4096)]
+               (32, 4096, 4096),
+               # prefill-sized: the persistent, TMEM-double-buffered kernel (>= 2 tiles per SM), ragged T / N / K too
+               (1024, 9600, 576), (1000, 9500, 320), (4096, 2500, 128)]
 
 
 @pytest.mark.parametrize("T,N,K", GEMM_SHAPES)
@@ -96,7 +98,8 @@ def test_gemm_rejects_empty_split():
     assert lib().dis_k_gemm(ptr(X), ptr(W), ptr(out), 8, 128, 576, 4, None) != 0  # 9 k-blocks / 4 -> empty slice
 
 
-@pytest.mark.parametrize("T,I,K", [(32, 256, 128), (9, 200, 320), (64, 512, 256), (128, 384, 128), (32, 14336, 4096)])
+@pytest.mark.parametrize("T,I,K", [(32, 256, 128), (9, 200, 320), (64, 512, 256), (128, 384, 128), (32, 14336, 4096),
+                                   (1024, 4800, 192), (1000, 4792, 320), (2048, 2432, 64)])  # persistent dual kernel
 def test_gemm_silu(T, I, K):
     rng = np.random.default_rng(T + I + K)
     X, Wgu = rand_bf16(rng, (T, K)), rand_bf16(rng, (2 * I, K), 0.05)
