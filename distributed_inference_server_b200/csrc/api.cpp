@@ -152,8 +152,8 @@ static int gemm_common(const uint16_t *X, const uint16_t *W, float *out, uint16_
   if (int rc = need_gpu()) return rc;
   dis::TmaMap wm, xm;
   const bool persist = split <= 1 && dis::gemm_use_persist(T, N, silu);  // the engine's choice for this shape
-  const int bn = persist ? (silu ? 128 : 256) : dis::gemm_token_tile(T);
-  const int rows = silu && !persist ? dis::gemm_pick_tile_rows(N) : 128;
+  const int bn = persist ? 256 : dis::gemm_token_tile(T);
+  const int rows = silu ? (persist ? 64 : dis::gemm_pick_tile_rows(N)) : 128;
   cudaError_t e = dis::make_tma_map_2d(&wm, W, (uint64_t)(silu ? 2 * N : N), (uint64_t)K, (uint32_t)rows);
   if (e == cudaSuccess) e = dis::make_tma_map_2d(&xm, X, (uint64_t)T, (uint64_t)K, (uint32_t)bn);
   if (e != cudaSuccess) return k_ret(e);

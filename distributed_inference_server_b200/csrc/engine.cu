@@ -111,6 +111,7 @@ int Engine::init(const dis_engine_config *c) {
   ENG_CUDA(make_tma_map_2d(&wo_map, wo, L * H, qd_l, 128));
   ENG_CUDA(make_tma_map_2d(&wgu_map, wgu, L * 2 * inter_l, H, (uint32_t)gemm_pick_tile_rows(inter_l)));
   ENG_CUDA(make_tma_map_2d(&wgu_map128, wgu, L * 2 * inter_l, H, 128));
+  ENG_CUDA(make_tma_map_2d(&wgu_map64, wgu, L * 2 * inter_l, H, 64));
   ENG_CUDA(make_tma_map_2d(&wdown_map, wdown, L * H, inter_l, 128));
   ENG_CUDA(make_tma_map_2d(&lm_map, lm_head, vocab_l, H, 128));
   // ---- activations
@@ -654,7 +655,7 @@ cudaError_t Engine::enqueue_layers(int T, int n_splits) {
       RET_CUDA(launch_gemv_silu(xn, wgu + (size_t)l * 2 * inter_l * H, act, T, inter_l, H, stream));
       kernel_launches += (uint64_t)((T + kGemvMaxT - 1) / kGemvMaxT);
     } else if (use_persist && gemm_use_persist(T, inter_l, true)) {
-      RET_CUDA(launch_gemm_persist_silu(wgu_map128, xn_map[2], act, T, inter_l, H, l * 2 * inter_l, stream));
+      RET_CUDA(launch_gemm_persist_silu(wgu_map64, xn_map[3], act, T, inter_l, H, l * 2 * inter_l, stream));
       kernel_launches++;
     } else if (gemm_token_tile(T) >= 128) {
       // prefill is tensor-bound: full 128-row tiles (the balanced, shorter tiles would idle MMA rows)

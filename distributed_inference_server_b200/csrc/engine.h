@@ -79,7 +79,7 @@ struct Engine {
   // weights
   uint16_t *embed = nullptr, *wqkv = nullptr, *wo = nullptr, *wgu = nullptr, *wdown = nullptr, *lm_head = nullptr;
   float *attn_norm = nullptr, *mlp_norm = nullptr, *final_norm = nullptr;
-  TmaMap wqkv_map, wo_map, wgu_map, wgu_map128, wdown_map, lm_map;  // wgu_map: balanced tile height, wgu_map128: 128-row boxes
+  TmaMap wqkv_map, wo_map, wgu_map, wgu_map128, wgu_map64, wdown_map, lm_map;  // wgu_map: balanced tile height, wgu_map128 / 64: 128- / 64-row boxes
   // activations
   float *x = nullptr, *partial = nullptr, *logits = nullptr, *ar_buf = nullptr, *attn_scratch = nullptr;
   float *full_logits = nullptr, *gather_buf = nullptr, *cand_val = nullptr, *cand_val_all = nullptr;

@@ -98,6 +98,9 @@ cudaError_t launch_add_rmsnorm(float *x, const uint32_t *tokens, const uint16_t 
   if (H % 4 != 0 || H * 4 > 200 * 1024) { set_last_error("add_rmsnorm: H must be a multiple of 4 and <= 51200"); return cudaErrorInvalidValue; }
   int threads = (H / 4 + 31) / 32 * 32;
   threads = threads > 1024 ? 1024 : threads;
+  // prefill-sized T is a streaming job: 256-thread CTAs put 8 rows per SM in different phases (load / reduce /
+  // store), where two 1024-thread rows leave the memory pipe idle during every reduction (T = 8192: 135 -> see DESIGN)
+  if (T >= 1024 && threads > 256) threads = 256;
   const size_t smem = H <= threads * 4 ? 0 : (size_t)H * sizeof(float);
   if (smem > 48 * 1024) DIS_CUDA_TRY(cudaFuncSetAttribute(add_rmsnorm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   return launch_k(add_rmsnorm_kernel, dim3(T), dim3(threads), smem, st, x, tokens, embed, partial, n_partial, partial_stride, gain,
@@ -236,6 +239,7 @@ cudaError_t launch_rope_kv_write(const float *qkv, int n_partial, long long part
   const int units = (n_heads + n_kv) * (d / 8) + n_kv * d / 4;
   int threads = (units + 31) / 32 * 32;
   threads = threads > 1024 ? 1024 : threads;
+  if (T >= 1024 && threads > 256) threads = 256;  // streaming job: many small CTAs per SM hide each other's index chasing
   return launch_k(rope_kv_write_kernel, dim3(T), dim3(threads), 0, st, qkv, n_partial, partial_stride, q, kv_pool, page_table,
                   max_pages, pt_row, pos, rope_cos, rope_sin, n_heads, n_kv, d, page_size);
 }

@@ -174,11 +174,163 @@ gemm_persist_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_cons
   if (warp == 1) tmem_dealloc<512>(tmem_base);
 }
 
-// Worth it from two tiles per SM; the dual tile is 128 tokens wide, the plain one 256.
+// ------------------------------------------------------------------------------------ gate-up, paired tile
+// The gate-up projection with the SiLU-gate epilogue as ONE 128 x 256 MMA per k-step: the A tile is 64 gate rows
+// (TMEM lanes 0-63) over their 64 up rows (lanes 64-127), so the tile keeps the 256-token width -- a 128-wide
+// token tile re-reads the A operand from shared memory twice as often and measured 1.17 PFLOP/s against 1.3-1.4
+// for the 256-wide plain tiles -- and its accumulator still fits twice into TMEM.  gate and up of one feature sit
+// in different lane quarters, i.e. different epilogue warps: the up warps (quarters 2, 3) pass their values to the
+// gate warps (quarters 0, 1) for the even 32-column chunks and the gate warps theirs to the up warps for the odd
+// ones, through shared memory, double-buffered, one named barrier (64 threads: an up warp + a gate warp) per pair
+// of chunks -- all four warps do an equal share of the SiLU and of the stores.
+constexpr int kPairChunkFloats = 32 * 32;                    // [token column][lane]
+constexpr int kPairXchgBytes = 2 /*pairs*/ * 2 /*buffers*/ * 2 /*directions*/ * kPairChunkFloats * 4;  // 32 KB
+
+__device__ __forceinline__ void named_bar_sync(int id, int n) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(n) : "memory"); }
+__device__ __forceinline__ void named_bar_arrive(int id, int n) { asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(n) : "memory"); }
+
+__global__ void __launch_bounds__(kGemmThreads, 1)
+gemm_persist_pair_kernel(const __grid_constant__ CUtensorMap w_map64, const __grid_constant__ CUtensorMap x_map,
+                         uint16_t *__restrict__ out_act, int T, int I, int K, int w_row0, int tiles_n, int tiles_t,
+                         int t_fast) {
+  constexpr int BN = 256, kHalf = 64;
+  using Cfg = PersistCfg<256, false>;
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t xchg_base = smem_base + Cfg::kStages * Cfg::kStageBytes;
+  const uint32_t bar_base = xchg_base + kPairXchgBytes;
+  auto full_bar = [&](int s) { return bar_base + 8u * s; };
+  auto empty_bar = [&](int s) { return bar_base + 8u * (Cfg::kStages + s); };
+  auto acc_full = [&](int b) { return bar_base + 8u * (2 * Cfg::kStages + b); };
+  auto acc_empty = [&](int b) { return bar_base + 8u * (2 * Cfg::kStages + 2 + b); };
+  const uint32_t tmem_slot = bar_base + 8u * (2 * Cfg::kStages + 4);
+  auto a_tile = [&](int s) { return smem_base + s * Cfg::kStageBytes; };
+  auto b_tile = [&](int s) { return a_tile(s) + Cfg::kABytes; };
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int num_kb = (K + kBK - 1) / kBK;
+  const int n_tiles = tiles_n * tiles_t;
+  auto tile_n0 = [&](int tile) { return (t_fast ? tile / tiles_t : tile % tiles_n) * kHalf; };
+  auto tile_t0 = [&](int tile) { return (t_fast ? tile % tiles_t : tile / tiles_n) * BN; };
+  const uint64_t w_hint = t_fast ? kEvictFirst : kEvictLast, x_hint = t_fast ? kEvictLast : kEvictFirst;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&w_map64);
+    tma_prefetch_desc(&x_map);
+    for (int s = 0; s < Cfg::kStages; s++) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
+    for (int b = 0; b < 2; b++) { mbar_init(acc_full(b), 1); mbar_init(acc_empty(b), 4); }
+    fence_barrier_init();
+    fence_proxy_async();
+  }
+  if (warp == 1) tmem_alloc<512>(tmem_slot);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  uint32_t tmem_base;
+  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
+  pdl_launch_dependents();
+
+  if (warp == 0) {
+    if (lane == 0) {
+      pdl_wait();
+      int s = 0;
+      uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        const int n0 = tile_n0(tile), t0 = tile_t0(tile);
+        for (int kb = 0; kb < num_kb; kb++) {
+          mbar_wait(empty_bar(s), phase ^ 1u);
+          mbar_expect_tx(full_bar(s), Cfg::kStageBytes);
+          tma_load_2d(a_tile(s), &w_map64, kb * kBK, w_row0 + n0, full_bar(s), w_hint);                      // gate rows -> lanes 0-63
+          tma_load_2d(a_tile(s) + kHalf * kBK * 2, &w_map64, kb * kBK, w_row0 + I + n0, full_bar(s), w_hint);  // up rows -> lanes 64-127
+          tma_load_2d(b_tile(s), &x_map, kb * kBK, t0, full_bar(s), x_hint);
+          if (++s == Cfg::kStages) { s = 0; phase ^= 1u; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      constexpr uint32_t idesc = umma_idesc<BN>();
+      int s = 0, buf = 0;
+      uint32_t phase = 0, aphase[2] = {0u, 0u};
+      for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        mbar_wait(acc_empty(buf), aphase[buf] ^ 1u);
+        tc_fence_after();
+        const uint32_t acc_addr = tmem_base + (uint32_t)(buf * BN);
+        for (int kb = 0; kb < num_kb; kb++) {
+          mbar_wait(full_bar(s), phase);
+          tc_fence_after();
+#pragma unroll
+          for (int k = 0; k < kBK / 16; k++)
+            umma_bf16(acc_addr, umma_desc_sw128(a_tile(s) + k * 32), umma_desc_sw128(b_tile(s) + k * 32), idesc,
+                      (kb > 0 || k > 0) ? 1u : 0u);
+          umma_commit(empty_bar(s));
+          if (++s == Cfg::kStages) { s = 0; phase ^= 1u; }
+        }
+        umma_commit(acc_full(buf));
+        aphase[buf] ^= 1u;
+        buf ^= 1;
+      }
+    }
+  } else {
+    const int quarter = warp & 3;
+    const bool is_up = quarter >= 2;
+    const int pair = quarter & 1;  // gate quarter q works with up quarter q + 2
+    // exchange area of this pair: [2 buffers][2 directions][32 columns][32 lanes] floats
+    float *xchg = reinterpret_cast<float *>(smem_raw + (xchg_base - smem_u32(smem_raw))) + (size_t)pair * 4 * kPairChunkFloats;
+    const int bar_id = 1 + pair;  // named barrier of the pair (64 threads)
+    int step = 0;                 // chunk pairs handled so far: selects the exchange buffer
+    int buf = 0;
+    uint32_t aphase[2] = {0u, 0u};
+    bool waited = false;
+    for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+      const int n = tile_n0(tile) + pair * 32 + lane, t0 = tile_t0(tile);
+      mbar_wait(acc_full(buf), aphase[buf]);
+      tc_fence_after();
+      if (!waited) { pdl_wait(); waited = true; }
+      const uint32_t lane_addr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(buf * BN);
+      // Columns in pairs of 32-column chunks: the gate warp finishes the even chunk (it needs the up values of it),
+      // the up warp the odd one (it needs the gate values): each warp sends one chunk, keeps one, stores one.
+#pragma unroll 1
+      for (int c = 0; c < BN; c += 64, step++) {
+        float *give = xchg + ((step & 1) * 2 + (is_up ? 0 : 1)) * kPairChunkFloats;  // what this warp sends
+        float *take = xchg + ((step & 1) * 2 + (is_up ? 1 : 0)) * kPairChunkFloats;  // what it receives
+        const int c_send = c + (is_up ? 0 : 32), c_keep = c + (is_up ? 32 : 0);
+        uint32_t sv[32], kv[32];
+        tmem_ld_32x32(lane_addr + c_send, sv);
+        tmem_ld_32x32(lane_addr + c_keep, kv);
+        tmem_ld_wait();
+#pragma unroll
+        for (int jj = 0; jj < 32; jj++) give[jj * 32 + lane] = __uint_as_float(sv[jj]);
+        named_bar_sync(bar_id, 64);  // both directions written; the buffers of step - 1 are free again after this
+        if (n < I) {
+#pragma unroll
+          for (int jj = 0; jj < 32; jj++) {
+            const int t = t0 + c_keep + jj;
+            if (t < T) {
+              const float other = take[jj * 32 + lane], mine = __uint_as_float(kv[jj]);
+              const float gv = is_up ? other : mine, uv = is_up ? mine : other;
+              out_act[(size_t)t * I + n] = float_to_bf16_bits((gv / (1.0f + expf(-gv))) * uv);
+            }
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(acc_empty(buf));
+      aphase[buf] ^= 1u;
+      buf ^= 1;
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc<512>(tmem_base);
+}
+
+// Worth it from two tiles per SM (tiles: 128 features, or 64 gate + 64 up features, x 256 tokens).
 bool gemm_use_persist(int T, int N, bool dual) {
-  const int bn = dual ? 128 : 256;
-  if (T < 2 * bn) return false;
-  const long long tiles = (long long)((N + kBM - 1) / kBM) * ((T + bn - 1) / bn);
+  if (T < 512) return false;
+  const int rows = dual ? 64 : kBM;  // output features per tile
+  const long long tiles = (long long)((N + rows - 1) / rows) * ((T + 255) / 256);
   return tiles >= 2 * kNumSMs;
 }
 
@@ -213,11 +365,31 @@ cudaError_t launch_gemm_persist_partial(const TmaMap &w_map, const TmaMap &x_map
   return persist_launch<256, false>(w_map, x_map256, out, nullptr, T, N, K, w_row0, 0, st);
 }
 
-// w_map: 128-row boxes over the fused [2I][K] weight; x_map: 128-row boxes.  act[t][n] = bf16(silu(gate) * up).
-cudaError_t launch_gemm_persist_silu(const TmaMap &w_map, const TmaMap &x_map128, uint16_t *act, int T, int I, int K,
+// w_map64: 64-row boxes over the fused [2I][K] weight (gate rows, then up rows); x_map256: 256-row boxes.
+// act[t][n] = bf16(silu(gate) * up).
+cudaError_t launch_gemm_persist_silu(const TmaMap &w_map64, const TmaMap &x_map256, uint16_t *act, int T, int I, int K,
                                      int w_row0, cudaStream_t st) {
   if (T <= 0) return cudaSuccess;
-  return persist_launch<128, true>(w_map, x_map128, nullptr, act, T, I, K, w_row0, I, st);
+  using Cfg = PersistCfg<256, false>;
+  constexpr int smem = Cfg::kSmemBytes + kPairXchgBytes;
+  static bool attr_set = false;
+  if (!attr_set) {
+    DIS_CUDA_TRY(cudaFuncSetAttribute(gemm_persist_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    attr_set = true;
+  }
+  static int n_sm = 0;
+  if (!n_sm) {
+    int dev = 0;
+    DIS_CUDA_TRY(cudaGetDevice(&dev));
+    DIS_CUDA_TRY(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev));
+  }
+  const int tiles_n = (I + 63) / 64, tiles_t = (T + 255) / 256;
+  const int n_tiles = tiles_n * tiles_t;
+  const int grid = n_tiles < n_sm ? n_tiles : n_sm;
+  const int t_fast = 2LL * I > (long long)T ? 1 : 0;
+  return launch_k(gemm_persist_pair_kernel, dim3(grid), dim3(kGemmThreads), (size_t)smem, st,
+                  *reinterpret_cast<const CUtensorMap *>(&w_map64), *reinterpret_cast<const CUtensorMap *>(&x_map256), act, T, I,
+                  K, w_row0, tiles_n, tiles_t, t_fast);
 }
 
 }  // namespace dis

@@ -86,7 +86,7 @@ int gemm_pick_tile_rows(int N);
 bool gemm_use_persist(int T, int N, bool dual);
 cudaError_t launch_gemm_persist_partial(const TmaMap &w_map128, const TmaMap &x_map256, float *out, int T, int N, int K,
                                         int w_row0, cudaStream_t st);
-cudaError_t launch_gemm_persist_silu(const TmaMap &w_map128, const TmaMap &x_map128, uint16_t *act, int T, int I, int K,
+cudaError_t launch_gemm_persist_silu(const TmaMap &w_map64, const TmaMap &x_map256, uint16_t *act, int T, int I, int K,
                                      int w_row0, cudaStream_t st);
 cudaError_t launch_gemm_silu(const TmaMap &w_map, const TmaMap &x_map, uint16_t *act, int T, int I, int K,
                              int w_row0, int tile_rows, cudaStream_t st);
