@@ -224,7 +224,7 @@ int Engine::init(const dis_engine_config *c) {
   if (tp_size > 1) {
     if (tp_size > kTpMaxRanks) return fail(DIS_ERR_INVALID_ARGUMENT, "tp_size > 8");
     ar_cap_rows = std::min(std::max(max_batch, 128), 256);
-    const size_t data_b = (size_t)2 * tp_size * ar_cap_rows * m.hidden * sizeof(float);
+    const size_t data_b = (size_t)std::max(2 * tp_size, 8) * ar_cap_rows * m.hidden * sizeof(float);  // 8: flag-in-data two-shot areas
     const size_t flags_b = align_up((size_t)2 * 2 * tp_size * ar_cap_rows * 4, 256);  // two hops
     const size_t cand_b = align_up((size_t)2 * tp_size * ar_cap_rows * 2 * 4, 256);
     sym_bytes = data_b + flags_b + cand_b + 256;
@@ -249,7 +249,7 @@ int Engine::tp_export(uint8_t out[64]) {
 int Engine::tp_import(const uint8_t *handles) {
   if (tp_size <= 1 || !sym || !handles) return fail(DIS_ERR_INVALID_ARGUMENT, "tp_import: engine is not tensor parallel");
   ENG_CUDA(cudaSetDevice(cfg.device));
-  const size_t data_b = (size_t)2 * tp_size * ar_cap_rows * m.hidden * sizeof(float);
+  const size_t data_b = (size_t)std::max(2 * tp_size, 8) * ar_cap_rows * m.hidden * sizeof(float);  // 8: flag-in-data two-shot areas
   const size_t flags_b = align_up((size_t)2 * 2 * tp_size * ar_cap_rows * 4, 256);  // two hops
   const size_t cand_b = align_up((size_t)2 * tp_size * ar_cap_rows * 2 * 4, 256);
   for (int r = 0; r < tp_size; r++) {
@@ -271,14 +271,14 @@ int Engine::tp_import(const uint8_t *handles) {
   peers.tp = tp_size;
   peers.cap_rows = ar_cap_rows;
   // one-shot (tp-1)*T*H*4 bytes and one flag hop, or two-shot 2*(tp-1)/tp*T*H*4 bytes and two hops
-  // measured at batch 64, H = 4096: TP=4 (3 MB per rank and exchange) one-shot 2.80 vs two-shot 3.00 ms per step;
-  // TP=8 (7 MB) one-shot 2.88 vs two-shot 2.67 ms -- the second flag hop costs ~3 us, the bytes ~1 us per MB.
-  // The choice is fixed per engine (the two kernels lay the symmetric buffer out differently).
-  const size_t oneshot_bytes = (size_t)(tp_size - 1) * max_batch * m.hidden * sizeof(float);
-  peers.two_shot = tp_size >= 4 && m.hidden % (4 * tp_size) == 0 && oneshot_bytes >= ((size_t)5 << 20);
+  // measured at batch 64, H = 4096, ms per step (one-shot / fenced two-shot / flag-in-data two-shot):
+  //   TP=2  3.44 / 3.76 / 3.28      TP=4  2.80 / 3.00 / 2.64      TP=8  2.88 / 2.67 / 2.42
+  // The choice is fixed per engine (the kernels lay the symmetric buffer out differently).
+  peers.two_shot = m.hidden % (4 * tp_size) == 0 ? 2 : 0;
   if (const char *e = getenv("DIS_TP_EXCHANGE")) {
     if (!strcmp(e, "oneshot")) peers.two_shot = 0;
     else if (!strcmp(e, "twoshot") && m.hidden % (4 * tp_size) == 0) peers.two_shot = 1;
+    else if (!strcmp(e, "ll") && m.hidden % (4 * tp_size) == 0) peers.two_shot = 2;
   }
   tp_custom = true;
   return DIS_OK;

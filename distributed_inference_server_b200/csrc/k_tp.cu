@@ -218,6 +218,113 @@ tp_add_rmsnorm2_kernel(TpPeers peers, float *__restrict__ x, const float *__rest
   }
 }
 
+// Two-shot exchange with the flag INSIDE the data ("LL" protocol): every pair of fp32 values travels as one 16-byte
+// store {v0, epoch, v1, epoch}.  An aligned 8-byte half is written atomically, so a receiver that sees the epoch
+// of this exchange in a half also sees its value: no release fence (an NVLink round trip per hop in the kernels
+// above), no separate flag store, no flag polling thread, no __syncthreads between the hops -- every thread spins on
+// exactly the words it consumes.  Twice the bytes per hop, which the two-shot schedule can afford
+// (4*(tp-1)/tp*T*H*4 per rank).  Same additions in the same order as the other two kernels: bit-identical results.
+//   RS area: data + [parity][source][cap_rows][H/tp] pairs      AG area: data + 4*cap_rows*H + the same shape
+// (a pair = 2 floats: value, epoch; areas are addressed in floats, so every index below is doubled)
+__device__ __forceinline__ void st_ll(float *p, float v0, float v1, uint32_t e) {
+  asm volatile("st.global.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(__float_as_uint(v0)), "r"(e), "r"(__float_as_uint(v1)), "r"(e) : "memory");
+}
+__device__ __forceinline__ void ld_ll(const float *p, uint32_t e, float &v0, float &v1) {
+  uint32_t a, fa, b, fb;
+  long long spins = 0;
+  do {
+    asm volatile("ld.volatile.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(a), "=r"(fa), "=r"(b), "=r"(fb) : "l"(p) : "memory");
+    if (++spins > (1ll << 27)) __trap();  // a peer died or the protocol is broken: fail the launch, do not hang the GPU
+  } while (fa != e || fb != e);
+  v0 = __uint_as_float(a); v1 = __uint_as_float(b);
+}
+
+__global__ void __launch_bounds__(1024)
+tp_add_rmsnorm_ll_kernel(TpPeers peers, float *__restrict__ x, const float *__restrict__ partial, int n_partial,
+                         long long partial_stride, const float *__restrict__ gain, uint16_t *__restrict__ xn,
+                         const uint32_t *__restrict__ step_ptr, uint32_t idx, int parity, int H, float eps) {
+  __shared__ float red[32];
+  extern __shared__ float row[];  // [H]: every element is written and read back by the same thread until the reduction
+  const int t = blockIdx.x;
+  pdl_launch_dependents();
+  pdl_wait();
+  const uint32_t epoch = *step_ptr * 256u + idx;
+  const int step = blockDim.x * 4;
+  const int me = peers.rank, tp = peers.tp, cap = peers.cap_rows;
+  const int Hs = H / tp;
+  const size_t ag_base = (size_t)4 * cap * H;
+  const size_t blk_me = (((size_t)parity * tp + me) * cap + t) * (size_t)Hs * 2;  // block written by this rank, row t
+
+  // ---- hop 1: split-K reduce, each column block goes to its owner
+  for (int i = threadIdx.x * 4; i < H; i += step) {
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    const float *pp = partial + (size_t)t * H + i;
+#pragma unroll 4
+    for (int s = 0; s < n_partial; s++) {
+      const float4 p = *reinterpret_cast<const float4 *>(pp + (size_t)s * partial_stride);
+      v.x += p.x; v.y += p.y; v.z += p.z; v.w += p.w;
+    }
+    const int owner = i / Hs;
+    if (owner != me) {
+      float *dst = peers.data[owner] + blk_me + (size_t)(i - owner * Hs) * 2;
+      st_ll(dst, v.x, v.y, epoch);
+      st_ll(dst + 4, v.z, v.w, epoch);
+    } else {
+      *reinterpret_cast<float4 *>(row + i) = v;
+    }
+  }
+  // ---- owner (the same threads that kept their block): sum in rank order, add the residual, hop 2
+  for (int i = threadIdx.x * 4; i < H; i += step) {
+    if (i / Hs != me) continue;
+    const int j = i - me * Hs;
+    float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int r = 0; r < tp; r++) {
+      float4 v;
+      if (r == me) v = *reinterpret_cast<const float4 *>(row + i);
+      else {
+        const float *src = peers.data[me] + (((size_t)parity * tp + r) * cap + t) * (size_t)Hs * 2 + (size_t)j * 2;
+        ld_ll(src, epoch, v.x, v.y);
+        ld_ll(src + 4, epoch, v.z, v.w);
+      }
+      a.x += v.x; a.y += v.y; a.z += v.z; a.w += v.w;
+    }
+    const float4 xv = *reinterpret_cast<const float4 *>(x + (size_t)t * H + i);
+    a.x += xv.x; a.y += xv.y; a.z += xv.z; a.w += xv.w;
+    for (int r = 0; r < tp; r++)
+      if (r != me) {
+        float *dst = peers.data[r] + ag_base + blk_me + (size_t)j * 2;
+        st_ll(dst, a.x, a.y, epoch);
+        st_ll(dst + 4, a.z, a.w, epoch);
+      }
+    *reinterpret_cast<float4 *>(row + i) = a;
+  }
+  // ---- full row: own block from shared memory, the others as they arrive; RMSNorm
+  float ss = 0.f;
+  for (int i = threadIdx.x * 4; i < H; i += step) {
+    const int owner = i / Hs;
+    float4 a;
+    if (owner == me) a = *reinterpret_cast<const float4 *>(row + i);
+    else {
+      const float *src = peers.data[me] + ag_base + (((size_t)parity * tp + owner) * cap + t) * (size_t)Hs * 2 + (size_t)(i - owner * Hs) * 2;
+      ld_ll(src, epoch, a.x, a.y);
+      ld_ll(src + 4, epoch, a.z, a.w);
+      *reinterpret_cast<float4 *>(row + i) = a;
+    }
+    *reinterpret_cast<float4 *>(x + (size_t)t * H + i) = a;
+    ss = sumsq4(ss, a);
+  }
+  ss = tp_block_sum(ss, red);
+  const float inv = rsqrtf(ss / (float)H + eps);
+  for (int i = threadIdx.x * 4; i < H; i += step) {
+    const float4 v = *reinterpret_cast<const float4 *>(row + i);
+    const float4 g = *reinterpret_cast<const float4 *>(gain + i);
+    uint2 o;
+    o.x = float2_to_bf16x2(v.x * inv * g.x, v.y * inv * g.y);
+    o.y = float2_to_bf16x2(v.z * inv * g.z, v.w * inv * g.w);
+    *reinterpret_cast<uint2 *>(xn + (size_t)t * H + i) = o;
+  }
+}
+
 cudaError_t launch_tp_add_rmsnorm(const TpPeers &peers, float *x, const float *partial, int n_partial,
                                   long long partial_stride, const float *gain, uint16_t *xn, const uint32_t *step_ptr,
                                   uint32_t idx, int parity, int T, int H, float eps, cudaStream_t st) {
@@ -226,6 +333,13 @@ cudaError_t launch_tp_add_rmsnorm(const TpPeers &peers, float *x, const float *p
   if (H % 4 != 0) { set_last_error("tp_add_rmsnorm: H must be a multiple of 4"); return cudaErrorInvalidValue; }
   int threads = (H / 4 + 31) / 32 * 32;
   threads = threads > 1024 ? 1024 : threads;
+  if (peers.two_shot == 2) {
+    if (H % (4 * peers.tp) != 0) { set_last_error("tp_add_rmsnorm: the LL exchange needs H % (4 * tp) == 0"); return cudaErrorInvalidValue; }
+    const size_t smem2 = (size_t)H * sizeof(float);
+    if (smem2 > 48 * 1024) DIS_CUDA_TRY(cudaFuncSetAttribute(tp_add_rmsnorm_ll_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));
+    return launch_k(tp_add_rmsnorm_ll_kernel, dim3(T), dim3(threads), smem2, st, peers, x, partial, n_partial, partial_stride,
+                    gain, xn, step_ptr, idx, parity, H, eps);
+  }
   if (peers.two_shot) {
     if (H % (4 * peers.tp) != 0) { set_last_error("tp_add_rmsnorm: two-shot exchange needs H % (4 * tp) == 0"); return cudaErrorInvalidValue; }
     const size_t smem2 = (size_t)H * sizeof(float);

@@ -32,7 +32,8 @@ cudaError_t launch_bf16_to_f32(const uint16_t *src, float *dst, size_t n, cudaSt
 // k_tp.cu : exchange over peer memory.  Every rank owns one symmetric allocation:
 //   data [2 parities][tp sources][cap_rows][H] fp32 | flags [2 hops][2][tp][cap_rows] u32 | cand [2][tp][cap_rows][2] u32 |
 //   cand_flags [2][tp] u32     (peers PUSH into the slot of their own rank; the owner polls and reads locally)
-// two_shot: the data area is used as a reduce-scatter area + an all-gather area instead (see k_tp.cu).
+// two_shot: the data area is used as a reduce-scatter area + an all-gather area instead (see k_tp.cu); the
+// flag-in-data variant needs 8 * cap_rows * H floats of it.
 constexpr int kTpMaxRanks = 8;
 struct TpPeers {
   float *data[kTpMaxRanks];
@@ -40,7 +41,7 @@ struct TpPeers {
   uint32_t *cand[kTpMaxRanks];
   uint32_t *cand_flags[kTpMaxRanks];
   int rank, tp, cap_rows;
-  int two_shot;  // 0: one-shot push all-reduce, 1: reduce-scatter + all-gather over column blocks
+  int two_shot;  // 0: one-shot push all-reduce, 1: reduce-scatter + all-gather over column blocks, 2: the same with flag-in-data stores
 };
 cudaError_t launch_tp_add_rmsnorm(const TpPeers &peers, float *x, const float *partial, int n_partial,
                                   long long partial_stride, const float *gain, uint16_t *xn, const uint32_t *step_ptr,

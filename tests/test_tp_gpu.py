@@ -88,7 +88,7 @@ def _prompts():
 
 
 @needs2
-@pytest.mark.parametrize("custom", ["oneshot", "twoshot", None], ids=["peer-memory", "peer-memory-twoshot", "nccl"])
+@pytest.mark.parametrize("custom", ["oneshot", "twoshot", "ll", None], ids=["peer-memory", "peer-memory-twoshot", "peer-memory-ll", "nccl"])
 @pytest.mark.parametrize("sampled", [False, True], ids=["greedy", "sampled"])
 def test_tp2_matches_oracle(sampled, custom):
     n_new = 12
@@ -124,3 +124,5 @@ def test_twoshot_exchange_is_bit_identical_to_oneshot():
     diff = np.abs(a[0][1] - b[0][1])
     assert np.array_equal(a[0][1], b[0][1]), (float(diff.max()), int((diff > 0).sum()), diff.size)
     assert a[0][0] == b[0][0]
+    c = _run(prompts, 24, [0.0] * 3, "ll")      # flag-in-data variant of the two-shot schedule
+    assert np.array_equal(a[0][1], c[0][1]) and a[0][0] == c[0][0]
