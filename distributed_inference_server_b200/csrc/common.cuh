@@ -1,5 +1,6 @@
 // common.cuh -- shared device/host helpers for the sm_100a kernels.
 #pragma once
+#include <atomic>
 
 #include <cuda_bf16.h>
 #include <cuda_runtime.h>
@@ -25,6 +26,18 @@ const char *get_last_error();
   } while (0)
 
 constexpr int kNumSMs = 148;
+
+// cudaFuncSetAttribute applies to the CURRENT device: a launcher that raises its kernel's dynamic shared memory
+// limit must do so once per device, not once per process (a host may run one engine per GPU in one process).
+struct DeviceOnce {
+  std::atomic<unsigned long long> seen{0};
+  bool first_on_this_device() {
+    int d = 0;
+    if (cudaGetDevice(&d) != cudaSuccess || d < 0 || d > 63) return true;
+    const unsigned long long bit = 1ull << d;
+    return (seen.fetch_or(bit) & bit) == 0;
+  }
+};
 
 // ---- bf16 helpers -----------------------------------------------------------------------------
 __host__ __device__ inline float bf16_bits_to_float(uint16_t b) {

@@ -339,10 +339,9 @@ static cudaError_t persist_launch(const TmaMap &w_map, const TmaMap &x_map, floa
                                   int K, int w_row0, int up_off, cudaStream_t st) {
   using Cfg = PersistCfg<BN, kDual>;
   auto kern = gemm_persist_kernel<BN, kDual>;
-  static bool attr_set = false;
-  if (!attr_set) {
+  static DeviceOnce once;
+  if (once.first_on_this_device()) {
     DIS_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
-    attr_set = true;
   }
   static int n_sm = 0;
   if (!n_sm) {
@@ -372,10 +371,9 @@ cudaError_t launch_gemm_persist_silu(const TmaMap &w_map64, const TmaMap &x_map2
   if (T <= 0) return cudaSuccess;
   using Cfg = PersistCfg<256, false>;
   constexpr int smem = Cfg::kSmemBytes + kPairXchgBytes;
-  static bool attr_set = false;
-  if (!attr_set) {
+  static DeviceOnce once;
+  if (once.first_on_this_device()) {
     DIS_CUDA_TRY(cudaFuncSetAttribute(gemm_persist_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    attr_set = true;
   }
   static int n_sm = 0;
   if (!n_sm) {

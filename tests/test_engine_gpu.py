@@ -259,6 +259,18 @@ def test_context_limit_and_page_exhaustion():
     w.shutdown()
 
 
+def test_kv_pool_sized_from_free_memory():
+    """kv_pages = 0: the pool takes kv_mem_fraction of the free device memory, but never more pages than max_batch
+    sequences of max_ctx tokens can use."""
+    w = small_worker(kv_pages=0, kv_mem_fraction=0.01, max_batch=4)         # context 128 = 8 pages of 16 per sequence
+    st = w.status()
+    assert st.kv_pages_total == 4 * 8 and st.kv_pages_free == st.kv_pages_total
+    r = w.infer(InferenceBatch([[5] * 40, [6] * 3], requests=[BatchedRequest(params=InferenceParams(6, 0.0)) for _ in range(2)]))
+    assert [len(x.tokens) for x in r.results] == [6, 6]
+    assert w.status().kv_pages_free == st.kv_pages_total                      # everything handed back
+    w.shutdown()
+
+
 def test_error_codes():
     shape = ModelShape(1024, 256, 2, 4, 1, 128, 512, 128)
     e = Engine(WorkerConfig(shape, max_batch=2, kv_pages=8, page_size=16, max_step_tokens=64))
