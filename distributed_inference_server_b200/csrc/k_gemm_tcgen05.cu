@@ -239,10 +239,9 @@ static cudaError_t gemm_launch(const TmaMap &w_map, const TmaMap &x_map, float *
                                int K, int w_row0, int up_off, int split_k, int tile_rows, cudaStream_t st) {
   using Cfg = GemmCfg<BN, kDual>;
   auto kern = gemm_tcgen05_kernel<BN, kDual>;
-  static bool attr_set = false;
-  if (!attr_set) {
+  static DeviceOnce once;
+  if (once.first_on_this_device()) {
     DIS_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxDynSmem));
-    attr_set = true;
   }
   const int num_kb = (K + kBK - 1) / kBK;
   const int per = (num_kb + split_k - 1) / split_k;
