@@ -16,7 +16,8 @@ SHAPE = O.ModelShape(2048, 512, 3, 8, 2, 64, 1408, 256)
 SEED = 21
 
 
-def _rank(rank, world, idq, outq, prompts, n_new, temps, hq, custom):
+def _rank(rank, world, idq, outq, prompts, n_new, temps, hq, custom, SHAPE=None):
+    SHAPE = SHAPE or globals()["SHAPE"]
     if custom:  # "oneshot" / "twoshot": which peer-memory exchange kernel the engine uses (k_tp.cu)
         os.environ["DIS_TP_EXCHANGE"] = custom
     from distributed_inference_server_b200 import Engine, InferenceParams, WorkerConfig, shard_plan as SP
@@ -47,6 +48,7 @@ def _rank(rank, world, idq, outq, prompts, n_new, temps, hq, custom):
         e.tp_import([handles[r] for r in range(world)])
     # each rank holds exactly the plan's slice
     for kind, layer in [(O.WQ, 1), (O.WK, 0), (O.WV, 2), (O.WO, 1), (O.WGATE, 0), (O.WUP, 2), (O.WDOWN, 1), (O.LM_HEAD, 0), (O.EMBED, 0)]:
+        layer = min(layer, SHAPE.layers - 1)
         got = O.from_bf16_bits(e.read_tensor(kind, layer))
         want = O.synth_tensor(SHAPE, SEED, kind, layer)[SP.shard_slices(SHAPE, kind, rank, world)].reshape(-1)
         assert np.array_equal(got, want), (rank, kind, layer)
@@ -62,11 +64,11 @@ def _rank(rank, world, idq, outq, prompts, n_new, temps, hq, custom):
     e.close()
 
 
-def _run(prompts, n_new, temps, custom, world=2):
+def _run(prompts, n_new, temps, custom, world=2, shape=None):
     ctx = mp.get_context("spawn")
     idq, outq = ctx.Queue(), ctx.Queue()
     hq = [ctx.Queue() for _ in range(world)]
-    procs = [ctx.Process(target=_rank, args=(r, world, idq, outq, prompts, n_new, temps, hq, custom)) for r in range(world)]
+    procs = [ctx.Process(target=_rank, args=(r, world, idq, outq, prompts, n_new, temps, hq, custom, shape)) for r in range(world)]
     for p in procs:
         p.start()
     res = {}
@@ -126,3 +128,22 @@ def test_twoshot_exchange_is_bit_identical_to_oneshot():
     assert a[0][0] == b[0][0]
     c = _run(prompts, 24, [0.0] * 3, "ll")      # flag-in-data variant of the two-shot schedule
     assert np.array_equal(a[0][1], c[0][1]) and a[0][0] == c[0][0]
+
+
+WIDE = O.ModelShape(512, 8192, 1, 64, 8, 128, 1024, 128)   # hidden 8192 (Llama-3-70B's): two float4 per thread in the exchange kernels
+
+
+@needs2
+@pytest.mark.parametrize("custom", ["oneshot", "twoshot", "ll"])
+def test_tp2_wide_hidden_matches_oracle(custom):
+    """The exchange kernels walk a row of more than 4096 columns in several passes (shared-memory row instead of
+    registers): the path Llama-3-70B takes, checked here on a one-layer model of that width."""
+    rng = np.random.default_rng(4)
+    prompts = [rng.integers(0, WIDE.vocab, n).tolist() for n in (5, 21)]
+    res = _run(prompts, 6, [0.0, 0.0], custom, shape=WIDE)
+    assert res[0][0] == res[1][0] and np.array_equal(res[0][1], res[1][1])
+    ref = O.Oracle(WIDE, act_round=False); ref.fill_synthetic(SEED, True)
+    want = ref.generate(prompts, 1, n_logit_steps=1)
+    rel = np.abs(res[0][1] - want["logits"][:, 0]).max() / np.abs(want["logits"]).max()
+    assert rel <= 2e-2, rel
+
