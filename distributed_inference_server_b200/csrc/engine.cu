@@ -248,6 +248,8 @@ int Engine::tp_export(uint8_t out[64]) {
 
 int Engine::tp_import(const uint8_t *handles) {
   if (tp_size <= 1 || !sym || !handles) return fail(DIS_ERR_INVALID_ARGUMENT, "tp_import: engine is not tensor parallel");
+  // exchange epochs are step * 256 + index of the exchange inside the forward pass (2 per layer, 255 = candidate merge)
+  if (2 * m.layers >= 255) return fail(DIS_ERR_INVALID_ARGUMENT, "tp_import: the peer-memory exchange supports at most 127 layers (NCCL path remains)");
   ENG_CUDA(cudaSetDevice(cfg.device));
   const size_t data_b = (size_t)std::max(2 * tp_size, 8) * ar_cap_rows * m.hidden * sizeof(float);  // 8: flag-in-data two-shot areas
   const size_t flags_b = align_up((size_t)2 * 2 * tp_size * ar_cap_rows * 4, 256);  // two hops
