@@ -90,6 +90,7 @@ PROTOTYPES = {
     "dis_engine_decode": (C.c_int, [vp, C.c_int32, vp, vp, vp]),
     "dis_engine_last_logits": (C.c_int, [vp, vp, C.c_int32]),
     "dis_engine_profile_decode": (C.c_int, [vp, C.c_int32, vp, vp, vp, vp, vp]),
+    "dis_engine_replay_last_step": (C.c_int, [vp, C.c_int32, f32p]),
     "dis_engine_status": (C.c_int, [vp, C.POINTER(WorkerStatus)]),
     "dis_engine_model_info": (C.c_int, [vp, C.POINTER(ModelConfig)]),
     "dis_tp_unique_id": (C.c_int, [vp]),

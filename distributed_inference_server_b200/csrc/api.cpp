@@ -86,6 +86,11 @@ int dis_engine_profile_decode(dis_engine *e, int32_t n, const int32_t *slots, ui
   LOCKED(e);
   return e->eng.profile_decode(n, slots, out_tokens, out_finish, class_ms, class_launches);
 }
+int dis_engine_replay_last_step(dis_engine *e, int32_t n, float *avg_ms) {
+  if (int rc = guard_null(e)) return rc;
+  LOCKED(e);
+  return e->eng.replay_last_step(n, avg_ms);
+}
 int dis_engine_last_logits(dis_engine *e, float *host, int32_t n_rows) {
   if (int rc = guard_null(e)) return rc;
   LOCKED(e);

@@ -891,6 +891,7 @@ int Engine::decode(int n, const int *slots, uint32_t *out_tokens, int *out_finis
       it = graphs.emplace(key, ex).first;
     }
     ENG_CUDA(cudaGraphLaunch(it->second, stream));
+    last_graph = it->second;
     kernel_launches += graph_launches[key];
   }
   ENG_CUDA(cudaMemcpyAsync(h_out_tokens, d_out_tokens, (size_t)T * 4, cudaMemcpyDeviceToHost, stream));
@@ -908,6 +909,19 @@ int Engine::decode(int n, const int *slots, uint32_t *out_tokens, int *out_finis
     finish_check(s, h_out_tokens[r]);
     out_finish[i] = s.finish;
   }
+  return DIS_OK;
+}
+
+int Engine::replay_last_step(int n, float *avg_ms) {
+  if (!last_graph || n <= 0 || !avg_ms) return fail(DIS_ERR_INVALID_ARGUMENT, "replay_last_step: no captured decode step yet");
+  ENG_CUDA(cudaSetDevice(cfg.device));
+  ENG_CUDA(cudaEventRecord(ev0, stream));
+  for (int i = 0; i < n; i++) ENG_CUDA(cudaGraphLaunch(last_graph, stream));
+  ENG_CUDA(cudaEventRecord(ev1, stream));
+  ENG_CUDA(cudaEventSynchronize(ev1));
+  float ms = 0.f;
+  ENG_CUDA(cudaEventElapsedTime(&ms, ev0, ev1));
+  *avg_ms = ms / (float)n;
   return DIS_OK;
 }
 

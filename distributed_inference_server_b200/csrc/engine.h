@@ -118,6 +118,8 @@ struct Engine {
   std::vector<cudaEvent_t> prof_events;  // pool
   std::vector<std::pair<int, int>> prof_marks;  // (class, index of the event recorded BEFORE that class)
   void prof_mark(int cls);
+  cudaGraphExec_t last_graph = nullptr;
+  int replay_last_step(int n, float *avg_ms);
   int profile_decode(int n, const int *slots, uint32_t *out_tokens, int *out_finish, float *class_ms, int *class_launches);
   // tensor parallel
   NcclApi *nccl = nullptr;

@@ -252,6 +252,12 @@ class Engine:
                                                        ms.ctypes.data, cnt.ctypes.data))
         return toks, fin, {k: (float(ms[i]), int(cnt[i])) for i, k in enumerate(B.PROF_CLASSES)}
 
+    def replay_last_step(self, n: int) -> float:
+        """Average device milliseconds of the last decode step's CUDA graph replayed n times back to back."""
+        ms = C.c_float()
+        self._check(self.lib.dis_engine_replay_last_step(self.h, int(n), C.byref(ms)))
+        return float(ms.value)
+
     def last_logits(self, n_rows: int) -> np.ndarray:
         out = np.empty((n_rows, self.vocab), np.float32)
         self._check(self.lib.dis_engine_last_logits(self.h, out.ctypes.data, n_rows))

@@ -160,6 +160,11 @@ enum { DIS_PROF_NORM = 0, DIS_PROF_QKV, DIS_PROF_ROPE, DIS_PROF_ATTN, DIS_PROF_O
        DIS_PROF_ALLREDUCE, DIS_PROF_HEAD_NORM, DIS_PROF_LM_HEAD, DIS_PROF_SAMPLE, DIS_PROF_COUNT };
 DIS_API int dis_engine_profile_decode(dis_engine *e, int32_t n, const int32_t *slots, uint32_t *out_tokens,
                                       int32_t *out_finish, float *class_ms, int32_t *class_launches);
+/* Measurement only (no reference counterpart): replays the CUDA graph of the most recent dis_engine_decode call
+ * `n` times back to back -- same inputs, same outputs, nothing advances -- and returns the average device time of
+ * one replay.  The difference to the time of a real step is what the host adds between steps (metadata upload,
+ * launch, token read-back, the caller's own work). */
+DIS_API int dis_engine_replay_last_step(dis_engine *e, int32_t n, float *avg_ms);
 /* Logits of the last prefill/decode call, row i = i-th listed sequence, [n][vocab] fp32 (gathered
  * across tensor-parallel ranks). For parity tests and TokenEvent.logprob (models.rs:276). */
 DIS_API int dis_engine_last_logits(dis_engine *e, float *host, int32_t n_rows);
