@@ -271,6 +271,25 @@ def test_kv_pool_sized_from_free_memory():
     w.shutdown()
 
 
+def test_replay_last_step_changes_nothing():
+    """dis_engine_replay_last_step is a measurement aid: replaying the last decode graph must leave the sequence
+    exactly where it was (same next tokens as an engine that never replayed)."""
+    shape = ModelShape(1024, 256, 2, 4, 1, 128, 512, 128)
+    outs = []
+    for replay in (False, True):
+        e = Engine(WorkerConfig(shape, max_batch=4, kv_pages=32, page_size=16, max_step_tokens=64))
+        e.load_synthetic(3); e.finalize()
+        slots = [e.seq_add(p, InferenceParams(max_tokens=12, temperature=0.0)) for p in ([1, 2, 3, 4, 5], [9] * 20)]
+        toks = [list(map(int, e.prefill(slots)[0]))]
+        for i in range(8):
+            toks.append(list(map(int, e.decode(slots)[0])))
+            if replay and i % 3 == 1:
+                assert e.replay_last_step(5) > 0.0
+        outs.append(toks)
+        e.close()
+    assert outs[0] == outs[1]
+
+
 def test_error_codes():
     shape = ModelShape(1024, 256, 2, 4, 1, 128, 512, 128)
     e = Engine(WorkerConfig(shape, max_batch=2, kv_pages=8, page_size=16, max_step_tokens=64))
