@@ -9,8 +9,10 @@
 //     between tiles;
 //   * the accumulator is double-buffered in TMEM (2 x 256 columns = all 512): the MMA warp starts tile i+1 in
 //     one buffer while the epilogue warps read tile i from the other (acc_full / acc_empty mbarriers);
-//   * non-dual tiles are 128 features x 256 tokens; the gate-up ("dual") tile is 2 x 128 features x 128 tokens,
-//     i.e. the same 48 KB per k-block and the same bytes per flop, with both of its accumulators double-buffered.
+//   * tiles are 128 features x 256 tokens.  The gate-up projection runs as gemm_persist_pair_kernel below (64 gate
+//     rows over their 64 up rows in ONE 128 x 256 MMA); the kDual = true instantiation of this kernel (2 x 128
+//     features x 128 tokens, two N = 128 MMAs per k-step) is the measured alternative it replaced (1.17 against
+//     1.28 PFLOP/s) and is no longer instantiated.
 // No split-K: callers use it only when there are at least two tiles per SM (gemm_use_persist).
 #include <cuda.h>
 

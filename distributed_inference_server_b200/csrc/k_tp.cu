@@ -9,7 +9,13 @@
 //                    -> residual add + RMSNorm -> bf16 GEMM input.        One kernel, one CTA per token row.
 //   tp_argmax_merge: vocab-parallel greedy sampling: (max, id) candidates exchanged the same way.
 //
-// This is a one-shot all-reduce: every rank sends (tp-1) * T * H * 4 bytes; no NVLink round trip is on the
+// Three interchangeable kernels (same additions in the same order, bit-identical results; TpPeers.two_shot picks):
+//   tp_add_rmsnorm_kernel     one-shot push, one flag hop                       (tp-1)   * T*H*4 bytes per rank
+//   tp_add_rmsnorm2_kernel    reduce-scatter + all-gather of column blocks      2(tp-1)/tp * T*H*4, two flag hops
+//   tp_add_rmsnorm_ll_kernel  the same two hops with the flag inside the data   4(tp-1)/tp * T*H*4, no fence, no flag
+//                             (DEFAULT: 3.28 / 2.64 / 2.42 ms per step at TP = 2 / 4 / 8, batch 64)
+//
+// The first is a one-shot all-reduce: every rank sends (tp-1) * T * H * 4 bytes; no NVLink round trip is on the
 // critical path (stores are fire-and-forget, polling and reads are local).  Synchronisation is per ROW (a
 // CTA only waits for the same row of each peer), so there is no grid-wide barrier and no CTA ever waits for
 // another CTA of its own GPU.  Buffers are double-buffered by all-reduce parity: a rank can only reach
