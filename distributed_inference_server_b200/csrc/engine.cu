@@ -529,7 +529,8 @@ cudaError_t Engine::upload_step(int T, int R) {
     pt_dirty = false;
   }
   (void)T; (void)R;
-  cur_meta->h<uint32_t>(cur_meta->o_arstep)[0] = ++ar_step;
+  if (((++ar_step) & 0xFFFFFFu) == 0) ++ar_step;  // exchange epochs are (step << 8) + index: never 0, the value of an untouched flag
+  cur_meta->h<uint32_t>(cur_meta->o_arstep)[0] = ar_step;
   ar_idx = 0;
   return cudaMemcpyAsync(cur_meta->dev, cur_meta->host, cur_meta->bytes, cudaMemcpyHostToDevice, stream);
 }
