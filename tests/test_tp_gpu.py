@@ -16,8 +16,9 @@ SHAPE = O.ModelShape(2048, 512, 3, 8, 2, 64, 1408, 256)
 SEED = 21
 
 
-def _rank(rank, world, idq, outq, prompts, n_new, temps, hq, custom, SHAPE=None):
+def _rank(rank, world, idq, outq, prompts, n_new, temps, hq, custom, SHAPE=None, SEED=None):
     SHAPE = SHAPE or globals()["SHAPE"]
+    SEED = SEED or globals()["SEED"]
     if custom:  # "oneshot" / "twoshot": which peer-memory exchange kernel the engine uses (k_tp.cu)
         os.environ["DIS_TP_EXCHANGE"] = custom
     from distributed_inference_server_b200 import Engine, InferenceParams, WorkerConfig, shard_plan as SP
@@ -64,11 +65,11 @@ def _rank(rank, world, idq, outq, prompts, n_new, temps, hq, custom, SHAPE=None)
     e.close()
 
 
-def _run(prompts, n_new, temps, custom, world=2, shape=None):
+def _run(prompts, n_new, temps, custom, world=2, shape=None, seed=None):
     ctx = mp.get_context("spawn")
     idq, outq = ctx.Queue(), ctx.Queue()
     hq = [ctx.Queue() for _ in range(world)]
-    procs = [ctx.Process(target=_rank, args=(r, world, idq, outq, prompts, n_new, temps, hq, custom, shape)) for r in range(world)]
+    procs = [ctx.Process(target=_rank, args=(r, world, idq, outq, prompts, n_new, temps, hq, custom, shape, seed)) for r in range(world)]
     for p in procs:
         p.start()
     res = {}
@@ -146,4 +147,14 @@ def test_tp2_wide_hidden_matches_oracle(custom):
     want = ref.generate(prompts, 1, n_logit_steps=1)
     rel = np.abs(res[0][1] - want["logits"][:, 0]).max() / np.abs(want["logits"]).max()
     assert rel <= 2e-2, rel
+
+
+@needs2
+def test_tp2_64_greedy_tokens_identical_to_transformers():
+    """The 64-token fixture of tests/golden (clear margin at every step) on two GPUs: both ranks produce the
+    transformers continuation token for token."""
+    z = np.load(os.path.join(os.path.dirname(__file__), "golden", "mini_llama3_64.npz"))
+    shape = O.ModelShape(*[int(v) for v in z["shape"]], float(z["rope_theta"]), float(z["rms_eps"]))
+    res = _run([z["prompt"].tolist()], 64, [0.0], "ll", shape=shape, seed=int(z["weight_seed"]))
+    assert res[0][0] == res[1][0] == [z["greedy"].tolist()]
 
