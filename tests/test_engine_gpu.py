@@ -187,6 +187,33 @@ def test_llama3_8b_width_two_layers():
     e.close()
 
 
+def test_llama3_8b_full_size_properties():
+    """BASELINE configs[1] at FULL size (32 layers, random-init): no CPU oracle finishes this in seconds, so the check is
+    through properties that do not depend on size -- two copies of a prompt in one batch give bit-identical logits and
+    tokens (row invariance of every kernel), a second run of the same batch reproduces the first bit for bit
+    (determinism: no atomics, fixed summation orders), a prompt alone and inside a batch agree within the logit
+    tolerance, and everything is finite and inside the vocabulary."""
+    shape = O.LLAMA3_8B
+    e = make_engine(shape, seed=0, max_batch=8, kv_pages=8 * 10, page_size=64, max_step_tokens=2048)
+    rng = np.random.default_rng(5)
+    p0, p2 = rng.integers(0, shape.vocab, 512).tolist(), rng.integers(0, shape.vocab, 300).tolist()
+    batch = [p0, list(p0), p2, list(p2), rng.integers(0, shape.vocab, 17).tolist()]
+    runs = []
+    for _ in range(2):
+        got, logits = greedy(e, batch, 16, want_logits=True)
+        runs.append((got, logits))
+    got, logits = runs[0]
+    assert got[0] == got[1] and got[2] == got[3]
+    for step in logits:
+        assert np.isfinite(step).all()
+        assert np.array_equal(step[0], step[1]) and np.array_equal(step[2], step[3])
+    assert all(0 <= t < shape.vocab for seq in got for t in seq)
+    assert runs[1][0] == got and all(np.array_equal(a, b) for a, b in zip(runs[1][1], logits))
+    alone, lg = greedy(e, [p0], 2, want_logits=True)
+    assert rel_err(lg[0][0], logits[0][0]) <= LOGIT_TOL
+    e.close()
+
+
 # ---- the worker interface: structural contracts of the spec (SURVEY.md §4) -----------------------
 
 def small_worker(**kw):
