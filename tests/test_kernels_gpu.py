@@ -92,6 +92,34 @@ def test_gemm_tcgen05(T, N, K):
         assert np.abs(got - ref).max() <= 1e-4 * np.abs(ref).max() + 1e-6, (split, np.abs(got - ref).max())
 
 
+@pytest.mark.parametrize("T,N,K,silu", [(8192, 6144, 4096, False), (4096, 4096, 14336, False), (8192, 14336, 4096, True),
+                                        (32, 28672 // 2, 4096, True), (512, 6144, 4096, False)])
+def test_gemm_full_size_against_torch(T, N, K, silu):
+    """BASELINE-sized projections (Llama-3-8B qkv / down / gate-up at an 8192-token prefill chunk, a decode batch, a
+    single 512-token request): too large for the CPU oracle in seconds, so the reference is a plain torch fp32 matmul
+    of the same bf16 operands on the device (tolerance: fp32 accumulation order only, 2e-4 of max|y|; the SiLU-gate
+    output is bf16, one ulp)."""
+    g = torch.Generator(device=DEV); g.manual_seed(T + N + K)
+    X = (torch.randn((T, K), device=DEV, generator=g)).to(torch.bfloat16)
+    W = (torch.randn(((2 if silu else 1) * N, K), device=DEV, generator=g) * 0.02).to(torch.bfloat16)
+    if silu:
+        act = torch.empty((T, N), dtype=torch.bfloat16, device=DEV)
+        check(lib().dis_k_gemm_silu(ptr(X), ptr(W), ptr(act), T, N, K, None))
+        sync()
+        gate, up = X.float() @ W[:N].float().T, X.float() @ W[N:].float().T
+        ref = torch.nn.functional.silu(gate) * up
+        err = (act.float() - ref).abs().max().item()
+        assert err <= BF16_ULP * ref.abs().max().item() * 1.05 + 1e-6, err
+    else:
+        out = torch.full((1, T, N), float("nan"), dtype=torch.float32, device=DEV)
+        check(lib().dis_k_gemm(ptr(X), ptr(W), ptr(out), T, N, K, 1, None))
+        sync()
+        ref = X.float() @ W.float().T
+        assert torch.isfinite(out).all()
+        err = (out[0] - ref).abs().max().item()
+        assert err <= 2e-4 * ref.abs().max().item(), err
+
+
 def test_gemm_rejects_empty_split():
     X, W = dev_bf16(np.zeros((8, 576), np.float32)), dev_bf16(np.zeros((128, 576), np.float32))
     out = torch.zeros((4, 8, 128), dtype=torch.float32, device=DEV)
