@@ -231,6 +231,43 @@ def test_rope_kv_write_and_attention(d, nh, nkv):
         assert np.abs(got - ref).max() <= 2 * BF16_ULP * np.abs(ref).max() + 1e-5, (splits, np.abs(got - ref).max())
 
 
+def test_attention_full_size_against_torch():
+    """Llama-3-8B geometry (32 query heads, 8 kv heads, d = 128, 64-token pages), batch 32 with contexts from 1 to 8000
+    tokens on shuffled pages: decode attention with 1 and 4 history splits against softmax(q K^T / sqrt(d)) V in fp32
+    torch on the same bf16 K/V (tolerance: P is rounded to bf16 for the P.V MMA -- two bf16 ulps of the output scale)."""
+    g = torch.Generator(device=DEV); g.manual_seed(9)
+    d, nh, nkv, ps, B = 128, 32, 8, 64, 32
+    rng = np.random.default_rng(9)
+    ctx = np.concatenate([[1, 63, 64, 65, 8000], rng.integers(100, 4000, B - 5)]).astype(np.int32)
+    pages_per = [(int(c) + ps - 1) // ps for c in ctx]
+    n_pages, max_pages = sum(pages_per) + 3, max(pages_per)
+    perm = rng.permutation(n_pages)
+    pt = np.zeros((B, max_pages), np.int32)
+    k0 = 0
+    for b in range(B):
+        pt[b, :pages_per[b]] = perm[k0:k0 + pages_per[b]]; k0 += pages_per[b]
+    pool = torch.randn((n_pages, 2, nkv, ps, d), device=DEV, generator=g).to(torch.bfloat16)
+    q = torch.randn((B, nh * d), device=DEV, generator=g).to(torch.bfloat16)
+    dpt, dctx, drow = dev_i32(pt), dev_i32(ctx), dev_i32(np.arange(B))
+    ref = torch.empty((B, nh, d), dtype=torch.float32, device=DEV)
+    for b in range(B):
+        pages = torch.as_tensor(pt[b, :pages_per[b]].astype(np.int64), device=DEV)
+        kv = pool[pages].float()                                   # [pages, 2, nkv, ps, d]
+        K = kv[:, 0].permute(1, 0, 2, 3).reshape(nkv, -1, d)[:, :int(ctx[b])]
+        V = kv[:, 1].permute(1, 0, 2, 3).reshape(nkv, -1, d)[:, :int(ctx[b])]
+        qb = q[b].float().reshape(nkv, nh // nkv, d)
+        p = torch.softmax(qb @ K.transpose(1, 2) / d ** 0.5, dim=-1)
+        ref[b] = (p @ V).reshape(nh, d)
+    for splits in (1, 4):
+        out = torch.empty((B, nh * d), dtype=torch.bfloat16, device=DEV)
+        scr = torch.empty(max(lib().dis_k_attn_scratch_elems(B, nh, d, splits), 1), dtype=torch.float32, device=DEV)
+        check(lib().dis_k_attn_paged(ptr(q), ptr(pool), n_pages, ptr(dpt), max_pages, ptr(drow), ptr(dctx), ptr(out), ptr(scr),
+                                     splits, B, nh, nkv, d, ps, None))
+        sync()
+        err = (out.float().reshape(B, nh, d) - ref).abs().max().item()
+        assert err <= 2 * BF16_ULP * ref.abs().max().item() + 1e-5, (splits, err)
+
+
 def test_attention_long_context_tiles():
     rng = np.random.default_rng(3)
     d, nh, nkv, page_size = 128, 4, 1, 64
