@@ -345,9 +345,9 @@ def test_sampler_argmax_and_ties():
     assert ref[1] == 500
 
 
-def test_sampler_top_p_matches_oracle():
+@pytest.mark.parametrize("T,V", [(48, 4099), (24, 128256)], ids=["ragged-vocab", "llama3-vocab"])
+def test_sampler_top_p_matches_oracle(T, V):
     rng = np.random.default_rng(1)
-    T, V = 48, 4099
     lg = (rng.standard_normal((T, V)) * 2.5).astype(np.float32)
     temps = rng.choice([0.0, 0.5, 1.0, 1.7], T).astype(np.float32)
     tps = rng.choice([0.1, 0.5, 0.9, 0.95, 1.0], T).astype(np.float32)
