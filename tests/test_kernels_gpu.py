@@ -330,6 +330,48 @@ def test_attention_prefill_blocks(d, nh, nkv, page_size):
     assert np.abs(got - ref).max() <= 2 * BF16_ULP * np.abs(ref).max() + 1e-5, np.abs(got - ref).max()
 
 
+def test_attention_prefill_full_size_against_torch():
+    """Llama-3-8B geometry, a 3000-token prompt prefilled from position 0 and the last 1000 tokens of a 4000-token one
+    (a later chunk of a chunked prefill), 64-token pages in shuffled order: causal attention against fp32 torch."""
+    g = torch.Generator(device=DEV); g.manual_seed(13)
+    d, nh, nkv, ps = 128, 32, 8, 64
+    lens, starts = [3000, 4000], [0, 3000]
+    rng = np.random.default_rng(13)
+    pages_per = [(n + ps - 1) // ps for n in lens]
+    n_pages, max_pages = sum(pages_per) + 2, max(pages_per)
+    perm = rng.permutation(n_pages)
+    pt = np.zeros((2, max_pages), np.int32)
+    pt[0, :pages_per[0]] = perm[:pages_per[0]]; pt[1, :pages_per[1]] = perm[pages_per[0]:pages_per[0] + pages_per[1]]
+    pool = torch.randn((n_pages, 2, nkv, ps, d), device=DEV, generator=g).to(torch.bfloat16)
+    tok0, qlen, pos0, ptrow, t = [], [], [], [], 0
+    for s in range(2):
+        for p0 in range(starts[s], lens[s], 16):
+            ln = min(16, lens[s] - p0)
+            tok0.append(t); qlen.append(ln); pos0.append(p0); ptrow.append(s); t += ln
+    q = torch.randn((t, nh * d), device=DEV, generator=g).to(torch.bfloat16)
+    out = torch.empty((t, nh * d), dtype=torch.bfloat16, device=DEV)
+    check(lib().dis_k_attn_prefill(ptr(q), ptr(pool), n_pages, ptr(dev_i32(pt)), max_pages, ptr(dev_i32(tok0)), ptr(dev_i32(qlen)),
+                                   ptr(dev_i32(pos0)), ptr(dev_i32(ptrow)), ptr(out), len(tok0), nh, nkv, d, ps, None))
+    sync()
+    row, worst, scale = 0, 0.0, 0.0
+    for s in range(2):
+        pages = torch.as_tensor(pt[s, :pages_per[s]].astype(np.int64), device=DEV)
+        kv = pool[pages].float()
+        K = kv[:, 0].permute(1, 0, 2, 3).reshape(nkv, -1, d)[:, :lens[s]]
+        V = kv[:, 1].permute(1, 0, 2, 3).reshape(nkv, -1, d)[:, :lens[s]]
+        n_q = lens[s] - starts[s]
+        qs = q[row:row + n_q].float().reshape(n_q, nkv, nh // nkv, d).permute(1, 2, 0, 3)       # [nkv, G, n_q, d]
+        sc = qs @ K.transpose(1, 2).unsqueeze(1) / d ** 0.5                                     # [nkv, G, n_q, keys]
+        keys = torch.arange(lens[s], device=DEV)[None, :]
+        qpos = torch.arange(starts[s], lens[s], device=DEV)[:, None]
+        sc = sc.masked_fill(keys > qpos, float("-inf"))
+        ref = (torch.softmax(sc, dim=-1) @ V.unsqueeze(1)).permute(2, 0, 1, 3).reshape(n_q, nh * d)
+        worst = max(worst, (out[row:row + n_q].float() - ref).abs().max().item())
+        scale = max(scale, ref.abs().max().item())
+        row += n_q
+    assert worst <= 2 * BF16_ULP * scale + 1e-5, (worst, scale)
+
+
 def test_sampler_argmax_and_ties():
     rng = np.random.default_rng(0)
     T, V = 6, 128256
