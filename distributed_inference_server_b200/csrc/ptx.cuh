@@ -15,8 +15,11 @@ __device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
 __device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
 }
+// A wait that never comes true (a TMA box that does not match the bytes the barrier expects, a lost arrive) would
+// hang the GPU until a watchdog kills the process: after ~2^26 failed polls -- tens of seconds, no legitimate wait in
+// these kernels is longer than milliseconds -- the kernel traps instead, which fails the launch with an error.
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
-  uint32_t ok;
+  uint32_t ok, polls = 0;
   do {
     asm volatile(
         "{\n\t.reg .pred p;\n\t"
@@ -25,6 +28,7 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
         : "=r"(ok)
         : "r"(bar), "r"(parity)
         : "memory");
+    if (!ok && ++polls > (1u << 26)) __trap();
   } while (!ok);
 }
 __device__ __forceinline__ void fence_barrier_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }

@@ -1,2 +1,2 @@
-timeout 600 python -m pytest tests -m gpu -x -q 2>&1 | tail -3
-timeout 600 python bench.py > gpurun_out/bench_full.json 2> gpurun_out/bench_full.err
+timeout 300 python -m pytest tests -m gpu -x -q 2>&1 | tail -3
+timeout 300 python bench.py > gpurun_out/bench_full.json 2> gpurun_out/bench_full.err
