@@ -9,7 +9,7 @@ TAG=${2:-r1}
 KRE=${3:-gemm_tcgen05_kernel}
 SKIP=${4:-0}
 CNT=${5:-2}
-CMD="python bench.py --steps 1 --warmup 1 --layers 4 --no-cpu --profile-steps 0 --no-graph --ttft-runs 1 --prompt-len 512"
+CMD="timeout 200 python bench.py --steps 1 --warmup 1 --layers 4 --no-cpu --profile-steps 0 --no-graph --ttft-runs 1 --prompt-len 512"
 if [ "$MODE" = launches ]; then
   $CMD > gpurun_out/plain_$TAG.log 2>&1 &&
   ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches_$TAG.csv $CMD > gpurun_out/ncu_launch_$TAG.log 2>&1
