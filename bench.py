@@ -12,6 +12,16 @@ for checkpoints or datasets.  `value` is timed with CUDA events on the engine's 
 steps; `e2e` is the same loop on the host clock through the C-ABI decode call, whose host buffers
 (slot list in, token ids out) cross PCIe inside the timed region every step.
 
+Other lines (diagnostics and the remaining BASELINE configs, never the default):
+  --batch 1 / --model 70b            configs[1] batch 1, configs[3] Llama-3-70B TP = 8 batch 32
+  --workload serving                 configs[4]: 256 requests, prompts 128-8192, through dis_serving_*
+  --workload prefix                  TTFT with prefix KV reuse
+  --shard-of N                       one rank's shard of a TP = N run on one GPU, no exchange
+  --tp-exchange / --nccl-allreduce   A/B of the exchange kernels (k_tp.cu) against each other and NCCL
+Extra keys: roofline (dominant kernel, from an eager step timed per kernel class), step_roofline (whole step),
+graph_only_ms_last_step (the last step's CUDA graph replayed back to back), ttft_* (prefill of the whole batch and of
+one request), kernel_class_ms_per_step, clocks.
+
 The reference has no implementation of this path (crates/inference/src/worker.rs:1), so the
 `--impl reference` arm and `cpu_baseline` time the CPU oracle port (oracle/llama_oracle.c) on the
 host cores on a bounded sample of the same workload.
