@@ -208,6 +208,7 @@ int Engine::init(const dis_engine_config *c) {
     memset(h_page_table, 0, (size_t)max_batch * max_pages * sizeof(int));
   }
   seqs.resize((size_t)max_batch);
+  slot_stamp.assign((size_t)max_batch, 0);
   use_pdl = !(c->flags & DIS_FLAG_NO_PDL);
   if (const char *g = getenv("DIS_GEMM_PERSIST")) use_persist = atoi(g) != 0;
   if (const char *g = getenv("DIS_GEMV_MAX_T")) gemv_max_t = std::max(0, std::min(kGemvMaxT, atoi(g)));
@@ -749,10 +750,12 @@ int Engine::prefill(int n, const int *slots, uint32_t *out_tokens, int *out_fini
   if (shut) return fail(DIS_ERR_SHUTDOWN, "engine is shut down");
   if (!loaded) return fail(DIS_ERR_MODEL_NOT_LOADED, "model not loaded");
   if (n <= 0 || n > max_batch || !slots || !out_tokens || !out_finish) return fail(DIS_ERR_INVALID_ARGUMENT, "prefill: bad argument");
+  const uint64_t stamp = ++call_stamp;  // a slot seen twice in one call carries this call's stamp already
   for (int i = 0; i < n; i++) {
     if (slots[i] < 0 || slots[i] >= max_batch || !seqs[(size_t)slots[i]].used || seqs[(size_t)slots[i]].prefilled)
       return fail(DIS_ERR_INVALID_ARGUMENT, "prefill: sequence missing or already prefilled");
-    for (int k = 0; k < i; k++) if (slots[k] == slots[i]) return fail(DIS_ERR_INVALID_ARGUMENT, "prefill: duplicate slot");
+    if (slot_stamp[(size_t)slots[i]] == stamp) return fail(DIS_ERR_INVALID_ARGUMENT, "prefill: duplicate slot");
+    slot_stamp[(size_t)slots[i]] = stamp;
   }
   ENG_CUDA(cudaSetDevice(cfg.device));
   ENG_CUDA(cudaEventRecord(ev0, stream));
@@ -831,11 +834,13 @@ int Engine::decode(int n, const int *slots, uint32_t *out_tokens, int *out_finis
   if (shut) return fail(DIS_ERR_SHUTDOWN, "engine is shut down");
   if (!loaded) return fail(DIS_ERR_MODEL_NOT_LOADED, "model not loaded");
   if (n <= 0 || n > max_batch || !slots || !out_tokens || !out_finish) return fail(DIS_ERR_INVALID_ARGUMENT, "decode: bad argument");
+  const uint64_t stamp = ++call_stamp;
   for (int i = 0; i < n; i++) {
     if (slots[i] < 0 || slots[i] >= max_batch) return fail(DIS_ERR_INVALID_ARGUMENT, "decode: slot out of range");
     const Sequence &s = seqs[(size_t)slots[i]];
     if (!s.used || !s.prefilled) return fail(DIS_ERR_INVALID_ARGUMENT, "decode: sequence missing or not prefilled");
-    for (int k = 0; k < i; k++) if (slots[k] == slots[i]) return fail(DIS_ERR_INVALID_ARGUMENT, "decode: duplicate slot");
+    if (slot_stamp[(size_t)slots[i]] == stamp) return fail(DIS_ERR_INVALID_ARGUMENT, "decode: duplicate slot");
+    slot_stamp[(size_t)slots[i]] = stamp;
   }
   ENG_CUDA(cudaSetDevice(cfg.device));
   // Sequences that cannot take another token (finished, out of context, out of pages) are left out

@@ -104,6 +104,8 @@ struct Engine {
   StepMeta *cur_meta = &meta_dec;
   int n_qblocks = 0;                // > 0 while a prefill chunk is being enqueued
   std::vector<Sequence> seqs;
+  std::vector<uint64_t> slot_stamp;  // duplicate-slot detection in O(n): stamp of the last call that listed the slot
+  uint64_t call_stamp = 0;
   int last_rows = 0;  // logits rows of the last call
   // decode graphs keyed by (T, n_splits, all_greedy)
   std::map<uint64_t, cudaGraphExec_t> graphs;
