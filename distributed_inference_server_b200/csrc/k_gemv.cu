@@ -30,7 +30,10 @@ __device__ __forceinline__ float dot8(const uint4 &w, const uint4 &x) {
 // shared memory and are added in warp order (deterministic).
 // Measured and rejected: a persistent one-wave variant walking (row group, chunk) items with the register ring
 // kept full across row groups -- 4.15 ms per step: the per-item bookkeeping and a barrier per row group cost more
-// issue slots than the CTA turnover they remove; 4 rows x depth 4 -- 3.62 ms (fewer CTAs resident).
+// issue slots than the CTA turnover they remove; 4 rows x depth 4 -- 3.62 ms (fewer CTAs resident); this kernel as ONE
+// wave of CTAs each walking ~13 row groups (so that the dependent kernel is released at once) -- 4.18 ms: without
+// loads in flight across the group boundary the memory pipe idles during every reduction.  The tcgen05 path at
+// T = 1 takes 3.06 ms against this kernel's 3.17 (same box, alternating runs).
 // kSilu: rows n < N are gate rows, rows N + n the matching up rows; output bf16 act[t][n].
 template <int kT, bool kSilu, int kW = kGemvW, int kDepthT = kGemvDepth>
 __global__ void __launch_bounds__(kGemvWarps * 32, (kT == 1 && kW * kDepthT <= 8) ? 3 : 2)
