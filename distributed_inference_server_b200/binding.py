@@ -64,11 +64,12 @@ class PrefixStats(C.Structure):
 
 
 class ServingEvent(C.Structure):
-    _fields_ = [("request_id", C.c_uint64), ("kind", C.c_int32), ("token", C.c_uint32), ("index", C.c_int32),
-                ("finish_reason", C.c_int32), ("prompt_tokens", C.c_int32), ("waited_ms", C.c_double)]
+    _fields_ = [("request_id", C.c_uint8 * 16), ("kind", C.c_int32), ("token", C.c_uint32), ("index", C.c_int32),
+                ("finish_reason", C.c_int32), ("prompt_tokens", C.c_int32), ("waited_ms", C.c_double),
+                ("logprob", C.c_float)]
 
 
-TOKEN_CALLBACK = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int32, C.c_uint32, C.c_int32, C.c_int32)
+TOKEN_CALLBACK = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int32, C.c_uint32, C.c_int32, C.c_int32, C.c_float)
 
 u16p, u32p, i32p, f32p, u64p, vp = (C.POINTER(C.c_uint16), C.POINTER(C.c_uint32), C.POINTER(C.c_int32),
                                     C.POINTER(C.c_float), C.POINTER(C.c_uint64), C.c_void_p)
@@ -89,6 +90,7 @@ PROTOTYPES = {
     "dis_engine_prefill": (C.c_int, [vp, C.c_int32, vp, vp, vp]),
     "dis_engine_decode": (C.c_int, [vp, C.c_int32, vp, vp, vp]),
     "dis_engine_last_logits": (C.c_int, [vp, vp, C.c_int32]),
+    "dis_engine_last_logprobs": (C.c_int, [vp, C.c_int32, vp, vp]),
     "dis_engine_profile_decode": (C.c_int, [vp, C.c_int32, vp, vp, vp, vp, vp]),
     "dis_engine_replay_last_step": (C.c_int, [vp, C.c_int32, f32p]),
     "dis_engine_status": (C.c_int, [vp, C.POINTER(WorkerStatus)]),
@@ -101,8 +103,9 @@ PROTOTYPES = {
     "dis_serving_create": (C.c_int, [vp, C.POINTER(QueueConfig), C.c_int32, C.POINTER(vp)]),
     "dis_serving_destroy": (C.c_int, [vp]),
     "dis_serving_last_error": (C.c_char_p, [vp]),
-    "dis_serving_submit": (C.c_int, [vp, C.c_uint64, vp, C.c_int32, C.POINTER(SamplingParams), C.c_int32]),
-    "dis_serving_submit_at": (C.c_int, [vp, C.c_uint64, vp, C.c_int32, C.POINTER(SamplingParams), C.c_int32, C.c_double]),
+    "dis_serving_submit": (C.c_int, [vp, vp, vp, C.c_int32, C.POINTER(SamplingParams), C.c_int32]),
+    "dis_serving_submit_at": (C.c_int, [vp, vp, vp, C.c_int32, C.POINTER(SamplingParams), C.c_int32, C.c_double]),
+    "dis_serving_cancel": (C.c_int, [vp, vp]),
     "dis_serving_step": (C.c_int, [vp, C.POINTER(ServingEvent), C.c_int32, i32p]),
     "dis_serving_step_at": (C.c_int, [vp, C.c_double, C.POINTER(ServingEvent), C.c_int32, i32p]),
     "dis_serving_depth": (C.c_int, [vp, C.POINTER(QueueDepth)]),
@@ -130,7 +133,7 @@ PROTOTYPES = {
                                           C.c_int32, C.c_int32, vp]),
     "dis_k_attn_prefill": (C.c_int, [vp, vp, C.c_int64, vp, C.c_int32, vp, vp, vp, vp, vp, C.c_int32, C.c_int32, C.c_int32,
                                      C.c_int32, C.c_int32, vp]),
-    "dis_k_sample": (C.c_int, [vp, C.c_int64, C.c_int32, C.c_int32, vp, vp, vp, vp, vp, vp]),
+    "dis_k_sample": (C.c_int, [vp, C.c_int64, C.c_int32, C.c_int32, vp, vp, vp, vp, vp, vp, vp]),
     "dis_k_synth_bf16": (C.c_int, [vp, C.c_size_t, C.c_uint64, C.c_int32, C.c_int32, C.c_float, C.c_float, vp]),
 }
 

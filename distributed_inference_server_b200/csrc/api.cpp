@@ -96,6 +96,11 @@ int dis_engine_last_logits(dis_engine *e, float *host, int32_t n_rows) {
   LOCKED(e);
   return e->eng.last_logits_host(host, n_rows);
 }
+int dis_engine_last_logprobs(dis_engine *e, int32_t n, const int32_t *slots, float *out) {
+  if (int rc = guard_null(e)) return rc;
+  LOCKED(e);
+  return e->eng.last_logprobs(n, slots, out);
+}
 int dis_engine_status(dis_engine *e, dis_worker_status *out) {
   if (int rc = guard_null(e)) return rc;
   LOCKED(e);
@@ -216,11 +221,11 @@ int dis_k_attn_prefill(const uint16_t *q, const uint16_t *kv_pool, int64_t n_pag
                                         n_heads, n_kv, d, page_size, (cudaStream_t)stream));
 }
 int dis_k_sample(const float *logits, int64_t ld, int32_t T, int32_t V, const float *temperature, const float *top_p,
-                 const uint64_t *seeds, const uint64_t *steps, uint32_t *out_tokens, void *stream) {
+                 const uint64_t *seeds, const uint64_t *steps, uint32_t *out_tokens, float *out_logprob, void *stream) {
   if (int rc = need_gpu()) return rc;
   return k_ret(dis::launch_sample(logits, ld, T, V, temperature, top_p, reinterpret_cast<const unsigned long long *>(seeds),
-                                  reinterpret_cast<const unsigned long long *>(steps), out_tokens, 0, nullptr,
-                                  (cudaStream_t)stream));
+                                  reinterpret_cast<const unsigned long long *>(steps), out_tokens, 0, nullptr, nullptr,
+                                  out_logprob, (cudaStream_t)stream));
 }
 int dis_k_synth_bf16(uint16_t *dst, size_t n, uint64_t seed, int32_t kind, int32_t layer, float amp, float offset,
                      void *stream) {

@@ -1,6 +1,7 @@
 // common.cuh -- shared device/host helpers for the sm_100a kernels.
 #pragma once
 #include <atomic>
+#include <mutex>
 
 #include <cuda_bf16.h>
 #include <cuda_runtime.h>
@@ -30,12 +31,22 @@ constexpr int kNumSMs = 148;
 // cudaFuncSetAttribute applies to the CURRENT device: a launcher that raises its kernel's dynamic shared memory
 // limit must do so once per device, not once per process (a host may run one engine per GPU in one process).
 struct DeviceOnce {
-  std::atomic<unsigned long long> seen{0};
-  bool first_on_this_device() {
+  std::atomic<unsigned long long> done{0};
+  std::mutex mu;
+  // Runs f() (the cudaFuncSetAttribute calls) once per device, with that device current.  The device's bit is
+  // published only AFTER f() has succeeded, and under a mutex: a second host thread making its first launch on the
+  // same device either sees the bit (attribute set) or waits for the first thread to finish setting it.
+  template <class F>
+  cudaError_t run(F &&f) {
     int d = 0;
-    if (cudaGetDevice(&d) != cudaSuccess || d < 0 || d > 63) return true;
+    if (cudaGetDevice(&d) != cudaSuccess || d < 0 || d > 63) return f();
     const unsigned long long bit = 1ull << d;
-    return (seen.fetch_or(bit) & bit) == 0;
+    if (done.load(std::memory_order_acquire) & bit) return cudaSuccess;
+    std::lock_guard<std::mutex> g(mu);
+    if (done.load(std::memory_order_relaxed) & bit) return cudaSuccess;
+    const cudaError_t e = f();
+    if (e == cudaSuccess) done.fetch_or(bit, std::memory_order_release);
+    return e;
   }
 };
 

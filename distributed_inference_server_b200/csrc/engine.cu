@@ -127,8 +127,9 @@ int Engine::init(const dis_engine_config *c) {
   ENG_CUDA(dev_alloc(&logits, (size_t)max_batch * vocab_l, &bytes_allocated));
   attn_scratch_elems = (size_t)(max_batch + 2 * kNumSMs + 64) * nh_l * (2 + m.head_dim);
   ENG_CUDA(dev_alloc(&attn_scratch, attn_scratch_elems, &bytes_allocated));
-  ENG_CUDA(dev_alloc(&d_out_tokens, (size_t)max_batch, &bytes_allocated));
-  ENG_CUDA(cudaMallocHost(reinterpret_cast<void **>(&h_out_tokens), (size_t)max_batch * sizeof(uint32_t)));
+  // sampler output: [max_batch] token ids, then [max_batch] log-probabilities (fp32) -- one D2H copy per step
+  ENG_CUDA(dev_alloc(&d_out_tokens, (size_t)2 * max_batch, &bytes_allocated));
+  ENG_CUDA(cudaMallocHost(reinterpret_cast<void **>(&h_out_tokens), (size_t)2 * max_batch * sizeof(uint32_t)));
   if (tp_size > 1) {
     ENG_CUDA(dev_alloc(&ar_buf, cap * H, &bytes_allocated));
     ENG_CUDA(dev_alloc(&full_logits, (size_t)max_batch * m.vocab, &bytes_allocated));
@@ -137,6 +138,8 @@ int Engine::init(const dis_engine_config *c) {
     ENG_CUDA(dev_alloc(&cand_tok, (size_t)max_batch, &bytes_allocated));
     ENG_CUDA(dev_alloc(&cand_val_all, (size_t)max_batch * tp_size, &bytes_allocated));
     ENG_CUDA(dev_alloc(&cand_tok_all, (size_t)max_batch * tp_size, &bytes_allocated));
+    ENG_CUDA(dev_alloc(&cand_sum, (size_t)max_batch, &bytes_allocated));
+    ENG_CUDA(dev_alloc(&cand_sum_all, (size_t)max_batch * tp_size, &bytes_allocated));
   }
   const uint32_t boxes[4] = {32, 64, 128, 256};
   for (int i = 0; i < 4; i++) {
@@ -227,7 +230,7 @@ int Engine::init(const dis_engine_config *c) {
     ar_cap_rows = std::min(std::max(max_batch, 128), 256);
     const size_t data_b = (size_t)std::max(2 * tp_size, 8) * ar_cap_rows * m.hidden * sizeof(float);  // 8: flag-in-data two-shot areas
     const size_t flags_b = align_up((size_t)2 * 2 * tp_size * ar_cap_rows * 4, 256);  // two hops
-    const size_t cand_b = align_up((size_t)2 * tp_size * ar_cap_rows * 2 * 4, 256);
+    const size_t cand_b = align_up((size_t)2 * tp_size * ar_cap_rows * 4 * 4, 256);
     sym_bytes = data_b + flags_b + cand_b + 256;
     ENG_CUDA(dev_alloc(&sym, sym_bytes, &bytes_allocated));
     ENG_CUDA(cudaMemset(sym, 0, sym_bytes));
@@ -254,7 +257,7 @@ int Engine::tp_import(const uint8_t *handles) {
   ENG_CUDA(cudaSetDevice(cfg.device));
   const size_t data_b = (size_t)std::max(2 * tp_size, 8) * ar_cap_rows * m.hidden * sizeof(float);  // 8: flag-in-data two-shot areas
   const size_t flags_b = align_up((size_t)2 * 2 * tp_size * ar_cap_rows * 4, 256);  // two hops
-  const size_t cand_b = align_up((size_t)2 * tp_size * ar_cap_rows * 2 * 4, 256);
+  const size_t cand_b = align_up((size_t)2 * tp_size * ar_cap_rows * 4 * 4, 256);
   for (int r = 0; r < tp_size; r++) {
     uint8_t *base = sym;
     if (r != tp_rank) {
@@ -295,7 +298,7 @@ Engine::~Engine() {
   if (comm && nccl) nccl->CommDestroy(comm);
   for (int r = 0; r < kTpMaxRanks; r++) if (peer_base[r]) cudaIpcCloseMemHandle(peer_base[r]);
   void *ptrs[] = {embed, wqkv, wo, wgu, wdown, lm_head, attn_norm, mlp_norm, final_norm, x, partial, logits, ar_buf,
-                  attn_scratch, full_logits, gather_buf, cand_val, cand_val_all, cand_tok, cand_tok_all, xn, q, attn,
+                  attn_scratch, full_logits, gather_buf, cand_val, cand_val_all, cand_tok, cand_tok_all, cand_sum, cand_sum_all, xn, q, attn,
                   act, d_out_tokens, kv_pool, d_page_table, rope_cos, rope_sin, meta_dec.dev, meta_pre.dev, sym};
   for (void *p : ptrs) if (p) cudaFree(p);
   if (h_out_tokens) cudaFreeHost(h_out_tokens);
@@ -609,6 +612,9 @@ cudaError_t Engine::enqueue_layers(int T, int n_splits) {
   const bool gemv = (cfg.flags & DIS_FLAG_FORCE_GEMV) || T <= gemv_max_t;
   const bool fused_ar = tp_size > 1 && tp_custom && T <= ar_cap_rows;  // exchange over peer memory, no NCCL kernel
   const bool pdl_ok = use_pdl && !profiling && (tp_size == 1 || fused_ar);
+  // the PDL switch is thread-local state of the launch helper: whatever way this function is left, later
+  // kernel-level calls on this host thread must not inherit it
+  struct PdlOff { ~PdlOff() { pdl_enabled() = false; } } pdl_off;
   pend_ptr = nullptr; pend_count = 0; pend_str = 0; pend_needs_ar = false;
   const uint32_t *tokens = cur_meta->d<uint32_t>(cur_meta->o_tokens);
   const int *pos = cur_meta->d<int>(cur_meta->o_pos), *ptrow = cur_meta->d<int>(cur_meta->o_ptrow), *ctx = cur_meta->d<int>(cur_meta->o_ctx);
@@ -703,28 +709,31 @@ cudaError_t Engine::enqueue_head(int R, bool all_greedy) {
   prof_mark(P_SAMPLE);
   const float *temp = cur_meta->d<float>(cur_meta->o_temp), *topp = cur_meta->d<float>(cur_meta->o_topp);
   const unsigned long long *seed = cur_meta->d<unsigned long long>(cur_meta->o_seed), *step = cur_meta->d<unsigned long long>(cur_meta->o_step);
+  float *d_logprob = reinterpret_cast<float *>(d_out_tokens + max_batch);  // TokenEvent.logprob, models.rs:276
   if (tp_size == 1) {
     kernel_launches++;
-    return launch_sample(logits, vocab_l, R, vocab_l, temp, topp, seed, step, d_out_tokens, 0, nullptr, stream);
+    return launch_sample(logits, vocab_l, R, vocab_l, temp, topp, seed, step, d_out_tokens, 0, nullptr, nullptr, d_logprob, stream);
   }
   if (all_greedy && tp_custom) {
-    // vocab-parallel argmax: local (value, id), exchanged and merged over peer memory in one kernel
-    RET_CUDA(launch_sample(logits, vocab_l, R, vocab_l, nullptr, nullptr, nullptr, nullptr, cand_tok, vocab_off, cand_val, stream));
+    // vocab-parallel argmax: local (value, id, sum-exp), exchanged and merged over peer memory in one kernel
+    RET_CUDA(launch_sample(logits, vocab_l, R, vocab_l, nullptr, nullptr, nullptr, nullptr, cand_tok, vocab_off, cand_val, cand_sum, nullptr, stream));
     kernel_launches += 2;
-    return launch_tp_argmax_merge(peers, cand_val, cand_tok, cur_meta->d<uint32_t>(cur_meta->o_arstep), R, d_out_tokens, stream);
+    return launch_tp_argmax_merge(peers, cand_val, cand_tok, cand_sum, cur_meta->d<uint32_t>(cur_meta->o_arstep), R, d_out_tokens,
+                                  d_logprob, stream);
   }
   if (all_greedy) {
-    // vocab-parallel argmax: local (value, id) -> all-gather -> merge
-    RET_CUDA(launch_sample(logits, vocab_l, R, vocab_l, nullptr, nullptr, nullptr, nullptr, cand_tok, vocab_off, cand_val, stream));
+    // vocab-parallel argmax: local (value, id, sum-exp) -> all-gather -> merge
+    RET_CUDA(launch_sample(logits, vocab_l, R, vocab_l, nullptr, nullptr, nullptr, nullptr, cand_tok, vocab_off, cand_val, cand_sum, nullptr, stream));
     int r = nccl->AllGather(cand_val, cand_val_all, (size_t)R, /*ncclFloat32*/ 7, comm, stream);
     if (r == 0) r = nccl->AllGather(cand_tok, cand_tok_all, (size_t)R, /*ncclUint32*/ 3, comm, stream);
+    if (r == 0) r = nccl->AllGather(cand_sum, cand_sum_all, (size_t)R, /*ncclFloat32*/ 7, comm, stream);
     if (r != 0) { set_last_error(std::string("ncclAllGather: ") + nccl->GetErrorString(r)); return cudaErrorUnknown; }
-    kernel_launches += 4;
-    return launch_argmax_merge(cand_val_all, cand_tok_all, tp_size, R, d_out_tokens, stream);
+    kernel_launches += 5;
+    return launch_argmax_merge(cand_val_all, cand_tok_all, cand_sum_all, tp_size, R, d_out_tokens, d_logprob, stream);
   }
   RET_CUDA(gather_full_logits(R));
   kernel_launches++;
-  return launch_sample(full_logits, m.vocab, R, m.vocab, temp, topp, seed, step, d_out_tokens, 0, nullptr, stream);
+  return launch_sample(full_logits, m.vocab, R, m.vocab, temp, topp, seed, step, d_out_tokens, 0, nullptr, nullptr, d_logprob, stream);
 }
 
 __global__ void interleave_logits_kernel(const float *__restrict__ gathered, float *__restrict__ full, int tp, int R,
@@ -807,10 +816,18 @@ int Engine::prefill(int n, const int *slots, uint32_t *out_tokens, int *out_fini
     ENG_CUDA(enqueue_layers(T, 1));
     if (R > 0) {
       ENG_CUDA(enqueue_head(R, all_greedy));
-      ENG_CUDA(cudaMemcpyAsync(h_out_tokens, d_out_tokens, (size_t)R * 4, cudaMemcpyDeviceToHost, stream));
+      ENG_CUDA(cudaMemcpyAsync(h_out_tokens, d_out_tokens, (size_t)(max_batch + R) * 4, cudaMemcpyDeviceToHost, stream));
+    } else if (pend_needs_ar) {
+      // A chunk that ends no prompt needs no logits, but its last exchange must still happen: the exchange buffers
+      // alternate by the parity of the exchange index, which only lines up across forward passes if every pass
+      // performs the same (even) number of exchanges, 2 per layer.
+      ENG_CUDA(consume_pending(final_norm, nullptr, T, T));
     }
     ENG_CUDA(cudaStreamSynchronize(stream));  // the pinned metadata block is reused by the next chunk
-    for (int r = 0; r < R; r++) out_tokens[owners[(size_t)r]] = h_out_tokens[r];
+    for (int r = 0; r < R; r++) {
+      out_tokens[owners[(size_t)r]] = h_out_tokens[r];
+      seqs[(size_t)slots[owners[(size_t)r]]].last_logprob = reinterpret_cast<const float *>(h_out_tokens + max_batch)[r];
+    }
     last_rows = R;
   }
   ENG_CUDA(cudaEventRecord(ev1, stream));
@@ -906,7 +923,7 @@ int Engine::decode(int n, const int *slots, uint32_t *out_tokens, int *out_finis
     last_graph = it->second;
     kernel_launches += graph_launches[key];
   }
-  ENG_CUDA(cudaMemcpyAsync(h_out_tokens, d_out_tokens, (size_t)T * 4, cudaMemcpyDeviceToHost, stream));
+  ENG_CUDA(cudaMemcpyAsync(h_out_tokens, d_out_tokens, (size_t)(max_batch + T) * 4, cudaMemcpyDeviceToHost, stream));
   ENG_CUDA(cudaEventRecord(ev1, stream));
   ENG_CUDA(cudaEventSynchronize(ev1));
   float ms = 0.f;
@@ -918,6 +935,7 @@ int Engine::decode(int n, const int *slots, uint32_t *out_tokens, int *out_finis
     Sequence &s = seqs[(size_t)slots[i]];
     s.len += 1;  // the consumed token is now in the cache
     out_tokens[i] = h_out_tokens[r];
+    s.last_logprob = reinterpret_cast<const float *>(h_out_tokens + max_batch)[r];
     finish_check(s, h_out_tokens[r]);
     out_finish[i] = s.finish;
   }
@@ -979,6 +997,15 @@ int Engine::last_logits_host(float *host, int rows) {
     ENG_CUDA(cudaMemcpyAsync(host, full_logits, (size_t)rows * m.vocab * 4, cudaMemcpyDeviceToHost, stream));
   }
   ENG_CUDA(cudaStreamSynchronize(stream));
+  return DIS_OK;
+}
+
+int Engine::last_logprobs(int n, const int *slots, float *out) {
+  if (n <= 0 || !slots || !out) return fail(DIS_ERR_INVALID_ARGUMENT, "last_logprobs: bad argument");
+  for (int i = 0; i < n; i++) {
+    if (slots[i] < 0 || slots[i] >= max_batch || !seqs[(size_t)slots[i]].used) return fail(DIS_ERR_INVALID_ARGUMENT, "last_logprobs: no such sequence");
+    out[i] = seqs[(size_t)slots[i]].last_logprob;
+  }
   return DIS_OK;
 }
 

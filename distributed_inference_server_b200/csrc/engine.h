@@ -35,6 +35,7 @@ struct Sequence {
   int cached = 0;          // leading prompt tokens whose K/V came from the prefix cache
   int len = 0;             // tokens whose K/V are in the cache
   uint32_t last_token = 0;  // sampled, not yet in the cache
+  float last_logprob = 0.f; // log-probability of last_token (TokenEvent.logprob)
   int generated = 0;
   int finish = DIS_FINISH_NONE;
   int32_t max_tokens = 0;
@@ -84,6 +85,7 @@ struct Engine {
   float *x = nullptr, *partial = nullptr, *logits = nullptr, *ar_buf = nullptr, *attn_scratch = nullptr;
   float *full_logits = nullptr, *gather_buf = nullptr, *cand_val = nullptr, *cand_val_all = nullptr;
   uint32_t *cand_tok = nullptr, *cand_tok_all = nullptr;
+  float *cand_sum = nullptr, *cand_sum_all = nullptr;  // sum exp(z - max) over the rank's vocabulary slice (logprob)
   uint16_t *xn = nullptr, *q = nullptr, *attn = nullptr, *act = nullptr;
   size_t partial_elems = 0, attn_scratch_elems = 0;
   TmaMap xn_map[4], attn_map[4], act_map[4];  // box rows 32 / 64 / 128 / 256
@@ -154,6 +156,7 @@ struct Engine {
   int prefill(int n, const int *slots, uint32_t *out_tokens, int *out_finish);
   int decode(int n, const int *slots, uint32_t *out_tokens, int *out_finish);
   int last_logits_host(float *host, int rows);
+  int last_logprobs(int n, const int *slots, float *out);
   int status(dis_worker_status *out);
   int prefix_stats(dis_prefix_stats *out);
 

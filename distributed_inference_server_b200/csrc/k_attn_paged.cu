@@ -545,9 +545,7 @@ static cudaError_t attn_launch(const TmaMap &kv_map, long long row0, const AttnR
                                int n_splits, int T, int n_heads, int n_kv, int page_shift, cudaStream_t st) {
   dim3 grid(n_splits, n_kv, T);
   static DeviceOnce once;
-  if (once.first_on_this_device()) {
-    DIS_CUDA_TRY(cudaFuncSetAttribute(attn_paged_kernel<D, G>, cudaFuncAttributeMaxDynamicSharedMemorySize, AttnCfg<D>::kSmemBytes));
-  }
+  DIS_CUDA_TRY(once.run([&] { return cudaFuncSetAttribute(attn_paged_kernel<D, G>, cudaFuncAttributeMaxDynamicSharedMemorySize, AttnCfg<D>::kSmemBytes); }));
   DIS_CUDA_TRY(launch_k(attn_paged_kernel<D, G>, grid, dim3(kAttnThreads), AttnCfg<D>::kSmemBytes, st,
                         *reinterpret_cast<const CUtensorMap *>(&kv_map), row0, rope, q, page_table, max_pages, pt_row, ctx, out,
                         scratch, n_splits, T, n_heads, n_kv, page_shift));
@@ -609,9 +607,7 @@ static cudaError_t prefill_launch(const TmaMap &kv_map, long long row0, const ui
                                   const int *qb_ptrow, uint16_t *out, int n_blocks, int n_heads, int n_kv,
                                   int page_shift, cudaStream_t st) {
   static DeviceOnce once;
-  if (once.first_on_this_device()) {
-    DIS_CUDA_TRY(cudaFuncSetAttribute(attn_prefill_kernel<D, G>, cudaFuncAttributeMaxDynamicSharedMemorySize, AttnCfg<D>::kSmemBytes));
-  }
+  DIS_CUDA_TRY(once.run([&] { return cudaFuncSetAttribute(attn_prefill_kernel<D, G>, cudaFuncAttributeMaxDynamicSharedMemorySize, AttnCfg<D>::kSmemBytes); }));
   return launch_k(attn_prefill_kernel<D, G>, dim3(n_blocks, n_kv), dim3(G * 32), AttnCfg<D>::kSmemBytes, st,
                   *reinterpret_cast<const CUtensorMap *>(&kv_map), row0, q, page_table, max_pages, qb_tok0, qb_len, qb_pos0,
                   qb_ptrow, out, n_heads, n_kv, page_shift);

@@ -281,7 +281,7 @@ __global__ void __launch_bounds__(kSampThreads)
 sample_kernel(const float *__restrict__ logits, long long ld, int V, const float *__restrict__ temperature,
               const float *__restrict__ top_p, const unsigned long long *__restrict__ seeds,
               const unsigned long long *__restrict__ steps, uint32_t *__restrict__ out, int vocab_offset,
-              float *__restrict__ out_val) {
+              float *__restrict__ out_val, float *__restrict__ out_sumexp, float *__restrict__ out_logprob) {
   __shared__ float red[32];
   __shared__ ArgMax red_am[32];
   __shared__ float scan[kSampThreads / 32];
@@ -308,7 +308,20 @@ sample_kernel(const float *__restrict__ logits, long long ld, int V, const float
   __syncthreads();
   am = red_am[0];
   if (temp <= 0.f) {
-    if (threadIdx.x == 0) { out[t] = (uint32_t)(am.i + vocab_offset); if (out_val) out_val[t] = am.v; }
+    // TokenEvent.logprob (crates/core/src/models.rs:276): log softmax(logits)[token].  The argmax element has
+    // z - max = 0, so its log-probability is -log(sum exp(z - max)).  A vocab-parallel rank reports the sum over
+    // its own slice relative to its own max (out_sumexp); the candidate merge combines the slices.
+    float se = 0.f;
+    if (out_sumexp || out_logprob) {
+      for (int i = threadIdx.x; i < V; i += kSampThreads) se += expf(row[i] - am.v);
+      se = block_sum<kSampThreads>(se, red);
+    }
+    if (threadIdx.x == 0) {
+      out[t] = (uint32_t)(am.i + vocab_offset);
+      if (out_val) out_val[t] = am.v;
+      if (out_sumexp) out_sumexp[t] = se;
+      if (out_logprob) out_logprob[t] = -logf(se);
+    }
     return;
   }
 
@@ -385,20 +398,24 @@ sample_kernel(const float *__restrict__ logits, long long ld, int V, const float
     if (tok < 0) tok = am.i;  // rounding left no interval: fall back to the mode
     out[t] = (uint32_t)(tok + vocab_offset);
     if (out_val) out_val[t] = row[tok];
+    // log-probability of the drawn token under softmax(logits / temperature), before the nucleus cut
+    if (out_logprob) out_logprob[t] = row[tok] * inv_t - m - logf(z);
   }
 }
 
 cudaError_t launch_sample(const float *logits, long long ld, int T, int V, const float *temperature,
                           const float *top_p, const unsigned long long *seeds, const unsigned long long *steps,
-                          uint32_t *out_tokens, int vocab_offset, float *out_val, cudaStream_t st) {
+                          uint32_t *out_tokens, int vocab_offset, float *out_val, float *out_sumexp, float *out_logprob,
+                          cudaStream_t st) {
   if (T <= 0) return cudaSuccess;
   return launch_k(sample_kernel, dim3(T), dim3(kSampThreads), 0, st, logits, ld, V, temperature, top_p, seeds, steps, out_tokens,
-                  vocab_offset, out_val);
+                  vocab_offset, out_val, out_sumexp, out_logprob);
 }
 
 // Final step of a vocab-parallel greedy argmax: cand_val/cand_tok are [tp][T] (all-gathered).
 __global__ void argmax_merge_kernel(const float *__restrict__ cand_val, const uint32_t *__restrict__ cand_tok,
-                                    int tp, int T, uint32_t *__restrict__ out) {
+                                    const float *__restrict__ cand_sum, int tp, int T, uint32_t *__restrict__ out,
+                                    float *__restrict__ out_logprob) {
   const int t = blockIdx.x * blockDim.x + threadIdx.x;
   if (t >= T) return;
   float bv = cand_val[t];
@@ -409,12 +426,17 @@ __global__ void argmax_merge_kernel(const float *__restrict__ cand_val, const ui
     if (v > bv || (v == bv && k < bt)) { bv = v; bt = k; }
   }
   out[t] = bt;
+  if (out_logprob && cand_sum) {  // the winner's value is the global max: log p = -log sum_r s_r * exp(m_r - max)
+    float se = 0.f;
+    for (int r = 0; r < tp; r++) se += cand_sum[(size_t)r * T + t] * expf(cand_val[(size_t)r * T + t] - bv);
+    out_logprob[t] = -logf(se);
+  }
 }
 
-cudaError_t launch_argmax_merge(const float *cand_val, const uint32_t *cand_tok, int tp, int T, uint32_t *out,
-                                cudaStream_t st) {
+cudaError_t launch_argmax_merge(const float *cand_val, const uint32_t *cand_tok, const float *cand_sum, int tp, int T,
+                                uint32_t *out, float *out_logprob, cudaStream_t st) {
   if (T <= 0) return cudaSuccess;
-  argmax_merge_kernel<<<(T + 127) / 128, 128, 0, st>>>(cand_val, cand_tok, tp, T, out);
+  argmax_merge_kernel<<<(T + 127) / 128, 128, 0, st>>>(cand_val, cand_tok, cand_sum, tp, T, out, out_logprob);
   return cudaGetLastError();
 }
 

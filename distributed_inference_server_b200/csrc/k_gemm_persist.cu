@@ -342,9 +342,7 @@ static cudaError_t persist_launch(const TmaMap &w_map, const TmaMap &x_map, floa
   using Cfg = PersistCfg<BN, kDual>;
   auto kern = gemm_persist_kernel<BN, kDual>;
   static DeviceOnce once;
-  if (once.first_on_this_device()) {
-    DIS_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
-  }
+  DIS_CUDA_TRY(once.run([&] { return cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes); }));
   static int n_sm = 0;
   if (!n_sm) {
     int dev = 0;
@@ -374,9 +372,7 @@ cudaError_t launch_gemm_persist_silu(const TmaMap &w_map64, const TmaMap &x_map2
   using Cfg = PersistCfg<256, false>;
   constexpr int smem = Cfg::kSmemBytes + kPairXchgBytes;
   static DeviceOnce once;
-  if (once.first_on_this_device()) {
-    DIS_CUDA_TRY(cudaFuncSetAttribute(gemm_persist_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-  }
+  DIS_CUDA_TRY(once.run([&] { return cudaFuncSetAttribute(gemm_persist_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem); }));
   static int n_sm = 0;
   if (!n_sm) {
     int dev = 0;

@@ -245,9 +245,7 @@ static cudaError_t gemm_launch(const TmaMap &w_map, const TmaMap &x_map, float *
   using Cfg = GemmCfg<BN, kDual>;
   auto kern = gemm_tcgen05_kernel<BN, kDual>;
   static DeviceOnce once;
-  if (once.first_on_this_device()) {
-    DIS_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxDynSmem));
-  }
+  DIS_CUDA_TRY(once.run([&] { return cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxDynSmem); }));
   const int num_kb = (K + kBK - 1) / kBK;
   const int per = (num_kb + split_k - 1) / split_k;
   if ((num_kb + per - 1) / per != split_k) { set_last_error("gemm: split_k leaves an empty K slice; use gemm_pick_split_k"); return cudaErrorInvalidValue; }

@@ -33,6 +33,14 @@ __device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t *p) {
   asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
   return v;
 }
+// Every wait on a peer is bounded: a dead peer, or a rank whose step counter has drifted, must fail the launch (the
+// engine then reports unhealthy) instead of hanging the GPU.  2^27 polls of an NVLink-visible word are tens of
+// seconds; no legitimate wait in these kernels is longer than milliseconds.
+__device__ __forceinline__ void wait_flag_sys(const uint32_t *f, uint32_t epoch) {
+  long long spins = 0;
+  while (ld_acquire_sys(f) != epoch)
+    if (++spins > (1ll << 27)) __trap();
+}
 __device__ __forceinline__ float4 ld_volatile_f4(const float *p) {
   float4 v;
   asm volatile("ld.volatile.global.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
@@ -94,7 +102,7 @@ tp_add_rmsnorm_kernel(TpPeers peers, float *__restrict__ x, const float *__restr
   // ---- wait for every peer's row (flags live in THIS rank's memory), one polling thread per source
   if (threadIdx.x < tp && threadIdx.x != me) {
     const uint32_t *f = peers.flags[me] + ((size_t)parity * tp + threadIdx.x) * peers.cap_rows + t;
-    while (ld_acquire_sys(f) != epoch) { }
+    wait_flag_sys(f, epoch);
   }
   __syncthreads();
   // ---- sum in rank order, add the residual
@@ -172,7 +180,7 @@ tp_add_rmsnorm2_kernel(TpPeers peers, float *__restrict__ x, const float *__rest
   if (threadIdx.x < tp && threadIdx.x != me) {
     st_release_sys(peers.flags[threadIdx.x] + flag_me, epoch);
     const uint32_t *f = peers.flags[me] + ((size_t)parity * tp + threadIdx.x) * cap + t;
-    while (ld_acquire_sys(f) != epoch) { }
+    wait_flag_sys(f, epoch);
   }
   __syncthreads();
   // ---- owner: sum in rank order, add the residual, hop 2: the finished block goes to everybody
@@ -195,7 +203,7 @@ tp_add_rmsnorm2_kernel(TpPeers peers, float *__restrict__ x, const float *__rest
   if (threadIdx.x < tp && threadIdx.x != me) {
     st_release_sys(peers.flags[threadIdx.x] + fl2 + flag_me, epoch);
     const uint32_t *f = peers.flags[me] + fl2 + ((size_t)parity * tp + threadIdx.x) * cap + t;
-    while (ld_acquire_sys(f) != epoch) { }
+    wait_flag_sys(f, epoch);
   }
   __syncthreads();
   // ---- full row: own block from shared memory, the others from the AG area; RMSNorm
@@ -359,50 +367,66 @@ cudaError_t launch_tp_add_rmsnorm(const TpPeers &peers, float *x, const float *p
                   xn, step_ptr, idx, parity, H, eps);
 }
 
-// One CTA.  Candidates are pushed into every peer's cand area: [parity][source rank][cap_rows][2] words.
+// One CTA.  Candidates are pushed into every peer's cand area: [parity][source rank][cap_rows][4] words
+// {max bits, token id, sum exp(z - max) over the source's vocabulary slice, unused}.
 __global__ void __launch_bounds__(1024)
 tp_argmax_merge_kernel(TpPeers peers, const float *__restrict__ val, const uint32_t *__restrict__ tok,
-                       const uint32_t *__restrict__ step_ptr, int T, uint32_t *__restrict__ out) {
+                       const float *__restrict__ sumexp, const uint32_t *__restrict__ step_ptr, int T,
+                       uint32_t *__restrict__ out, float *__restrict__ out_logprob) {
   pdl_wait();
   const uint32_t epoch = *step_ptr * 256u + 255u;
   const int parity = (int)(*step_ptr & 1u);  // one merge per forward pass: consecutive passes alternate
   const int t = threadIdx.x, me = peers.rank, tp = peers.tp;
   const size_t base_me = ((size_t)parity * tp + me) * peers.cap_rows;
   if (t < T) {
-    const uint32_t vb = __float_as_uint(val[t]), k = tok[t];
+    const uint4 c = make_uint4(__float_as_uint(val[t]), tok[t], __float_as_uint(sumexp ? sumexp[t] : 0.f), 0u);
     for (int r = 0; r < tp; r++)
-      if (r != me) { peers.cand[r][(base_me + t) * 2 + 0] = vb; peers.cand[r][(base_me + t) * 2 + 1] = k; }
+      if (r != me) *reinterpret_cast<uint4 *>(peers.cand[r] + (base_me + t) * 4) = c;
   }
   __syncthreads();
   if (t == 0) __threadfence_system();
   __syncthreads();
   if (t < tp && t != me) {
     st_release_sys(peers.cand_flags[t] + parity * tp + me, epoch);
-    while (ld_acquire_sys(peers.cand_flags[me] + parity * tp + t) != epoch) { }
+    wait_flag_sys(peers.cand_flags[me] + parity * tp + t, epoch);
   }
   __syncthreads();
   if (t < T) {
     float bv = -INFINITY;
     uint32_t bt = 0xffffffffu;
-    for (int r = 0; r < tp; r++) {
-      uint32_t vb, k;
-      if (r == me) { vb = __float_as_uint(val[t]); k = tok[t]; }
-      else {
-        const volatile uint32_t *c = peers.cand[me] + (((size_t)parity * tp + r) * peers.cap_rows + t) * 2;
-        vb = c[0]; k = c[1];
+    float mv[kTpMaxRanks], sv[kTpMaxRanks];
+#pragma unroll
+    for (int r = 0; r < kTpMaxRanks; r++) {
+      mv[r] = -INFINITY; sv[r] = 0.f;
+      if (r < tp) {
+        uint32_t vb, k, sb;
+        if (r == me) { vb = __float_as_uint(val[t]); k = tok[t]; sb = __float_as_uint(sumexp ? sumexp[t] : 0.f); }
+        else {
+          const volatile uint32_t *c = peers.cand[me] + (((size_t)parity * tp + r) * peers.cap_rows + t) * 4;
+          vb = c[0]; k = c[1]; sb = c[2];
+        }
+        const float v = __uint_as_float(vb);
+        mv[r] = v; sv[r] = __uint_as_float(sb);
+        if (v > bv || (v == bv && k < bt)) { bv = v; bt = k; }
       }
-      const float v = __uint_as_float(vb);
-      if (v > bv || (v == bv && k < bt)) { bv = v; bt = k; }
     }
     out[t] = bt;
+    if (out_logprob) {  // rank order: every rank computes the same bits
+      float se = 0.f;
+#pragma unroll
+      for (int r = 0; r < kTpMaxRanks; r++)
+        if (r < tp) se += sv[r] * expf(mv[r] - bv);
+      out_logprob[t] = -logf(se);
+    }
   }
 }
 
-cudaError_t launch_tp_argmax_merge(const TpPeers &peers, const float *val, const uint32_t *tok, const uint32_t *step_ptr,
-                                   int T, uint32_t *out, cudaStream_t st) {
+cudaError_t launch_tp_argmax_merge(const TpPeers &peers, const float *val, const uint32_t *tok, const float *sumexp,
+                                   const uint32_t *step_ptr, int T, uint32_t *out, float *out_logprob, cudaStream_t st) {
   if (T <= 0) return cudaSuccess;
   if (T > 1024 || T > peers.cap_rows) { set_last_error("tp_argmax_merge: too many rows"); return cudaErrorInvalidValue; }
-  return launch_k(tp_argmax_merge_kernel, dim3(1), dim3((T + 31) / 32 * 32), 0, st, peers, val, tok, step_ptr, T, out);
+  return launch_k(tp_argmax_merge_kernel, dim3(1), dim3((T + 31) / 32 * 32), 0, st, peers, val, tok, sumexp, step_ptr, T, out,
+                  out_logprob);
 }
 
 }  // namespace dis

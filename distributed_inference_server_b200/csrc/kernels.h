@@ -21,16 +21,17 @@ cudaError_t launch_rope_kv_write(const float *qkv, int n_partial, long long part
                                  int n_heads, int n_kv, int d, int page_size, cudaStream_t st);
 cudaError_t launch_sample(const float *logits, long long ld, int T, int V, const float *temperature,
                           const float *top_p, const unsigned long long *seeds, const unsigned long long *steps,
-                          uint32_t *out_tokens, int vocab_offset, float *out_val, cudaStream_t st);
-cudaError_t launch_argmax_merge(const float *cand_val, const uint32_t *cand_tok, int tp, int T, uint32_t *out,
-                                cudaStream_t st);
+                          uint32_t *out_tokens, int vocab_offset, float *out_val, float *out_sumexp, float *out_logprob,
+                          cudaStream_t st);
+cudaError_t launch_argmax_merge(const float *cand_val, const uint32_t *cand_tok, const float *cand_sum, int tp, int T,
+                                uint32_t *out, float *out_logprob, cudaStream_t st);
 cudaError_t launch_synth_bf16(uint16_t *dst, size_t n, unsigned long long seed, int kind, int layer, float amp,
                               float offset, size_t idx0, size_t row_len, size_t src_ld, size_t src_col0,
                               cudaStream_t st);
 cudaError_t launch_bf16_to_f32(const uint16_t *src, float *dst, size_t n, cudaStream_t st);
 
 // k_tp.cu : exchange over peer memory.  Every rank owns one symmetric allocation:
-//   data [2 parities][tp sources][cap_rows][H] fp32 | flags [2 hops][2][tp][cap_rows] u32 | cand [2][tp][cap_rows][2] u32 |
+//   data [2 parities][tp sources][cap_rows][H] fp32 | flags [2 hops][2][tp][cap_rows] u32 | cand [2][tp][cap_rows][4] u32 |
 //   cand_flags [2][tp] u32     (peers PUSH into the slot of their own rank; the owner polls and reads locally)
 // two_shot: the data area is used as a reduce-scatter area + an all-gather area instead (see k_tp.cu); the
 // flag-in-data variant needs 8 * cap_rows * H floats of it.
@@ -46,8 +47,8 @@ struct TpPeers {
 cudaError_t launch_tp_add_rmsnorm(const TpPeers &peers, float *x, const float *partial, int n_partial,
                                   long long partial_stride, const float *gain, uint16_t *xn, const uint32_t *step_ptr,
                                   uint32_t idx, int parity, int T, int H, float eps, cudaStream_t st);
-cudaError_t launch_tp_argmax_merge(const TpPeers &peers, const float *val, const uint32_t *tok, const uint32_t *step_ptr,
-                                   int T, uint32_t *out, cudaStream_t st);
+cudaError_t launch_tp_argmax_merge(const TpPeers &peers, const float *val, const uint32_t *tok, const float *sumexp,
+                                   const uint32_t *step_ptr, int T, uint32_t *out, float *out_logprob, cudaStream_t st);
 
 // k_gemv.cu : out[t][n] = sum_k X[t][k] W[n][k]  (T <= kGemvMaxT per launch; launcher loops)
 constexpr int kGemvMaxT = 4;

@@ -23,8 +23,15 @@
 
 namespace {
 
+// RequestID = Uuid (crates/core/src/types.rs:7): 16 opaque bytes, compared bytewise
+struct ReqId {
+  uint8_t b[16];
+  bool operator==(const ReqId &o) const { return memcmp(b, o.b, 16) == 0; }
+};
+static ReqId make_id(const uint8_t *p) { ReqId r; memcpy(r.b, p, 16); return r; }
+
 struct Queued {
-  uint64_t id;
+  ReqId id;
   int priority;
   double enqueued_at;
   std::vector<uint32_t> prompt;
@@ -64,6 +71,13 @@ class RequestQueue {
     }
     update();
   }
+  // a queued request whose client went away (requirements.md:85)
+  bool remove(const ReqId &id, Queued *out) {
+    for (auto &q : lanes_)
+      for (size_t i = 0; i < q.size(); i++)
+        if (q[i].id == id) { *out = std::move(q[i]); q.erase(q.begin() + (long)i); update(); return true; }
+    return false;
+  }
   size_t total() const { return lanes_[0].size() + lanes_[1].size() + lanes_[2].size(); }
   size_t depth(int p) const { return lanes_[p].size(); }
   bool accepting() const { return !backpressure_; }
@@ -86,7 +100,7 @@ double steady_now() {
 }
 
 struct Active {
-  uint64_t id;
+  ReqId id;
   int32_t slot;
   int32_t produced;
   int32_t prompt_tokens;
@@ -109,12 +123,13 @@ struct dis_serving {
   explicit dis_serving(const dis_queue_config &c) : cfg(c), queue(c) {}
 };
 
-static void emit(dis_serving *s, uint64_t id, int kind, uint32_t token, int32_t index, int32_t finish, int32_t prompt_tokens,
-                 double waited_ms) {
+static void emit(dis_serving *s, const ReqId &id, int kind, uint32_t token, int32_t index, int32_t finish, int32_t prompt_tokens,
+                 double waited_ms, float logprob = 0.f) {
   dis_serving_event e;
   memset(&e, 0, sizeof(e));
-  e.request_id = id; e.kind = kind; e.token = token; e.index = index; e.finish_reason = finish;
-  e.prompt_tokens = prompt_tokens; e.waited_ms = waited_ms;
+  memcpy(e.request_id, id.b, 16);
+  e.kind = kind; e.token = token; e.index = index; e.finish_reason = finish;
+  e.prompt_tokens = prompt_tokens; e.waited_ms = waited_ms; e.logprob = logprob;
   s->pending.push_back(e);
 }
 
@@ -142,12 +157,12 @@ int dis_serving_destroy(dis_serving *s) {
 
 const char *dis_serving_last_error(dis_serving *s) { return s ? s->last_error.c_str() : ""; }
 
-int dis_serving_submit_at(dis_serving *s, uint64_t request_id, const uint32_t *prompt, int32_t n_prompt,
+int dis_serving_submit_at(dis_serving *s, const uint8_t request_id[16], const uint32_t *prompt, int32_t n_prompt,
                           const dis_sampling_params *params, int32_t priority, double now_s) {
-  if (!s || !prompt || n_prompt <= 0 || !params) return DIS_ERR_INVALID_ARGUMENT;
+  if (!s || !request_id || !prompt || n_prompt <= 0 || !params) return DIS_ERR_INVALID_ARGUMENT;
   std::lock_guard<std::mutex> lk(s->mu);
   Queued q;
-  q.id = request_id; q.priority = priority; q.enqueued_at = now_s;
+  q.id = make_id(request_id); q.priority = priority; q.enqueued_at = now_s;
   q.prompt.assign(prompt, prompt + n_prompt);
   q.params = *params;
   size_t off = 0;
@@ -161,7 +176,7 @@ int dis_serving_submit_at(dis_serving *s, uint64_t request_id, const uint32_t *p
   return DIS_OK;
 }
 
-int dis_serving_submit(dis_serving *s, uint64_t request_id, const uint32_t *prompt, int32_t n_prompt,
+int dis_serving_submit(dis_serving *s, const uint8_t request_id[16], const uint32_t *prompt, int32_t n_prompt,
                        const dis_sampling_params *params, int32_t priority) {
   return dis_serving_submit_at(s, request_id, prompt, n_prompt, params, priority, steady_now());
 }
@@ -180,13 +195,36 @@ int dis_serving_depth(dis_serving *s, dis_queue_depth *out) {
 
 // Queue-only helper (tests of the admission order without an engine): pops up to `max` requests in
 // scheduling order and returns their ids.
-int dis_serving_debug_pop(dis_serving *s, int32_t max, uint64_t *ids, int32_t *n) {
+int dis_serving_debug_pop(dis_serving *s, int32_t max, uint8_t *ids /* [max][16] */, int32_t *n) {
   if (!s || !ids || !n) return DIS_ERR_INVALID_ARGUMENT;
   std::lock_guard<std::mutex> lk(s->mu);
   *n = 0;
   Queued q;
-  while (*n < max && s->queue.pop(&q)) ids[(*n)++] = q.id;
+  while (*n < max && s->queue.pop(&q)) { memcpy(ids + (size_t)*n * 16, q.id.b, 16); (*n)++; }
   return DIS_OK;
+}
+
+// The client of a request went away (requirements.md:85): a queued request leaves the queue, a running one gives
+// its slot and KV pages back at once.  Either way one DONE event with FinishReason::Stop closes the stream.
+int dis_serving_cancel(dis_serving *s, const uint8_t request_id[16]) {
+  if (!s || !request_id) return DIS_ERR_INVALID_ARGUMENT;
+  std::lock_guard<std::mutex> lk(s->mu);
+  const ReqId id = make_id(request_id);
+  Queued q;
+  if (s->queue.remove(id, &q)) {
+    emit(s, id, DIS_EVENT_DONE, 0, 0, DIS_FINISH_STOP, (int32_t)q.prompt.size(), 0.0);
+    return DIS_OK;
+  }
+  for (size_t i = 0; i < s->active.size(); i++)
+    if (s->active[i].id == id) {
+      const Active a = s->active[i];
+      if (s->eng) dis_engine_seq_remove(s->eng, a.slot);
+      s->active.erase(s->active.begin() + (long)i);
+      emit(s, id, DIS_EVENT_DONE, 0, a.produced, DIS_FINISH_STOP, a.prompt_tokens, 0.0);
+      return DIS_OK;
+    }
+  s->last_error = "cancel: no such request";
+  return DIS_ERR_INVALID_ARGUMENT;
 }
 
 static int drain(dis_serving *s, dis_serving_event *events, int32_t cap, int32_t *n_events) {
@@ -195,7 +233,7 @@ static int drain(dis_serving *s, dis_serving_event *events, int32_t cap, int32_t
   return DIS_OK;
 }
 
-int dis_serving_step_at(dis_serving *s, double now_s, dis_serving_event *events, int32_t cap, int32_t *n_events) {
+static int step_impl(dis_serving *s, double now_s, bool clock_injected, dis_serving_event *events, int32_t cap, int32_t *n_events) {
   if (!s || !events || !n_events || cap <= 0) return DIS_ERR_INVALID_ARGUMENT;
   std::lock_guard<std::mutex> lk(s->mu);
   if (!s->pending.empty()) return drain(s, events, cap, n_events);  // deliver what is owed first
@@ -239,7 +277,11 @@ int dis_serving_step_at(dis_serving *s, double now_s, dis_serving_event *events,
         dis_engine_seq_remove(s->eng, a.slot);
         continue;
       }
-      emit(s, a.id, DIS_EVENT_TOKEN, toks[i], a.produced, fin[i], a.prompt_tokens, a.produced == 0 ? (steady_now() - a.enqueued_at) * 1e3 : 0.0);
+      float lp = 0.f;
+      dis_engine_last_logprobs(s->eng, 1, &a.slot, &lp);
+      // under the injected clock of the *_at variants the step's own duration is not visible: TTFT = time queued
+      const double t_first = clock_injected ? now_s : steady_now();
+      emit(s, a.id, DIS_EVENT_TOKEN, toks[i], a.produced, fin[i], a.prompt_tokens, a.produced == 0 ? (t_first - a.enqueued_at) * 1e3 : 0.0, lp);
       a.produced++;
       if (fin[i] != DIS_FINISH_NONE) {
         emit(s, a.id, DIS_EVENT_DONE, 0, a.produced, fin[i], a.prompt_tokens, 0.0);
@@ -254,7 +296,15 @@ int dis_serving_step_at(dis_serving *s, double now_s, dis_serving_event *events,
     std::vector<uint32_t> toks(fresh.size());
     for (auto &a : fresh) slots.push_back(a.slot);
     const int rc = dis_engine_prefill(s->eng, (int32_t)slots.size(), slots.data(), toks.data(), fin.data());
-    if (rc != DIS_OK) { s->last_error = dis_engine_last_error(s->eng); for (auto &a : fresh) dis_engine_seq_remove(s->eng, a.slot); return rc; }
+    if (rc != DIS_OK) {
+      // the step failed as a whole: every newcomer gets its DONE/FAILED event, so no request id vanishes
+      s->last_error = dis_engine_last_error(s->eng);
+      for (auto &a : fresh) {
+        dis_engine_seq_remove(s->eng, a.slot);
+        emit(s, a.id, DIS_EVENT_DONE, 0, 0, DIS_FINISH_FAILED, a.prompt_tokens, (now_s - a.enqueued_at) * 1e3);
+      }
+      return rc;
+    }
     retire(fresh, toks, fin);
     s->active.insert(s->active.end(), fresh.begin(), fresh.end());
     s->decode_next = true;
@@ -271,8 +321,11 @@ int dis_serving_step_at(dis_serving *s, double now_s, dis_serving_event *events,
   return drain(s, events, cap, n_events);
 }
 
+int dis_serving_step_at(dis_serving *s, double now_s, dis_serving_event *events, int32_t cap, int32_t *n_events) {
+  return step_impl(s, now_s, true, events, cap, n_events);
+}
 int dis_serving_step(dis_serving *s, dis_serving_event *events, int32_t cap, int32_t *n_events) {
-  return dis_serving_step_at(s, steady_now(), events, cap, n_events);
+  return step_impl(s, steady_now(), false, events, cap, n_events);
 }
 
 }  // extern "C"

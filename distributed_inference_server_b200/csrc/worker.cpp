@@ -111,9 +111,9 @@ BatchResult InferenceWorker::infer(const InferenceBatch &batch, const TokenSink 
   }
   std::vector<uint32_t> toks(n * max_new, 0);
   struct Ctx { const TokenSink *sink; } ctx{&sink};
-  auto tramp = [](void *user, int32_t idx, uint32_t tok, int32_t index, int32_t fin) -> int {
+  auto tramp = [](void *user, int32_t idx, uint32_t tok, int32_t index, int32_t fin, float logprob) -> int {
     const TokenSink &s = *static_cast<Ctx *>(user)->sink;
-    return s((size_t)idx, tok, (size_t)index, fin != DIS_FINISH_NONE) ? 0 : 1;
+    return s((size_t)idx, tok, (size_t)index, fin != DIS_FINISH_NONE, logprob) ? 0 : 1;
   };
   dis_batch_result br;
   const int rc = dis_worker_infer(eng_, (int32_t)n, ids.data(), (int32_t)stride, lens.data(), params.data(), toks.data(),
@@ -165,7 +165,9 @@ extern "C" int dis_worker_infer(dis_engine *e, int32_t n, const uint32_t *input_
   if (rc != DIS_OK) { cleanup(); return rc; }
   std::vector<uint32_t> toks(live_idx.size());
   std::vector<int32_t> fin(live_idx.size());
+  std::vector<float> lps(live_idx.size());
   auto deliver = [&]() {
+    if (on_token && !live_slot.empty()) dis_engine_last_logprobs(e, (int32_t)live_slot.size(), live_slot.data(), lps.data());
     std::vector<int32_t> ni, ns;
     for (size_t k = 0; k < live_idx.size(); k++) {
       const int32_t i = live_idx[k];
@@ -176,7 +178,7 @@ extern "C" int dis_worker_infer(dis_engine *e, int32_t n, const uint32_t *input_
         out_lens[i]++;
         generated++;
         out_finish[i] = fin[k];
-        if (on_token && on_token(user, i, toks[k], out_lens[i] - 1, fin[k]) != 0 && fin[k] == DIS_FINISH_NONE) {
+        if (on_token && on_token(user, i, toks[k], out_lens[i] - 1, fin[k], lps[k]) != 0 && fin[k] == DIS_FINISH_NONE) {
           out_finish[i] = DIS_FINISH_STOP;  // dropped by the host
           keep = false;
         }

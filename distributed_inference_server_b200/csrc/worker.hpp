@@ -89,9 +89,9 @@ struct WorkerConfig {  // design.md:316-322 + the fields a GPU engine needs
   const uint8_t *nccl_id = nullptr;
 };
 
-// Called once per generated token (TokenEvent::Token, models.rs:272-277).  Return false to drop the
-// request (client disconnected, requirements.md:85).
-using TokenSink = std::function<bool(size_t request_index, uint32_t token, size_t index, bool finished)>;
+// Called once per generated token (TokenEvent::Token{token, index, logprob}, models.rs:272-277).  Return false
+// to drop the request (client disconnected, requirements.md:85).
+using TokenSink = std::function<bool(size_t request_index, uint32_t token, size_t index, bool finished, float logprob)>;
 
 class InferenceWorker {
  public:

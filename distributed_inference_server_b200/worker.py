@@ -258,6 +258,13 @@ class Engine:
         self._check(self.lib.dis_engine_replay_last_step(self.h, int(n), C.byref(ms)))
         return float(ms.value)
 
+    def last_logprobs(self, slots) -> np.ndarray:
+        """TokenEvent.logprob of the token each listed sequence got from its latest prefill/decode call."""
+        s = np.ascontiguousarray(slots, dtype=np.int32)
+        out = np.zeros(len(s), np.float32)
+        self._check(self.lib.dis_engine_last_logprobs(self.h, len(s), s.ctypes.data, out.ctypes.data))
+        return out
+
     def last_logits(self, n_rows: int) -> np.ndarray:
         out = np.empty((n_rows, self.vocab), np.float32)
         self._check(self.lib.dis_engine_last_logits(self.h, out.ctypes.data, n_rows))
@@ -328,9 +335,11 @@ class InferenceWorker:
         return self.config.model
 
     def infer(self, batch: InferenceBatch,
-              on_token: Optional[Callable[[int, int, int, bool], bool]] = None) -> BatchResult:
+              on_token: Optional[Callable[..., bool]] = None) -> BatchResult:
         """Run a padded batch to completion.  N requests in -> N results out (design.md:806-810); a
-        request that cannot be served is marked failed without failing the batch (design.md:812-816)."""
+        request that cannot be served is marked failed without failing the batch (design.md:812-816).
+        on_token(request_index, token, index, finished[, logprob]) is TokenEvent::Token (models.rs:272-277); a
+        callback that takes five arguments also receives the token's log-probability."""
         if self._shutdown:
             raise WorkerError(WorkerError.Shutdown)
         if self.engine is None:
@@ -368,8 +377,15 @@ class InferenceWorker:
         res = B.BatchResult()
         cb = None
         if on_token is not None:
-            def _cb(_user, idx, tok, index, f):
-                return 0 if on_token(idx, tok, index, f != B.FINISH_NONE) else 1
+            import inspect
+            try:
+                want_lp = len(inspect.signature(on_token).parameters) >= 5
+            except (TypeError, ValueError):
+                want_lp = False
+
+            def _cb(_user, idx, tok, index, f, lp):
+                args = (idx, tok, index, f != B.FINISH_NONE) + ((lp,) if want_lp else ())
+                return 0 if on_token(*args) else 1
             cb = B.TOKEN_CALLBACK(_cb)
         eng = self.engine
         rc = eng.lib.dis_worker_infer(eng.h, n, ids.ctypes.data, stride, lens.ctypes.data, params, toks.ctypes.data,
@@ -405,6 +421,20 @@ class ContinuousBatcher:
         if rc != B.OK:
             raise ValueError("dis_serving_create: bad queue configuration")
         self._events = (B.ServingEvent * 1024)()
+        self._ids = {}  # 16-byte wire id -> the object the caller submitted (int, uuid.UUID or bytes)
+
+    def _wire_id(self, request_id) -> bytes:
+        """RequestID is a Uuid (crates/core/src/types.rs:7): 16 bytes on the wire.  Ints are accepted for tests."""
+        if isinstance(request_id, uuid.UUID):
+            b = request_id.bytes
+        elif isinstance(request_id, (bytes, bytearray)):
+            b = bytes(request_id)
+            if len(b) != 16:
+                raise ValueError("request id must be 16 bytes")
+        else:
+            b = int(request_id).to_bytes(16, "little")
+        self._ids.setdefault(b, request_id)
+        return b
 
     def close(self):
         if getattr(self, "h", None):
@@ -417,18 +447,23 @@ class ContinuousBatcher:
         except Exception:
             pass
 
-    def submit(self, request_id: int, prompt: Sequence[int], params: InferenceParams, priority: int = B.PRIORITY_NORMAL,
+    def submit(self, request_id, prompt: Sequence[int], params: InferenceParams, priority: int = B.PRIORITY_NORMAL,
                now: Optional[float] = None) -> None:
         p = np.ascontiguousarray(prompt, dtype=np.uint32)
         sp, keep = _sampling(params)
+        rid = self._wire_id(request_id)
         if now is None:
-            rc = self.lib.dis_serving_submit(self.h, request_id, p.ctypes.data, len(p), C.byref(sp), priority)
+            rc = self.lib.dis_serving_submit(self.h, rid, p.ctypes.data, len(p), C.byref(sp), priority)
         else:
-            rc = self.lib.dis_serving_submit_at(self.h, request_id, p.ctypes.data, len(p), C.byref(sp), priority, now)
+            rc = self.lib.dis_serving_submit_at(self.h, rid, p.ctypes.data, len(p), C.byref(sp), priority, now)
         if rc == B.ERR_QUEUE_FULL:
             raise QueueFull()
         if rc != B.OK:
             raise WorkerError(_KIND.get(rc, WorkerError.InferenceFailed), "submit")
+
+    def cancel(self, request_id) -> bool:
+        """Client disconnect (requirements.md:85); False if the request is neither queued nor running."""
+        return self.lib.dis_serving_cancel(self.h, self._wire_id(request_id)) == B.OK
 
     def step(self, now: Optional[float] = None):
         """One scheduler iteration; returns the list of events it produced."""
@@ -439,8 +474,9 @@ class ContinuousBatcher:
             rc = self.lib.dis_serving_step_at(self.h, now, self._events, len(self._events), C.byref(n))
         if rc != B.OK:
             raise WorkerError(_KIND.get(rc, WorkerError.InferenceFailed), self.lib.dis_serving_last_error(self.h).decode())
-        return [(e.request_id, e.kind, e.token, e.index, e.finish_reason, e.prompt_tokens, e.waited_ms)
-                for e in self._events[:n.value]]
+        self.last_logprobs = [e.logprob for e in self._events[:n.value]]  # parallel to the returned list
+        return [(self._ids.get(bytes(e.request_id), bytes(e.request_id)), e.kind, e.token, e.index, e.finish_reason,
+                 e.prompt_tokens, e.waited_ms) for e in self._events[:n.value]]
 
     def depth(self) -> B.QueueDepth:
         d = B.QueueDepth()
@@ -448,10 +484,11 @@ class ContinuousBatcher:
         return d
 
     def debug_pop(self, max_count: int):
-        ids = (C.c_uint64 * max_count)()
+        ids = (C.c_uint8 * (16 * max_count))()
         n = C.c_int32(0)
         self.lib.dis_serving_debug_pop(self.h, max_count, ids, C.byref(n))
-        return list(ids[:n.value])
+        raw = bytes(ids)
+        return [self._ids.get(raw[16 * i:16 * i + 16], raw[16 * i:16 * i + 16]) for i in range(n.value)]
 
     def run_until_idle(self, max_steps: int = 1_000_000):
         """Drive the scheduler until queue and engine are empty; returns {request_id: (tokens, finish_reason)}."""

@@ -31,7 +31,7 @@ extern "C" {
 #endif
 
 #define DIS_API __attribute__((visibility("default")))
-#define DIS_ABI_VERSION 1
+#define DIS_ABI_VERSION 2 /* 2: 16-byte request ids, logprob on token events / callback, dis_serving_cancel */
 
 /* ---- status codes: WorkerError, crates/core/src/error.rs:115-128 ------------------------------ */
 typedef enum dis_status {
@@ -166,8 +166,14 @@ DIS_API int dis_engine_profile_decode(dis_engine *e, int32_t n, const int32_t *s
  * launch, token read-back, the caller's own work). */
 DIS_API int dis_engine_replay_last_step(dis_engine *e, int32_t n, float *avg_ms);
 /* Logits of the last prefill/decode call, row i = i-th listed sequence, [n][vocab] fp32 (gathered
- * across tensor-parallel ranks). For parity tests and TokenEvent.logprob (models.rs:276). */
+ * across tensor-parallel ranks). For parity tests. */
 DIS_API int dis_engine_last_logits(dis_engine *e, float *host, int32_t n_rows);
+/* TokenEvent.logprob (crates/core/src/models.rs:272-277): the log-probability of the token each listed sequence
+ * received from its most recent prefill/decode call, computed by the sampler kernel and copied back with the token
+ * ids (no logits leave the device).  Greedy (temperature 0): log softmax(logits)[token]; sampled: the same under
+ * softmax(logits / temperature), before the nucleus cut.  Under tensor parallelism the vocabulary slices' (max,
+ * sum-exp) pairs are merged with the candidates. */
+DIS_API int dis_engine_last_logprobs(dis_engine *e, int32_t n, const int32_t *slots, float *out_logprobs);
 
 /* ---- InferenceWorker::status / model_info (design.md:340-341) ---------------------------------- */
 DIS_API int dis_engine_status(dis_engine *e, dis_worker_status *out);
@@ -188,9 +194,9 @@ DIS_API int dis_engine_tp_import(dis_engine *e, const uint8_t *handles /* [tp_si
  * padded [n][stride] batch of InferenceBatch (design.md:244), lens[b] the unpadded length
  * (BatchedRequest.original_length, design.md:261).  out_tokens is [n][max_new_cap].
  * on_token (optional) is called once per generated token, in step order, from the calling thread
- * (TokenEvent::Token, models.rs:272-277); returning non-zero drops that sequence. */
+ * (TokenEvent::Token{token, index, logprob}, models.rs:272-277); returning non-zero drops that sequence. */
 typedef int (*dis_token_callback)(void *user, int32_t request_index, uint32_t token, int32_t index,
-                                  int32_t finish_reason);
+                                  int32_t finish_reason, float logprob);
 typedef struct dis_batch_result {
   double inference_ms;          /* BatchResult.inference_time  design.md:348 */
   double ttft_ms;               /* time to first token of the batch (prefill) */
@@ -220,26 +226,30 @@ typedef struct dis_queue_config {
 typedef struct dis_queue_depth { int32_t high, normal, low, total, accepting, active; } dis_queue_depth;
 typedef enum dis_event_kind { DIS_EVENT_TOKEN = 0, DIS_EVENT_DONE = 1, DIS_EVENT_EXPIRED = 2 } dis_event_kind;
 typedef struct dis_serving_event {
-  uint64_t request_id;
+  uint8_t request_id[16]; /* RequestID = Uuid (crates/core/src/types.rs:7): 16 opaque bytes, as submitted */
   int32_t kind;           /* dis_event_kind */
   uint32_t token;         /* TOKEN */
   int32_t index;          /* TOKEN: position in the completion; DONE: completion_tokens (Usage, models.rs:9-23) */
   int32_t finish_reason;  /* dis_finish_reason; DIS_FINISH_NONE on a token that does not end the request */
   int32_t prompt_tokens;
   double waited_ms;       /* first TOKEN: time from submit to first token (TTFT); EXPIRED: time spent queued */
+  float logprob;          /* TOKEN: TokenEvent.logprob (models.rs:276), see dis_engine_last_logprobs */
 } dis_serving_event;
 typedef struct dis_serving dis_serving;
 DIS_API int dis_serving_create(dis_engine *engine, const dis_queue_config *cfg, int32_t max_active, dis_serving **out);
 DIS_API int dis_serving_destroy(dis_serving *s);
 DIS_API const char *dis_serving_last_error(dis_serving *s);
-DIS_API int dis_serving_submit(dis_serving *s, uint64_t request_id, const uint32_t *prompt, int32_t n_prompt,
+DIS_API int dis_serving_submit(dis_serving *s, const uint8_t request_id[16], const uint32_t *prompt, int32_t n_prompt,
                                const dis_sampling_params *params, int32_t priority);
-DIS_API int dis_serving_submit_at(dis_serving *s, uint64_t request_id, const uint32_t *prompt, int32_t n_prompt,
+DIS_API int dis_serving_submit_at(dis_serving *s, const uint8_t request_id[16], const uint32_t *prompt, int32_t n_prompt,
                                   const dis_sampling_params *params, int32_t priority, double now_s);
+/* Client disconnect (requirements.md:85): a queued request leaves the queue, a running one frees its slot and KV
+ * pages; one DONE event with DIS_FINISH_STOP follows.  DIS_ERR_INVALID_ARGUMENT if the id is neither queued nor running. */
+DIS_API int dis_serving_cancel(dis_serving *s, const uint8_t request_id[16]);
 DIS_API int dis_serving_step(dis_serving *s, dis_serving_event *events, int32_t cap, int32_t *n_events);
 DIS_API int dis_serving_step_at(dis_serving *s, double now_s, dis_serving_event *events, int32_t cap, int32_t *n_events);
 DIS_API int dis_serving_depth(dis_serving *s, dis_queue_depth *out);
-DIS_API int dis_serving_debug_pop(dis_serving *s, int32_t max, uint64_t *ids, int32_t *n);
+DIS_API int dis_serving_debug_pop(dis_serving *s, int32_t max, uint8_t *ids /* [max][16] */, int32_t *n);
 
 /* ---- prefix KV reuse -------------------------------------------------------- *
  * The spec's KVCacheManager (design.md:363-413) caches K/V per token sequence as host Vec<f32> and hands the
@@ -343,10 +353,11 @@ DIS_API int dis_k_attn_prefill(const uint16_t *q, const uint16_t *kv_pool, int64
                                const int32_t *qb_pos0, const int32_t *qb_ptrow, uint16_t *out, int32_t n_blocks,
                                int32_t n_heads, int32_t n_kv, int32_t d, int32_t page_size, void *stream);
 /* Sampler over fp32 logits [T][V] (row stride ld): temperature 0 -> argmax, lowest index wins ties;
- * else nucleus sampling as oracle/llama_oracle.c states it.  out_tokens[T]. */
+ * else nucleus sampling as oracle/llama_oracle.c states it.  out_tokens[T]; out_logprob[T] (may be NULL) receives
+ * the chosen token's log-probability (see dis_engine_last_logprobs). */
 DIS_API int dis_k_sample(const float *logits, int64_t ld, int32_t T, int32_t V, const float *temperature,
                          const float *top_p, const uint64_t *seeds, const uint64_t *steps,
-                         uint32_t *out_tokens, void *stream);
+                         uint32_t *out_tokens, float *out_logprob, void *stream);
 /* Synthetic weights: dst[i] = bf16(offset + (2u-1)*amp), u from the counter hash (seed, kind, layer, i). */
 DIS_API int dis_k_synth_bf16(uint16_t *dst, size_t n, uint64_t seed, int32_t kind, int32_t layer, float amp,
                              float offset, void *stream);

@@ -27,19 +27,22 @@ def test_library_exports_every_declared_symbol():
     for n in names:
         assert hasattr(lib, n), n
         assert n in B.PROTOTYPES, f"binding.py lacks a prototype for {n}"
-    assert lib.dis_abi_version() == 1
+    assert lib.dis_abi_version() == 2
 
 
 def test_struct_layout_matches_header(tmp_path):
     probe = tmp_path / "probe.c"
-    probe.write_text('#include <stdio.h>\n#include "dis_engine.h"\nint main(){printf("%zu %zu %zu %zu %zu %zu\\n",'
+    probe.write_text('#include <stdio.h>\n#include "dis_engine.h"\nint main(){printf("%zu %zu %zu %zu %zu %zu %zu %zu %zu\\n",'
                      'sizeof(dis_model_config),sizeof(dis_engine_config),sizeof(dis_sampling_params),'
-                     'sizeof(dis_worker_status),sizeof(dis_batch_result),offsetof(dis_engine_config,nccl_id));return 0;}\n')
+                     'sizeof(dis_worker_status),sizeof(dis_batch_result),offsetof(dis_engine_config,nccl_id),'
+                     'sizeof(dis_serving_event),offsetof(dis_serving_event,kind),offsetof(dis_serving_event,logprob));return 0;}\n')
     exe = tmp_path / "probe"
     subprocess.run(["gcc", "-I", os.path.join(ROOT, "include"), str(probe), "-o", str(exe)], check=True)
     sizes = [int(x) for x in subprocess.run([str(exe)], capture_output=True, text=True, check=True).stdout.split()]
     assert sizes == [C.sizeof(B.ModelConfig), C.sizeof(B.EngineConfig), C.sizeof(B.SamplingParams),
-                     C.sizeof(B.WorkerStatus), C.sizeof(B.BatchResult), B.EngineConfig.nccl_id.offset]
+                     C.sizeof(B.WorkerStatus), C.sizeof(B.BatchResult), B.EngineConfig.nccl_id.offset,
+                     C.sizeof(B.ServingEvent), B.ServingEvent.kind.offset, B.ServingEvent.logprob.offset]
+    assert B.ServingEvent.kind.offset == 16           # RequestID = Uuid, 16 bytes (crates/core/src/types.rs:7)
 
 
 def test_header_is_plain_c():

@@ -380,11 +380,16 @@ def test_sampler_argmax_and_ties():
     lg[2, V - 1] = 11.0            # last element
     lg[3, 0] = 11.0                # first element
     out = torch.zeros(T, dtype=torch.int32, device=DEV)
-    check(lib().dis_k_sample(ptr(dev_f32(lg)), V, T, V, None, None, None, None, ptr(out), None))
+    lp = torch.zeros(T, dtype=torch.float32, device=DEV)
+    check(lib().dis_k_sample(ptr(dev_f32(lg)), V, T, V, None, None, None, None, ptr(out), ptr(lp), None))
     sync()
     ref = [O.argmax(lg[t])[0] for t in range(T)]
     assert out.cpu().tolist() == ref
     assert ref[1] == 500
+    # TokenEvent.logprob (models.rs:276): log softmax(logits)[token], against float64 numpy
+    z = lg.astype(np.float64)
+    want = z[np.arange(T), ref] - (np.log(np.exp(z - z.max(1, keepdims=True)).sum(1)) + z.max(1))
+    assert np.abs(lp.cpu().numpy() - want).max() <= 1e-4
 
 
 @pytest.mark.parametrize("T,V", [(48, 4099), (24, 128256)], ids=["ragged-vocab", "llama3-vocab"])
@@ -398,9 +403,15 @@ def test_sampler_top_p_matches_oracle(T, V):
     out = torch.zeros(T, dtype=torch.int32, device=DEV)
     ds = torch.from_numpy(seeds.view(np.int64)).to(DEV)
     dst = torch.from_numpy(steps.view(np.int64)).to(DEV)
-    check(lib().dis_k_sample(ptr(dev_f32(lg)), V, T, V, ptr(dev_f32(temps)), ptr(dev_f32(tps)), ptr(ds), ptr(dst), ptr(out), None))
+    lp = torch.zeros(T, dtype=torch.float32, device=DEV)
+    check(lib().dis_k_sample(ptr(dev_f32(lg)), V, T, V, ptr(dev_f32(temps)), ptr(dev_f32(tps)), ptr(ds), ptr(dst), ptr(out), ptr(lp), None))
     sync()
     got = out.cpu().tolist()
+    # log-probability of the drawn token under softmax(logits / temperature) (temperature 0: the plain softmax)
+    for t in range(T):
+        z = lg[t].astype(np.float64) / (float(temps[t]) if temps[t] > 0 else 1.0)
+        want = z[got[t]] - (np.log(np.exp(z - z.max()).sum()) + z.max())
+        assert abs(float(lp[t]) - want) <= 1e-3 * max(1.0, abs(want)), (t, float(lp[t]), want)
     mism = 0
     for t in range(T):
         ref, tau, mass = O.sample(lg[t], float(temps[t]), float(tps[t]), int(seeds[t]), int(steps[t]))

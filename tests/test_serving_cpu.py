@@ -88,3 +88,19 @@ def test_property8_timeout(arrivals, timeout, now):
     assert q.depth().total == len(arrivals) - len(want)
     for e in events:
         assert e[4] == B.FINISH_FAILED and e[5] == 2 and e[6] >= timeout * 1e3 - 1e-6
+
+
+def test_request_ids_are_16_byte_uuids_and_cancel_removes_a_queued_request():
+    """RequestID is a Uuid (crates/core/src/types.rs:7): ids cross the boundary as 16 bytes and come back unchanged;
+    a client that disconnects while queued (requirements.md:85) leaves the queue and gets one DONE/Stop event."""
+    import uuid
+    q = mk()
+    ids = [uuid.UUID(int=(0xfeedface << 96) | (k << 64) | 0x1234) for k in range(3)]   # differ only beyond the low 64 bits
+    for rid in ids:
+        q.submit(rid, [1, 2, 3], P, now=0.0)
+    assert q.depth().total == 3
+    assert q.cancel(ids[1]) and not q.cancel(uuid.uuid4())
+    assert q.depth().total == 2
+    ev = q.step(now=0.0)
+    assert [(e[0], e[1], e[4], e[5]) for e in ev] == [(ids[1], B.EVENT_DONE, B.FINISH_STOP, 3)]
+    assert q.debug_pop(5) == [ids[0], ids[2]]

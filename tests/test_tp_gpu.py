@@ -1,6 +1,8 @@
-"""Tensor parallel engine on 2 GPUs (skipped on a single-GPU box): one process per GPU, NCCL all-reduce
-after the O and down projections, vocab-parallel lm_head.  Checked against the oracle and against the
-product's shard plan (each rank's weights are exactly the plan's slice of the synthetic tensors)."""
+"""Tensor parallel engine on 2, 4 and 8 GPUs (each case skipped when the box has fewer): one process per GPU,
+the exchange after the O and down projections over peer memory (k_tp.cu) or NCCL, vocab-parallel lm_head.
+Checked against the oracle and against the product's shard plan (each rank's weights are exactly the plan's
+slice of the synthetic tensors).  World sizes above 2 exercise what a 2-rank run cannot: owner-block indexing
+Hs = H/tp, the rank-order sum over several sources, all-gather pushes to several peers."""
 import ctypes as C
 import os
 
@@ -13,7 +15,19 @@ from oracle import oracle as O
 
 pytestmark = pytest.mark.gpu
 SHAPE = O.ModelShape(2048, 512, 3, 8, 2, 64, 1408, 256)
+SHAPE8 = O.ModelShape(2048, 512, 3, 8, 8, 64, 2048, 256)   # 8 kv heads: shards over 4 and 8 ranks
 SEED = 21
+
+
+def needs(world):
+    return pytest.mark.skipif(not torch.cuda.is_available() or torch.cuda.device_count() < world, reason=f"needs {world} GPUs")
+
+
+WORLDS = [pytest.param(w, marks=needs(w), id=f"tp{w}") for w in (2, 4, 8)]
+
+
+def shape_for(world):
+    return SHAPE if world == 2 else SHAPE8
 
 
 def _rank(rank, world, idq, outq, prompts, n_new, temps, hq, custom, SHAPE=None, SEED=None):
@@ -57,11 +71,12 @@ def _rank(rank, world, idq, outq, prompts, n_new, temps, hq, custom, SHAPE=None,
     toks, _ = e.prefill(slots)
     out = [[int(t)] for t in toks]
     logits0 = e.last_logits(len(slots))
+    lp0 = e.last_logprobs(slots)
     for _ in range(n_new - 1):
         toks, _ = e.decode(slots)
         for i, t in enumerate(toks):
             out[i].append(int(t))
-    outq.put((rank, out, logits0))
+    outq.put((rank, out, logits0, lp0))
     e.close()
 
 
@@ -74,15 +89,13 @@ def _run(prompts, n_new, temps, custom, world=2, shape=None, seed=None):
         p.start()
     res = {}
     for _ in range(world):
-        r, out, lg = outq.get(timeout=300)
-        res[r] = (out, lg)
+        r, out, lg, lp = outq.get(timeout=300)
+        res[r] = (out, lg, lp)
     for p in procs:
         p.join(timeout=60)
         assert p.exitcode == 0
     return res
 
-
-needs2 = pytest.mark.skipif(not torch.cuda.is_available() or torch.cuda.device_count() < 2, reason="needs 2 GPUs")
 
 
 def _prompts():
@@ -90,16 +103,25 @@ def _prompts():
     return [rng.integers(0, SHAPE.vocab, n).tolist() for n in (7, 33, 18)]
 
 
-@needs2
+@pytest.mark.parametrize("world", WORLDS)
 @pytest.mark.parametrize("custom", ["oneshot", "twoshot", "ll", None], ids=["peer-memory", "peer-memory-twoshot", "peer-memory-ll", "nccl"])
 @pytest.mark.parametrize("sampled", [False, True], ids=["greedy", "sampled"])
-def test_tp2_matches_oracle(sampled, custom):
+def test_tp_matches_oracle(sampled, custom, world):
     n_new = 12
     prompts = _prompts()
     temps = [0.7, 0.0, 1.1] if sampled else [0.0, 0.0, 0.0]
-    res = _run(prompts, n_new, temps, custom)
-    assert res[0][0] == res[1][0]                       # every rank yields the same tokens
-    assert np.array_equal(res[0][1], res[1][1])         # and the same gathered logits
+    SHAPE = shape_for(world)
+    res = _run(prompts, n_new, temps, custom, world=world, shape=SHAPE)
+    for r in range(1, world):
+        assert res[0][0] == res[r][0]                   # every rank yields the same tokens
+        assert np.array_equal(res[0][1], res[r][1])     # and the same gathered logits
+    # TokenEvent.logprob: the vocabulary slices' (max, sum-exp) pairs merged across ranks = log softmax of the
+    # gathered logits at the chosen token (sampled rows: of logits / temperature)
+    for b, t in enumerate(temps):
+        z = res[0][1][b].astype(np.float64) / (t if t > 0 else 1.0)
+        want_lp = z[res[0][0][b][0]] - (np.log(np.exp(z - z.max()).sum()) + z.max())
+        for r in range(world):
+            assert abs(float(res[r][2][b]) - want_lp) <= 1e-3 * max(1.0, abs(want_lp)), (r, b, float(res[r][2][b]), want_lp)
     ref = O.Oracle(SHAPE, act_round=False); ref.fill_synthetic(SEED, True)
     want = ref.generate(prompts, 1, n_logit_steps=1)
     rel = np.abs(res[0][1] - want["logits"][:, 0]).max() / np.abs(want["logits"]).max()
@@ -113,43 +135,45 @@ def test_tp2_matches_oracle(sampled, custom):
                 assert w["margins"][b, i] <= 5e-3 * np.abs(w["logits"][b, i]).max(), (b, i)
 
 
-@needs2
-def test_twoshot_exchange_is_bit_identical_to_oneshot():
-    """Both exchange kernels add the same contributions in the same (rank) order, then the residual: the logits
-    and the greedy tokens must agree bit for bit."""
+@pytest.mark.parametrize("world", WORLDS)
+def test_twoshot_exchange_is_bit_identical_to_oneshot(world):
+    """All exchange kernels add the same contributions in the same (rank) order, then the residual: the logits
+    and the greedy tokens must agree bit for bit -- at every world size."""
     prompts = _prompts()
-    a = _run(prompts, 24, [0.0] * 3, "oneshot")
-    a2 = _run(prompts, 24, [0.0] * 3, "oneshot")
+    kw = dict(world=world, shape=shape_for(world))
+    a = _run(prompts, 24, [0.0] * 3, "oneshot", **kw)
+    a2 = _run(prompts, 24, [0.0] * 3, "oneshot", **kw)
     assert a[0][0] == a2[0][0] and np.array_equal(a[0][1], a2[0][1]), "the one-shot exchange is not run-to-run deterministic"
-    b = _run(prompts, 24, [0.0] * 3, "twoshot")
-    b2 = _run(prompts, 24, [0.0] * 3, "twoshot")
+    b = _run(prompts, 24, [0.0] * 3, "twoshot", **kw)
+    b2 = _run(prompts, 24, [0.0] * 3, "twoshot", **kw)
     assert b[0][0] == b2[0][0] and np.array_equal(b[0][1], b2[0][1]), "the two-shot exchange is not run-to-run deterministic"
     diff = np.abs(a[0][1] - b[0][1])
     assert np.array_equal(a[0][1], b[0][1]), (float(diff.max()), int((diff > 0).sum()), diff.size)
     assert a[0][0] == b[0][0]
-    c = _run(prompts, 24, [0.0] * 3, "ll")      # flag-in-data variant of the two-shot schedule
+    c = _run(prompts, 24, [0.0] * 3, "ll", **kw)      # flag-in-data variant of the two-shot schedule
     assert np.array_equal(a[0][1], c[0][1]) and a[0][0] == c[0][0]
 
 
 WIDE = O.ModelShape(512, 8192, 1, 64, 8, 128, 1024, 128)   # hidden 8192 (Llama-3-70B's): two float4 per thread in the exchange kernels
 
 
-@needs2
+@pytest.mark.parametrize("world", WORLDS[:2])
 @pytest.mark.parametrize("custom", ["oneshot", "twoshot", "ll"])
-def test_tp2_wide_hidden_matches_oracle(custom):
+def test_tp_wide_hidden_matches_oracle(custom, world):
     """The exchange kernels walk a row of more than 4096 columns in several passes (shared-memory row instead of
     registers): the path Llama-3-70B takes, checked here on a one-layer model of that width."""
     rng = np.random.default_rng(4)
     prompts = [rng.integers(0, WIDE.vocab, n).tolist() for n in (5, 21)]
-    res = _run(prompts, 6, [0.0, 0.0], custom, shape=WIDE)
-    assert res[0][0] == res[1][0] and np.array_equal(res[0][1], res[1][1])
+    res = _run(prompts, 6, [0.0, 0.0], custom, shape=WIDE, world=world)
+    for r in range(1, world):
+        assert res[0][0] == res[r][0] and np.array_equal(res[0][1], res[r][1])
     ref = O.Oracle(WIDE, act_round=False); ref.fill_synthetic(SEED, True)
     want = ref.generate(prompts, 1, n_logit_steps=1)
     rel = np.abs(res[0][1] - want["logits"][:, 0]).max() / np.abs(want["logits"]).max()
     assert rel <= 2e-2, rel
 
 
-@needs2
+@needs(2)
 def test_tp2_64_greedy_tokens_identical_to_transformers():
     """The 64-token fixture of tests/golden (clear margin at every step) on two GPUs: both ranks produce the
     transformers continuation token for token."""

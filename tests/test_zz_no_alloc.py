@@ -9,6 +9,7 @@ import pytest
 import torch
 
 from distributed_inference_server_b200 import binding as B
+from oracle import oracle as O
 from tests._gpu_util import DEV, check, dev_bf16, dev_i32, host, lib, ptr, rand_bf16, sync
 
 pytestmark = pytest.mark.gpu
@@ -29,8 +30,23 @@ def _case(seed, d, nh, nkv, page_size, ctx_lens, splits):
     pool = dev_bf16(rand_bf16(rng, (n_pages, 2, nkv, page_size, d)))
     q = dev_bf16(rand_bf16(rng, (n_seq, nh * d)))
     args = dict(q=q, pool=pool, n_pages=n_pages, pt=dev_i32(pt), max_pages=max_pages, row=dev_i32(np.arange(n_seq)),
-                ctx=dev_i32(ctx_lens), T=n_seq, nh=nh, nkv=nkv, d=d, ps=page_size, splits=splits)
+                ctx=dev_i32(ctx_lens), T=n_seq, nh=nh, nkv=nkv, d=d, ps=page_size, splits=splits, host_pt=pt, ctx_lens=ctx_lens)
     return args
+
+
+def _oracle_attention(a):
+    """The CPU checker's single-query attention (oracle/llama_oracle.c orc_attention_one) over each sequence's pages."""
+    pool, q = host(a["pool"]), host(a["q"])
+    out = np.zeros((a["T"], a["nh"] * a["d"]), np.float32)
+    for s in range(a["T"]):
+        n = a["ctx_lens"][s]
+        K = np.zeros((n, a["nkv"] * a["d"]), np.float32); V = np.zeros_like(K)
+        for t in range(n):
+            page, r = a["host_pt"][s, t // a["ps"]], t % a["ps"]
+            K[t] = pool[page, 0, :, r, :].reshape(-1)
+            V[t] = pool[page, 1, :, r, :].reshape(-1)
+        out[s] = O.attention_one(q[s], K, V, a["nh"], a["nkv"], a["d"])
+    return out
 
 
 def _run_both(a):
@@ -55,6 +71,10 @@ def test_static_scratch_matches_caller_scratch_twice_in_a_row():
         # same kernels, same summation order: identical; the bound is the one the attention parity tests use
         assert np.abs(got - want).max() <= 2 * BF16_ULP * np.abs(want).max() + 1e-5
         assert np.array_equal(got, want)
+        # ... and, standing on its own, against the CPU oracle (P is rounded to bf16 for the P.V MMA: two bf16 ulps
+        # of the output scale, the bound of the attention parity tests in test_kernels_gpu.py)
+        ref = _oracle_attention(case)
+        assert np.abs(got - ref).max() <= 2 * BF16_ULP * np.abs(ref).max() + 1e-5
 
 
 def test_static_scratch_allocates_nothing_and_refuses_oversize():
