@@ -20,11 +20,17 @@ Other lines (diagnostics and the remaining BASELINE configs, never the default):
   --tp-exchange / --nccl-allreduce   A/B of the exchange kernels (k_tp.cu) against each other and NCCL
 Extra keys: roofline (dominant kernel, from an eager step timed per kernel class), step_roofline (whole step),
 graph_only_ms_last_step (the last step's CUDA graph replayed back to back), ttft_* (prefill of the whole batch and of
-one request), kernel_class_ms_per_step, clocks.
+one request, measured AFTER the decode run), kernel_class_ms_per_step, clocks; N > 1 adds parity (the TP engines'
+tokens and logits against a TP=1 engine on rank 0, checked before anything is timed) and tp1_same_batch /
+scaling_vs_tp1_same_batch (the same batch on one GPU: the like-for-like denominator of the scaling curve).
+Order of the run: [TP parity] -> one prefill of the batch -> `--settle-steps` untimed decode steps (power state) ->
+W warm-up steps -> K timed steps -> graph replay, per-class profile, TTFT runs -> CPU legs.
 
 The reference has no implementation of this path (crates/inference/src/worker.rs:1), so the
 `--impl reference` arm and `cpu_baseline` time the CPU oracle port (oracle/llama_oracle.c) on the
-host cores on a bounded sample of the same workload.
+host cores: the same workload at full depth (every reported step is run) when the host has the 32 GB + KV the fp32
+model needs, else 2 of 32 layers scaled (the line then says so).  `cpu_config0` is BASELINE configs[0] (TinyLlama
+shape, full depth) on the same oracle.  All CPU legs run on rank 0 outside the process group.
 """
 from __future__ import annotations
 
@@ -116,57 +122,146 @@ class ClockSampler:
 
 
 # --------------------------------------------------------------------------------------- CPU arm
-def cpu_sample(batch, ctx, layers_sample=2, steps=1, warmup=1):
-    """Decode steps of the fp32 CPU oracle at Llama-3-8B width on `layers_sample` of the 32 layers,
-    batch `batch`, synthetic `ctx`-token histories; extrapolated to 32 layers + lm_head."""
+def host_cores():
+    try:
+        return len(os.sched_getaffinity(0))
+    except Exception:
+        return os.cpu_count() or 1
+
+
+def mem_available_gb():
+    try:
+        for line in open("/proc/meminfo"):
+            if line.startswith("MemAvailable:"):
+                return int(line.split()[1]) / 1e6
+    except Exception:
+        pass
+    return 0.0
+
+
+class CpuDecoder:
+    """The fp32 CPU oracle (oracle/llama_oracle.c) set up for decode steps of the GPU arm's workload: Llama-3-8B
+    width, batch `batch`, synthetic `ctx`-token KV histories.  FULL depth (32 layers, 32 GB of fp32 weights) when
+    the host has the memory for it -- every reported step is then really run, nothing is extrapolated; otherwise
+    2 of the 32 layers and the figure is scaled, which `sample` then says in words."""
+
+    def __init__(self, batch, ctx, n_steps, full=None):
+        from oracle import oracle as O
+        self.O = O
+        O.set_num_threads(host_cores())   # torch.distributed.run exports OMP_NUM_THREADS=1: never inherit that
+        s8 = O.LLAMA3_8B
+        kvd = s8.n_kv_heads * s8.head_dim
+        need_gb = 4 * (s8.layers * (2 * s8.hidden * s8.hidden + 2 * s8.hidden * kvd + 3 * s8.hidden * s8.inter)
+                       + 2 * s8.vocab * s8.hidden) / 1e9 + batch * (ctx + n_steps + 8) * kvd * 2 * 4 * s8.layers / 1e9
+        self.full = (mem_available_gb() > need_gb + 8.0) if full is None else full
+        self.layers = s8.layers if self.full else 2
+        self.batch, self.ctx = batch, ctx
+        shape = O.ModelShape(s8.vocab, s8.hidden, self.layers, s8.n_heads, s8.n_kv_heads, s8.head_dim,
+                             s8.inter, ctx + n_steps + 8, s8.rope_theta, s8.rms_eps)
+        t0 = time.perf_counter()
+        self.m = O.Oracle(shape, act_round=False)
+        self.m.fill_synthetic(0, True)
+        self.sids = [self.m.seq_new() for _ in range(batch)]
+        for s in self.sids:
+            self.m.seq_fill_synthetic(s, ctx, 7)
+        self.setup_s = time.perf_counter() - t0
+        self.rng = np.random.default_rng(1)
+        self.it = 0
+        self.cores = O.num_threads()
+        self.head_s = None
+
+    def step(self):
+        """One decode step of the whole batch; returns seconds (scaled to 32 layers when running a layer sample)."""
+        toks = self.rng.integers(0, self.m.shape.vocab, self.batch)
+        pos = np.full(self.batch, self.ctx + self.it, np.int32)
+        self.it += 1
+        if self.full:
+            t0 = time.perf_counter()
+            self.m.forward(toks, self.sids, pos, want_logits=np.ones(self.batch, bool))
+            return time.perf_counter() - t0
+        t0 = time.perf_counter()
+        self.m.forward(toks, self.sids, pos, want_logits=np.zeros(self.batch, bool))   # layers only
+        t1 = time.perf_counter()
+        if self.head_s is None:  # layers + head at the same positions (K/V rows are simply rewritten)
+            self.m.forward(toks, self.sids, pos, want_logits=np.ones(self.batch, bool))
+            self.head_s = max(time.perf_counter() - t1 - (t1 - t0), 0.0)
+        return (t1 - t0) * (32 / self.layers) + self.head_s
+
+    def describe(self, n_timed):
+        depth = ("all 32 layers + lm_head, every step really run" if self.full else
+                 f"{self.layers} of 32 layers timed and SCALED to 32 (+ lm_head timed once): host memory too small for the 32 GB fp32 model")
+        return (f"oracle/llama_oracle.c (fp32, OpenMP, {self.cores} threads): {n_timed} decode step(s) of batch {self.batch} at ctx "
+                f"{self.ctx}, Llama-3-8B shape, {depth}; the reference itself has no forward pass (crates/inference/src/worker.rs:1)")
+
+    def close(self):
+        self.m.close()
+
+
+def cpu_baseline_leg(batch, ctx):
+    """cpu_baseline of the GPU arm's line: a bounded sample (about 20-30 s) of the same workload on the host cores."""
+    dec = CpuDecoder(batch, ctx, n_steps=4)
+    dec.step()                                   # warm-up
+    ts = [dec.step() for _ in range(2)]
+    step_s = statistics.median(ts)
+    out = {"value": batch / step_s, "unit": "tokens/s", "cores": dec.cores, "kind": "port", "sample": dec.describe(len(ts)),
+           "ms_per_step": step_s * 1e3, "extrapolated": not dec.full}
+    dec.close()
+    return out
+
+
+def cpu_config0_leg(new_tokens=32):
+    """BASELINE configs[0]: TinyLlama-1.1B shape, random-init fp32, one request, 128-token prompt, greedy, on the CPU
+    oracle at FULL depth (22 layers).  Bounded: `new_tokens` decode steps instead of 128 (steady-state decode rate)."""
     from oracle import oracle as O
-    full = O.LLAMA3_8B
-    shape = O.ModelShape(full.vocab, full.hidden, layers_sample, full.n_heads, full.n_kv_heads, full.head_dim, full.inter,
-                         ctx + steps + warmup + 8, full.rope_theta, full.rms_eps)
+    O.set_num_threads(host_cores())
+    shape = O.ModelShape(*[getattr(O.TINYLLAMA, f) for f in ("vocab", "hidden", "layers", "n_heads", "n_kv_heads", "head_dim", "inter")],
+                         256, O.TINYLLAMA.rope_theta, O.TINYLLAMA.rms_eps)
     m = O.Oracle(shape, act_round=False)
     m.fill_synthetic(0, True)
-    sids = [m.seq_new() for _ in range(batch)]
-    for s in sids:
-        m.seq_fill_synthetic(s, ctx, 7)
-    rng = np.random.default_rng(1)
-    t_layers, t_total = [], []
-    for it in range(warmup + steps):
-        toks = rng.integers(0, shape.vocab, batch)
-        pos = np.full(batch, ctx + it, np.int32)
-        t0 = time.perf_counter()
-        m.forward(toks, sids, pos, want_logits=np.zeros(batch, bool))       # layers only
-        t1 = time.perf_counter()
-        m.forward(toks, sids, pos, want_logits=np.ones(batch, bool))        # layers + head (same positions)
-        t2 = time.perf_counter()
-        if it >= warmup:
-            t_layers.append(t1 - t0)
-            t_total.append(t2 - t1)
-    tl = statistics.median(t_layers)
-    th = max(statistics.median(t_total) - tl, 0.0)
-    step_s = tl * (full.layers / layers_sample) + th
-    cores = O.num_threads()
+    prompt = np.random.default_rng(1).integers(0, shape.vocab, 128)
+    sid = m.seq_new()
+    t0 = time.perf_counter()
+    lg = m.forward(prompt, [sid] * 128, np.arange(128), want_logits=np.arange(128) == 127)
+    t1 = time.perf_counter()
+    tok = int(np.argmax(lg[0]))
+    for i in range(new_tokens):
+        lg = m.forward([tok], [sid], [128 + i])
+        tok = int(np.argmax(lg[0]))
+    t2 = time.perf_counter()
     m.close()
-    return {"value": batch / step_s, "unit": "tokens/s", "cores": cores, "kind": "port",
-            "sample": (f"oracle/llama_oracle.c (fp32, OpenMP, {cores} threads): {steps} decode step(s) of batch {batch} at ctx {ctx} "
-                       f"on {layers_sample} of 32 Llama-3-8B-width layers + full lm_head, extrapolated to 32 layers "
-                       f"({tl:.2f} s / {layers_sample} layers, head {th:.2f} s); the reference itself has no forward pass")}, step_s
+    return {"workload": "BASELINE configs[0]: TinyLlama-1.1B-shape Llama decoder (22 layers), random-init fp32, one request, greedy, "
+                        f"128-token prompt -> {new_tokens} new tokens (bounded from 128), CPU oracle port, full depth, nothing extrapolated",
+            "prefill_s": t1 - t0, "decode_tokens_per_s": new_tokens / (t2 - t1), "cores": O.num_threads(), "kind": "port",
+            "parity": "the GPU engine is checked against this oracle at this shape by tests/test_baseline_configs_gpu.py"}
 
 
 def run_reference(args):
+    """`--impl reference`: the reference's CPU implementation of the path on the host cores.  The reference has none
+    (crates/inference/src/worker.rs:1 is a comment), so this is the CPU oracle port, on the GPU arm's config.  Every one
+    of the W + K steps is run; a step is one decode step of the whole batch."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0
     batch = args.batch or (32 if args.gpus == 1 else 64)
-    steps = max(1, min(args.steps, 3))
     t0 = time.perf_counter()
-    base, step_s = cpu_sample(batch, args.prompt_len, layers_sample=2, steps=steps, warmup=1 if args.warmup else 0)
+    dec = CpuDecoder(batch, args.prompt_len, n_steps=args.steps + args.warmup)
+    for _ in range(args.warmup):
+        dec.step()
+    ts = [dec.step() for _ in range(args.steps)]
+    step_s = sum(ts) / max(len(ts), 1)
+    base = {"value": batch / step_s, "unit": "tokens/s", "cores": dec.cores, "kind": "port", "sample": dec.describe(len(ts)),
+            "extrapolated": not dec.full, "setup_s": dec.setup_s}
+    cfg = workload_config(args.gpus, batch, args.prompt_len)
+    cfg["cpu_arm"] = f"run on {dec.cores} host threads; the tensor-parallel exchange does not exist on the CPU"
+    if not dec.full:
+        cfg["workload"] += " [CPU arm: 2 of 32 layers timed per step and scaled to 32; host memory too small for full depth]"
     line = {"impl": "reference", "metric": "decode tokens/s Llama-3-8B", "value": base["value"], "unit": "tokens/s",
-            "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": step_s * 1e3,
+            "n_gpus": args.gpus, "steps": len(ts), "warmup": args.warmup, "ms_per_step": step_s * 1e3,
             "higher_is_better": True, "scaling": "strong" if args.gpus > 1 else "weak", "vs_baseline": None, "dtype": "f32",
-            "data": "synthetic", "config": workload_config(args.gpus, batch, args.prompt_len),
-            "cpu_baseline": base,
+            "data": "synthetic", "config": cfg, "cpu_baseline": base,
             "e2e": {"value": base["value"], "unit": "tokens/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0, "wall_s": time.perf_counter() - t0}
+    dec.close()
     print(json.dumps(line))
     return 0
 
@@ -185,7 +280,83 @@ def workload_config(n_gpus, batch, prompt_len, model="8b"):
             "l2": "per-step working set (15 GB of weights + KV) is far larger than the 126 MB L2; no explicit flush"}
 
 
+def roofline_traffic(kernel_key):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernel, from the committed summary of the
+    ncu --set full capture (profiles/roofline_traffic.json, written by scripts/summarize_profile.py) -- a profiler is
+    never run inside the bench.  None when there is no capture for this kernel/shape."""
+    p = os.path.join(ROOT, "profiles", "roofline_traffic.json")
+    try:
+        d = json.load(open(p)).get(kernel_key)
+        if d:
+            return int(d["dram_bytes_read"]) + int(d["dram_bytes_write"]), d.get("source")
+    except Exception:
+        pass
+    return None, None
+
+
 # --------------------------------------------------------------------------------------- GPU arm
+def tp_parity_check(eng, make_engine, prompts, P, rank, world, dist, torch, gloo, steps=3):
+    """Before anything is timed: the tensor-parallel engines' first `steps` greedy tokens and their first-step logits
+    against a TP=1 engine with the same weights and prompts, built on rank 0 (torch.distributed is the plumbing).
+    Returns (parity dict on rank 0 / None, the TP=1 engine + its slots on rank 0 for the same-batch timing)."""
+    slots = [eng.seq_add(p, P) for p in prompts]
+    toks = [eng.prefill(slots)[0].astype(np.int64)]
+    logits = eng.last_logits(len(slots))                     # gathered over ranks (every rank takes part)
+    for _ in range(steps - 1):
+        toks.append(eng.decode(slots)[0].astype(np.int64))
+    for s in slots:
+        eng.seq_remove(s)
+    mine = torch.tensor(np.stack(toks), device="cuda")
+    every = [torch.zeros_like(mine) for _ in range(world)]
+    dist.all_gather(every, mine)
+    ranks_agree = all(bool(torch.equal(every[0], t)) for t in every)
+    lg_sum = torch.tensor([float(np.abs(logits.astype(np.float64)).sum())], device="cuda", dtype=torch.float64)
+    lg_all = [torch.zeros_like(lg_sum) for _ in range(world)]
+    dist.all_gather(lg_all, lg_sum)
+    ranks_agree = ranks_agree and all(float(t) == float(lg_all[0]) for t in lg_all)
+    parity, one, one_slots = None, None, None
+    if rank == 0:
+        one = make_engine(1, 0)
+        one_slots = [one.seq_add(p, P) for p in prompts]
+        ref_toks = [one.prefill(one_slots)[0].astype(np.int64)]
+        ref_logits = one.last_logits(len(one_slots))
+        for _ in range(steps - 1):
+            ref_toks.append(one.decode(one_slots)[0].astype(np.int64))
+        ref_toks = np.stack(ref_toks)
+        got = np.stack(toks)
+        rel = float(np.abs(logits - ref_logits).max() / np.abs(ref_logits).max())
+        # a sequence whose token differs: only its FIRST difference is comparable (the histories part there); it
+        # must sit where the TP=1 engine's own margin between the two candidates is below bf16 noise
+        n_seq = got.shape[1]
+        identical, explained, unexplained = 0, 0, []
+        for b in range(n_seq):
+            d = np.nonzero(got[:, b] != ref_toks[:, b])[0]
+            if len(d) == 0:
+                identical += 1
+                continue
+            if d[0] == 0:
+                r = ref_logits[b]
+                margin, scale = float(r[ref_toks[0, b]] - r[got[0, b]]), float(np.abs(r).max())
+                if margin <= 5e-3 * scale:
+                    explained += 1
+                else:
+                    unexplained.append((b, 0, margin / scale))
+            else:
+                explained += 1   # later steps: logits of those steps are not kept; counted, not judged
+        parity = {"against": "a TP=1 engine with the same weights and prompts on rank 0", "steps": steps, "sequences": n_seq,
+                  "sequences_with_identical_tokens": identical, "sequences_differing_at_a_sub_noise_margin_or_later_step": explained,
+                  "sequences_differing_at_a_clear_margin": len(unexplained), "first_step_logits_max_rel_err": rel,
+                  "logit_tolerance": 2e-2, "all_ranks_agree_bitwise": bool(ranks_agree),
+                  "ok": bool(ranks_agree and rel <= 2e-2 and not unexplained)}
+        if not parity["ok"]:
+            print(json.dumps({"parity_failed": parity, "clear_margin_differences": unexplained}), file=sys.stderr)
+    ok = torch.tensor([1 if (parity is None or parity["ok"]) else 0])    # host tensor over gloo: the waiting GPUs stay idle
+    dist.broadcast(ok, 0, group=gloo)
+    if int(ok) == 0:
+        raise SystemExit("tensor-parallel parity check failed: nothing was timed (details on rank 0's stderr)")
+    return parity, one, one_slots
+
+
 def run_ours(args):
     import torch
     from distributed_inference_server_b200 import Engine, InferenceParams, LLAMA3_8B, ModelShape, WorkerConfig
@@ -197,12 +368,13 @@ def run_ours(args):
     if world != args.gpus:
         if args.gpus != 1:
             raise SystemExit(f"--gpus {args.gpus} needs torch.distributed.run with {args.gpus} processes (WORLD_SIZE={world})")
-    dist = None
+    dist, gloo = None, None
     torch.cuda.set_device(local)
     nccl_id = None
     if world > 1:
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        gloo = dist.new_group(backend="gloo")   # host-side waits: a GPU that waits in an NCCL barrier spins a kernel
         idt = torch.zeros(128, dtype=torch.uint8, device="cuda")
         if rank == 0:
             import ctypes as C
@@ -223,18 +395,24 @@ def run_ours(args):
                            shape.inter // n, shape.max_ctx, shape.rope_theta, shape.rms_eps)
     batch = args.batch or (32 if (world == 1 or args.model == "70b") else 64)
     n_ttft = max(1, args.ttft_runs)
-    total_steps = args.warmup + args.steps + args.profile_steps + 2
+    total_steps = args.settle_steps + args.warmup + args.steps + args.profile_steps + 8
     page = 64
     pages_per_seq = (args.prompt_len + total_steps + page) // page + 1
     stream = torch.cuda.current_stream()
-    eng = Engine(WorkerConfig(shape, device=local, tp_rank=rank, tp_size=world, max_batch=batch,
-                              max_step_tokens=args.prefill_chunk, page_size=page, kv_pages=batch * pages_per_seq,
-                              context_size=args.prompt_len + total_steps + 8, stream=stream.cuda_stream, nccl_id=nccl_id,
-                              flags=(B.FLAG_NO_GRAPH if args.no_graph else 0) | (B.FLAG_NO_PDL if args.no_pdl else 0)))
-    eng.load_synthetic(0)
-    eng.finalize()
     if args.tp_exchange != "auto":
         os.environ["DIS_TP_EXCHANGE"] = args.tp_exchange
+
+    def make_engine(tp, tp_rank):
+        e = Engine(WorkerConfig(shape, device=local, tp_rank=tp_rank, tp_size=tp, max_batch=batch,
+                                max_step_tokens=args.prefill_chunk, page_size=page, kv_pages=batch * pages_per_seq,
+                                context_size=args.prompt_len + total_steps + 8, stream=stream.cuda_stream,
+                                nccl_id=nccl_id if tp > 1 else None,
+                                flags=(B.FLAG_NO_GRAPH if args.no_graph else 0) | (B.FLAG_NO_PDL if args.no_pdl else 0)))
+        e.load_synthetic(0)
+        e.finalize()
+        return e
+
+    eng = make_engine(world, rank)
     if world > 1 and not args.nccl_allreduce:
         # peer-memory exchange: all-gather the CUDA IPC handles of the symmetric buffers
         mine = torch.tensor(list(eng.tp_export()), dtype=torch.uint8, device="cuda")
@@ -251,55 +429,60 @@ def run_ours(args):
             dist.barrier()
         torch.cuda.synchronize()
 
-    # ---- TTFT of a single 512-token request on an idle engine (p50 of 5)
-    ttft1 = []
-    for i in range(5):
-        s1 = eng.seq_add(prompts[i % batch], P)
-        barrier()
+    def timed_decode(e, slots, steps, sync_ranks):
+        """K decode steps: CUDA events on the engine's stream (value) and the host clock around the same calls (e2e)."""
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier() if sync_ranks else torch.cuda.synchronize()
         t0 = time.perf_counter()
-        eng.prefill([s1])
-        torch.cuda.synchronize()
-        ttft1.append((time.perf_counter() - t0) * 1e3)
-        eng.seq_remove(s1)
-    # ---- TTFT: prefill of the whole batch (p50 over n_ttft runs); the last run's sequences are kept
+        ev0.record(stream)
+        for _ in range(steps):
+            e.decode(slots)
+        ev1.record(stream)
+        barrier() if sync_ranks else torch.cuda.synchronize()
+        wall = (time.perf_counter() - t0) * 1e3
+        return ev0.elapsed_time(ev1), wall
+
+    # ---- tensor parallel: parity against a TP=1 engine BEFORE anything is timed, and that engine's own decode time at
+    # the same batch (the like-for-like denominator of the scaling curve)
+    parity, tp1 = None, None
+    if world > 1 and not args.no_parity and args.model == "8b" and args.shard_of <= 1:
+        parity, one, one_slots = tp_parity_check(eng, make_engine, prompts, P, rank, world, dist, torch, gloo)
+        if rank == 0:
+            for _ in range(args.settle_steps + args.warmup):
+                one.decode(one_slots)
+            dev1, _ = timed_decode(one, one_slots, args.steps, False)
+            tp1 = {"value": batch * args.steps / (dev1 / 1e3), "unit": "tokens/s", "ms_per_step": dev1 / args.steps, "batch": batch,
+                   "what": "the same batch on ONE GPU (TP=1 engine on rank 0, same build, timed the same way while the other GPUs idle)"}
+            one.close()
+        dist.barrier(group=gloo)
+
+    # ---- the batch is prefilled once (TTFT sample 0, which includes one-time set-up costs)
     ttft = []
-    slots = None
-    for i in range(n_ttft):
-        if slots:
-            for s in slots:
-                eng.seq_remove(s)
-        slots = [eng.seq_add(p, P) for p in prompts]
-        barrier()
-        t0 = time.perf_counter()
-        eng.prefill(slots)
-        torch.cuda.synchronize()
-        ttft.append((time.perf_counter() - t0) * 1e3)
+    slots = [eng.seq_add(p, P) for p in prompts]
+    barrier()
+    t0 = time.perf_counter()
+    eng.prefill(slots)
+    torch.cuda.synchronize()
+    ttft_first = (time.perf_counter() - t0) * 1e3
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
-    # ---- warm-up (also captures the decode graph)
-    for _ in range(args.warmup):
+    # ---- settle: untimed decode steps that take the board from the prefill's power state to the decode's (a B200 sits at
+    # its power cap after a tensor-bound prefill and needs some 100 ms of the lighter decode load to clock back up);
+    # then the W warm-up steps the caller asked for, then EXACTLY K timed steps
+    for _ in range(args.settle_steps + args.warmup):
         eng.decode(slots)
     launches0 = eng.status().kernel_launches
-    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    barrier()
     sampler.mark_start()
-    t0 = time.perf_counter()
-    ev0.record(stream)
-    for _ in range(args.steps):
-        eng.decode(slots)
-    ev1.record(stream)
-    barrier()
-    wall_ms = (time.perf_counter() - t0) * 1e3
+    dev_ms, wall_ms = timed_decode(eng, slots, args.steps, True)
     sampler.mark_end()
-    dev_ms = ev0.elapsed_time(ev1)
     clocks = sampler.stop() if rank == 0 else None
     launches = eng.status().kernel_launches - launches0
     if dist is not None:
         t = torch.tensor([dev_ms, wall_ms], device="cuda", dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         dev_ms, wall_ms = float(t[0]), float(t[1])
-    mean_ctx = args.prompt_len + n_ttft * 0 + args.warmup + (args.steps + 1) / 2.0
+    mean_ctx = args.prompt_len + args.settle_steps + args.warmup + (args.steps + 1) / 2.0
 
     # ---- the LAST step's CUDA graph (longest context of the run) replayed back to back: what the GPU needs without
     # the host between steps; compare with the last steps' times, not with the run's average
@@ -316,6 +499,27 @@ def run_ours(args):
         for k, (ms, n) in cls.items():
             a = prof.setdefault(k, [0.0, 0])
             a[0] += ms; a[1] += n
+    # ---- TTFT, after the decode measurement so that the prefills' power state does not leak into it
+    for s in slots:
+        eng.seq_remove(s)
+    for i in range(n_ttft):
+        slots = [eng.seq_add(p, P) for p in prompts]
+        barrier()
+        t0 = time.perf_counter()
+        eng.prefill(slots)
+        torch.cuda.synchronize()
+        ttft.append((time.perf_counter() - t0) * 1e3)
+        for s in slots:
+            eng.seq_remove(s)
+    ttft1 = []
+    for i in range(5):     # a single request on an idle engine (p50 of 5)
+        s1 = eng.seq_add(prompts[i % batch], P)
+        barrier()
+        t0 = time.perf_counter()
+        eng.prefill([s1])
+        torch.cuda.synchronize()
+        ttft1.append((time.perf_counter() - t0) * 1e3)
+        eng.seq_remove(s1)
     st = eng.status()
     w_bytes, kv_per_tok = model_bytes(shape, world)
     step_bytes = w_bytes + batch * mean_ctx * kv_per_tok
@@ -330,35 +534,39 @@ def run_ours(args):
         roof = {"bound": "hbm", "kernel": "gemm_tcgen05_kernel<BN,dual=true> (gate-up projection + SiLU-gate)",
                 "achieved": None, "peak": peak, "unit": "GB/s", "frac": None, "traffic": None, "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": gu_bytes}
-        if world == 1 and args.model == "8b" and batch == 32 and args.shard_of <= 1:
-            # dram__bytes_read.sum + dram__bytes_write.sum of one launch of this kernel at this shape, from the
-            # committed ncu --set full capture (a profiler is never run inside the bench)
-            roof["traffic"] = 235321856 + 3654400
-            roof["traffic_source"] = "profiles/r1_r1f_full.txt (ncu --set full, same command, batch 32)"
+        if world == 1 and args.model == "8b" and args.shard_of <= 1:
+            roof["traffic"], roof["traffic_source"] = roofline_traffic(f"gateup_8b_batch{batch}")
         if prof.get("gateup", [0, 0])[1]:
             avg_ms = prof["gateup"][0] / prof["gateup"][1]
             roof["achieved"] = gu_bytes / (avg_ms * 1e-3) / 1e9
             roof["frac"] = roof["achieved"] / peak
             roof["avg_launch_ms"] = avg_ms
         step_gbs = step_bytes / (ms_per_step * 1e-3) / 1e9
+        cfg = workload_config(world, batch, args.prompt_len, args.model)
+        cfg["settle_steps"] = args.settle_steps
         line = {"metric": "decode tokens/s Llama-3-" + args.model.upper(), "value": value, "unit": "tokens/s", "n_gpus": world,
                 "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
                 "scaling": "strong" if world > 1 else "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-                "config": workload_config(world, batch, args.prompt_len, args.model),
+                "config": cfg,
                 "roofline": roof,
                 "step_roofline": {"bound": "hbm", "algorithmic_bytes_per_step_per_gpu": step_bytes, "achieved": step_gbs,
                                   "peak": peak, "unit": "GB/s", "frac": step_gbs / peak, "frac_of_nominal_8TBs": step_gbs / 8000.0,
                                   "mean_ctx": mean_ctx},
                 "e2e": {"value": batch * args.steps / (wall_ms / 1e3), "unit": "tokens/s",
-                        "h2d_bytes_per_step": int(60 * batch), "d2h_bytes_per_step": 4 * batch,
-                        "how": "host clock around K dis_engine_decode calls: slot list in, token ids out, per-step metadata H2D and token D2H inside"},
-                "ttft_ms_p50": statistics.median(ttft), "ttft_ms_all": ttft,
+                        "h2d_bytes_per_step": int(60 * batch), "d2h_bytes_per_step": 4 * (batch + batch),
+                        "how": "host clock around K dis_engine_decode calls: slot list in, token ids + log-probabilities out, per-step metadata H2D and result D2H inside"},
+                "ttft_ms_p50": statistics.median(ttft), "ttft_ms_all": ttft, "ttft_ms_first_call": ttft_first,
                 "ttft_note": f"ttft_ms_p50: prefill of all {batch} x {args.prompt_len}-token prompts in one call (every request waits for it); "
-                             f"ttft_single_ms_p50: one {args.prompt_len}-token request on an idle engine",
+                             f"ttft_single_ms_p50: one {args.prompt_len}-token request on an idle engine; measured after the decode run",
                 "ttft_single_ms_p50": statistics.median(ttft1),
                 "gpu_launches": int(launches), "clocks": clocks, "graph_only_ms_last_step": graph_only_ms,
                 "kernel_class_ms_per_step": {k: v[0] / max(args.profile_steps, 1) for k, v in prof.items()},
                 "kv_pages": st.kv_pages_total, "device_mem_gb": st.memory_used / 1e9}
+        if parity is not None:
+            line["parity"] = parity
+        if tp1 is not None:
+            line["tp1_same_batch"] = tp1
+            line["scaling_vs_tp1_same_batch"] = {"speedup": value / tp1["value"], "of_linear": value / tp1["value"] / world}
         if args.layers:
             line["config"]["workload"] += f" [REDUCED DEPTH {args.layers} layers: not a valid headline number]"
         if world > 1:
@@ -367,17 +575,21 @@ def run_ours(args):
         if args.shard_of > 1:
             line["config"]["workload"] += f" [DIAGNOSTIC: one rank's shard of TP={args.shard_of}, no exchange: not a headline number]"
     eng.close()
-    if rank == 0 and not args.no_cpu and world >= 1:
+    if dist is not None:
+        dist.barrier(group=gloo)
+        dist.destroy_process_group()
+    # ---- CPU legs: rank 0, N = 1 only, OUTSIDE the process group (no GPU waits on them)
+    if rank == 0 and world == 1 and not args.no_cpu:
         try:
-            line["cpu_baseline"], _ = cpu_sample(batch, args.prompt_len, layers_sample=2, steps=1, warmup=1)
+            line["cpu_baseline"] = cpu_baseline_leg(batch, args.prompt_len)
         except Exception as ex:  # the CPU figure is a reported baseline; never lose the GPU line over it
-            line["cpu_baseline"] = {"value": None, "unit": "tokens/s", "cores": os.cpu_count(), "kind": "port",
-                                    "sample": f"failed: {ex}"}
+            line["cpu_baseline"] = {"value": None, "unit": "tokens/s", "cores": host_cores(), "kind": "port", "sample": f"failed: {ex}"}
+        try:
+            line["cpu_config0"] = cpu_config0_leg()
+        except Exception as ex:
+            line["cpu_config0"] = {"failed": str(ex)}
     if rank == 0:
         print(json.dumps(line))
-    if dist is not None:
-        dist.barrier()
-        dist.destroy_process_group()
     return 0
 
 
@@ -502,6 +714,9 @@ def main():
     ap.add_argument("--requests", type=int, default=256)
     ap.add_argument("--shard-of", type=int, default=1, help="diagnostic: run one rank's shard of a TP=N model on one GPU, no exchange")
     ap.add_argument("--new-tokens", type=int, default=128)
+    ap.add_argument("--settle-steps", type=int, default=48,
+                    help="untimed decode steps before the W warm-up steps: lets the board leave the prefill's power state")
+    ap.add_argument("--no-parity", action="store_true", help="TP: skip the parity check against a TP=1 engine on rank 0")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)

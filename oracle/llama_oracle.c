@@ -574,6 +574,16 @@ ORC_API int orc_generate(orc_model *m, int B, const int *prompts, const int *pro
   return rc;
 }
 
+/* bench.py sets the thread count explicitly: a launcher such as torch.distributed.run exports OMP_NUM_THREADS=1,
+ * which would silently turn the CPU baseline into a one-core figure. */
+ORC_API void orc_set_num_threads(int n) {
+#ifdef _OPENMP
+  if (n > 0) omp_set_num_threads(n);
+#else
+  (void)n;
+#endif
+}
+
 ORC_API int orc_num_threads(void) {
 #ifdef _OPENMP
   return omp_get_max_threads();

@@ -107,6 +107,7 @@ def lib() -> C.CDLL:
         L.orc_sample.argtypes = [fp, C.c_int, C.c_float, C.c_float, C.c_uint64, C.c_uint64, fp, fp]
         L.orc_bf16_round_inplace.argtypes = [fp, C.c_size_t]
         L.orc_num_threads.restype = C.c_int
+        L.orc_set_num_threads.argtypes = [C.c_int]
     return _lib
 
 
@@ -303,3 +304,7 @@ def uniform(seed, key, idx):
 
 def num_threads():
     return lib().orc_num_threads()
+
+
+def set_num_threads(n: int):
+    lib().orc_set_num_threads(int(n))

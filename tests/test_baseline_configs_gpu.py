@@ -1,0 +1,191 @@
+"""Parity at BASELINE.json's OWN shapes, full depth, through the C ABI.
+
+configs[0]  TinyLlama-1.1B shape (22 layers, H=2048, 32/4 heads, d=64, I=5632, V=32000), random-init, one request,
+            128-token prompt, greedy: the one full-depth model the fp32 CPU oracle finishes in seconds.  The engine's
+            logits of EVERY step are compared with the oracle (<= 2e-2, north_star's tolerance) and its first 64
+            greedy ids with the oracle's.
+configs[1]  Llama-3-8B (32 layers, H=4096, 32/8 heads, d=128, I=14336, V=128256), random-init, 512-token prompt:
+            no CPU oracle finishes that, so the checker is an independent implementation run on the same GPU --
+            transformers' LlamaForCausalLM in fp32 (eager attention, TF32 off) holding the same synthetic tensors.
+            torch/transformers are the checker here, never the product path.
+
+Random-init logits are nearly flat (SURVEY.md §7 hard part 2): a greedy id may legitimately differ from the fp32
+reference where the reference's own top-1/top-2 margin is below bf16 noise.  Two checks separate the two effects:
+  * teacher-forced: the reference is run on the ENGINE's token history, so all 64 steps are judged even after a
+    flip; at each step the engine's token must be the reference argmax, or the reference's margin between its
+    argmax and the engine's token must be below 5e-3 of max|logit| (printed as a [margin report], never hidden);
+  * free-running: the reference's own greedy continuation; the first difference (if any) must sit at such a margin.
+The TinyLlama seeds below are the pair with the widest minimum margin among ~90 tried with the fp32 oracle (2.2e-3 of
+max|logit| over 64 steps; at V = 32000 nothing wider turned up, see _pick_note); the 8B seeds are bench.py's.  The
+tests therefore demand: logits within tolerance at EVERY step, every greedy id equal to the reference argmax or
+differing at a reported sub-noise margin, and they print how many of the 64 free-running ids were identical.
+"""
+import ctypes as C
+
+import numpy as np
+import pytest
+import torch
+
+from distributed_inference_server_b200 import Engine, InferenceParams, WorkerConfig
+from distributed_inference_server_b200 import binding as B
+from oracle import oracle as O
+from tests._gpu_util import to_engine_shape
+
+pytestmark = pytest.mark.gpu
+LOGIT_TOL = 2e-2      # north_star: max relative error of the logits against the fp32 reference
+MARGIN_NOISE = 5e-3   # of max|logit|: below this a top-1/top-2 decision is inside bf16 rounding noise
+
+# (weight seed, prompt seed): see _pick_note
+TINY_SEEDS = (1, 215)
+L8B_SEEDS = (0, 1)
+
+
+def _pick_note():
+    """How the seeds were picked (run in the build container, CPU only):
+        m = O.Oracle(O.TINYLLAMA, False); m.fill_synthetic(w, True)
+        r = m.generate([prompt(p)], 64, n_logit_steps=64); rel = r['margins'][0] / abs(r['logits'][0]).max(1)
+    over w in 0..5 x p in 100..102, then w = 1 x p in 200..271, keeping the pair whose min(rel) is largest
+    (w = 1, p = 215: 2.15e-3).  Nothing else was tuned."""
+
+
+def rel_err(a, b):
+    return float(np.abs(a - b).max() / np.abs(b).max())
+
+
+def run_engine(shape, wseed, prompt, n_new, ctx):
+    e = Engine(WorkerConfig(to_engine_shape(shape), max_batch=2, kv_pages=2 * ((len(prompt) + n_new) // 64 + 2), page_size=64,
+                            max_step_tokens=1024, context_size=ctx))
+    e.load_synthetic(wseed)
+    e.finalize()
+    s = e.seq_add(prompt, InferenceParams(max_tokens=n_new + 1, temperature=0.0))
+    toks = [int(e.prefill([s])[0][0])]
+    logits = [e.last_logits(1)[0].copy()]
+    lps = [float(e.last_logprobs([s])[0])]
+    for _ in range(n_new - 1):
+        toks.append(int(e.decode([s])[0][0]))
+        logits.append(e.last_logits(1)[0].copy())
+        lps.append(float(e.last_logprobs([s])[0]))
+    e.seq_remove(s)
+    return e, toks, np.stack(logits), np.array(lps)
+
+
+def judge(label, got, gpu_logits, ref_logits_forced, ref_free):
+    """gpu_logits [n][V]; ref_logits_forced [n][V] = reference logits on the engine's history; ref_free = reference's own ids."""
+    n = len(got)
+    worst = max(rel_err(gpu_logits[i], ref_logits_forced[i]) for i in range(n))
+    flips = 0
+    for i in range(n):
+        r = ref_logits_forced[i]
+        top = int(np.argmax(r))
+        if top != got[i]:
+            margin, scale = float(r[top] - r[got[i]]), float(np.abs(r).max())
+            flips += 1
+            print(f"[margin report] {label}: step {i}: engine {got[i]} vs reference argmax {top}, reference margin "
+                  f"{margin:.3e} = {margin / scale:.1e} of max|logit| {scale:.2f}")
+            assert margin <= MARGIN_NOISE * scale, (label, i, got[i], top, margin, scale)
+    same = next((k for k in range(n) if got[k] != ref_free[k]), n)
+    print(f"[parity report] {label}: logits max rel err over {n} steps {worst:.2e} (tolerance {LOGIT_TOL}); teacher-forced argmax "
+          f"agrees on {n - flips}/{n} steps; free-running greedy ids identical for the first {same}/{n}")
+    assert worst <= LOGIT_TOL, (label, worst)
+    return same, flips
+
+
+def test_config0_tinyllama_shape_full_depth_against_the_fp32_oracle():
+    shape = O.TINYLLAMA
+    wseed, pseed = TINY_SEEDS
+    prompt = np.random.default_rng(pseed).integers(0, shape.vocab, 128).tolist()
+    n_new = 64
+    e, got, gpu_logits, lps = run_engine(shape, wseed, prompt, n_new, ctx=512)
+    fp32 = O.Oracle(shape, act_round=False); fp32.fill_synthetic(wseed, True)
+    # the engine's device generator and the oracle's produce the same bf16 bits (spot check at full size)
+    for kind, layer in [(O.WQ, 21), (O.WDOWN, 0), (O.LM_HEAD, 0), (O.MLP_NORM, 11)]:
+        assert np.array_equal(O.from_bf16_bits(e.read_tensor(kind, layer)), fp32.tensor(kind, layer).reshape(-1)), (kind, layer)
+    e.close()
+    hist = prompt + got
+    sid = fp32.seq_new()
+    forced = fp32.forward(hist[:-1], [sid] * (len(hist) - 1), np.arange(len(hist) - 1))[len(prompt) - 1:]
+    free = fp32.generate([prompt], n_new)
+    same, flips = judge("configs[0] TinyLlama-1.1B shape", got, gpu_logits, forced, free["tokens"][0])
+    assert flips <= 3, flips
+    # the oracle run with the engine's bf16 rounding points: same ids, up to the same rule (its own margins)
+    mimic = O.Oracle(shape, act_round=True); mimic.fill_synthetic(wseed, True)
+    w = mimic.generate([prompt], n_new, n_logit_steps=n_new)
+    if w["tokens"][0] != got:
+        i = next(k for k in range(n_new) if got[k] != w["tokens"][0][k])
+        margin, scale = float(w["margins"][0, i]), float(np.abs(w["logits"][0, i]).max())
+        print(f"[margin report] configs[0] vs bf16-rounding oracle: first difference at step {i}, margin {margin / scale:.1e} of max|logit|")
+        assert margin <= MARGIN_NOISE * scale, (i, margin, scale)
+    # TokenEvent.logprob of every step against log softmax of the fp32 reference logits (float64)
+    z = forced.astype(np.float64)
+    want = z[np.arange(n_new), got] - (np.log(np.exp(z - z.max(1, keepdims=True)).sum(1)) + z.max(1))
+    assert np.abs(lps - want).max() <= 2e-2 * np.abs(forced).max(), float(np.abs(lps - want).max())
+
+
+def hf_llama_fp32_on_gpu(shape, wseed):
+    """transformers LlamaForCausalLM, fp32, on cuda:0, holding the synthetic tensors (generated on the device by
+    dis_k_synth_bf16 -- the generator test_synthetic_device_weights_match_oracle_generator pins to the oracle's)."""
+    from transformers import LlamaConfig, LlamaForCausalLM
+    torch.backends.cuda.matmul.allow_tf32 = False
+    torch.backends.cudnn.allow_tf32 = False
+    cfg = LlamaConfig(vocab_size=shape.vocab, hidden_size=shape.hidden, intermediate_size=shape.inter,
+                      num_hidden_layers=shape.layers, num_attention_heads=shape.n_heads,
+                      num_key_value_heads=shape.n_kv_heads, head_dim=shape.head_dim, max_position_embeddings=shape.max_ctx,
+                      rms_norm_eps=shape.rms_eps, rope_theta=shape.rope_theta, tie_word_embeddings=False,
+                      attention_bias=False, mlp_bias=False, attn_implementation="eager")
+    if hasattr(cfg, "rope_parameters"):
+        cfg.rope_parameters = {"rope_type": "default", "rope_theta": shape.rope_theta}
+    with torch.device("cuda:0"):
+        m = LlamaForCausalLM(cfg).to(torch.float32).eval()
+    lib = B.load()
+    ccfg = shape.c()
+
+    def fill(param, kind, layer):
+        amp, off = C.c_float(), C.c_float()
+        O.lib().orc_synth_params(C.byref(ccfg), kind, C.byref(amp), C.byref(off))
+        tmp = torch.empty(param.numel(), dtype=torch.bfloat16, device="cuda:0")
+        rc = lib.dis_k_synth_bf16(C.c_void_p(tmp.data_ptr()), tmp.numel(), wseed, kind, layer, amp.value, off.value, None)
+        assert rc == B.OK, lib.dis_last_error()
+        torch.cuda.synchronize()
+        with torch.no_grad():
+            param.copy_(tmp.view(param.shape).float())
+
+    fill(m.model.embed_tokens.weight, O.EMBED, 0)
+    fill(m.model.norm.weight, O.FINAL_NORM, 0)
+    fill(m.lm_head.weight, O.LM_HEAD, 0)
+    for l, layer in enumerate(m.model.layers):
+        fill(layer.input_layernorm.weight, O.ATTN_NORM, l)
+        fill(layer.self_attn.q_proj.weight, O.WQ, l)
+        fill(layer.self_attn.k_proj.weight, O.WK, l)
+        fill(layer.self_attn.v_proj.weight, O.WV, l)
+        fill(layer.self_attn.o_proj.weight, O.WO, l)
+        fill(layer.post_attention_layernorm.weight, O.MLP_NORM, l)
+        fill(layer.mlp.gate_proj.weight, O.WGATE, l)
+        fill(layer.mlp.up_proj.weight, O.WUP, l)
+        fill(layer.mlp.down_proj.weight, O.WDOWN, l)
+    return m
+
+
+def test_config1_llama3_8b_full_depth_against_transformers_fp32():
+    shape = O.LLAMA3_8B
+    wseed, pseed = L8B_SEEDS
+    prompt = np.random.default_rng(pseed).integers(0, shape.vocab, 512).tolist()
+    n_new = 64
+    e, got, gpu_logits, _ = run_engine(shape, wseed, prompt, n_new, ctx=1024)
+    m = hf_llama_fp32_on_gpu(shape, wseed)
+    # the engine holds the same tensors as the checker (bit for bit), sampled at both ends of the stack
+    for kind, layer, p in [(O.WQ, 31, m.model.layers[31].self_attn.q_proj.weight), (O.WDOWN, 0, m.model.layers[0].mlp.down_proj.weight),
+                           (O.WUP, 17, m.model.layers[17].mlp.up_proj.weight), (O.LM_HEAD, 0, m.lm_head.weight)]:
+        mine = torch.from_numpy(O.from_bf16_bits(e.read_tensor(kind, layer))).view(p.shape)
+        assert torch.equal(mine, p.detach().cpu()), (kind, layer)
+    e.close()
+    with torch.no_grad():
+        hist = torch.tensor([prompt + got[:-1]], device="cuda:0")
+        forced = m(hist).logits[0, len(prompt) - 1:].float().cpu().numpy()
+        ids = torch.tensor([prompt], device="cuda:0")
+        free = m.generate(ids, max_new_tokens=n_new, do_sample=False, pad_token_id=0, eos_token_id=None)[0, len(prompt):].cpu().tolist()
+    del m
+    torch.cuda.empty_cache()
+    same, flips = judge("configs[1] Llama-3-8B, 32 layers", got, gpu_logits, forced, free)
+    # every step was judged above (teacher-forced); the free-running comparison may stop early only at a reported,
+    # sub-noise margin -- judge() has already asserted that for the step where it happens
+    assert flips <= 4, flips
