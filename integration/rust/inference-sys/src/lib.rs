@@ -56,6 +56,8 @@ extern "C" {
     pub fn dis_engine_seq_remove(e: *mut dis_engine, slot: i32) -> c_int;
     pub fn dis_engine_prefill(e: *mut dis_engine, n: i32, slots: *const i32, out_tokens: *mut u32, out_finish: *mut i32) -> c_int;
     pub fn dis_engine_decode(e: *mut dis_engine, n: i32, slots: *const i32, out_tokens: *mut u32, out_finish: *mut i32) -> c_int;
+    /// TokenEvent::Token.logprob (crates/core/src/models.rs:272-277) of each listed sequence's newest token.
+    pub fn dis_engine_last_logprobs(e: *mut dis_engine, n: i32, slots: *const i32, out_logprobs: *mut f32) -> c_int;
     pub fn dis_engine_status(e: *mut dis_engine, out: *mut dis_worker_status) -> c_int;
     pub fn dis_engine_prefix_stats(e: *mut dis_engine, out: *mut dis_prefix_stats) -> c_int;
     pub fn dis_engine_model_info(e: *mut dis_engine, out: *mut dis_model_config) -> c_int;

@@ -70,3 +70,15 @@ def test_product_never_imports_the_oracle():
             if f.endswith((".py", ".cu", ".cpp", ".h", ".hpp", ".cuh")):
                 text = open(os.path.join(dirpath, f), errors="ignore").read()
                 assert "liboracle" not in text and "from oracle" not in text and "import oracle" not in text, f
+
+
+def test_build_recipes_list_the_same_sources():
+    """The nvcc source list exists three times: build.py (what is built and tested here), the Rust build.rs a maintainer
+    of the reference would add, and its copy in INTEGRATION.md.  They must not drift apart."""
+    from distributed_inference_server_b200 import build as b
+    want = list(b.SOURCES)
+    for path in ("integration/rust/inference-sys/build.rs", "INTEGRATION.md"):
+        text = open(os.path.join(ROOT, path)).read()
+        block = text[text.index("let files = ["):]
+        block = block[:block.index("];")]
+        assert re.findall(r'"([\w.]+\.(?:cu|cpp))"', block) == want, path
