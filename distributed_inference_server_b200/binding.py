@@ -89,6 +89,7 @@ PROTOTYPES = {
     "dis_engine_seq_remove": (C.c_int, [vp, C.c_int32]),
     "dis_engine_prefill": (C.c_int, [vp, C.c_int32, vp, vp, vp]),
     "dis_engine_decode": (C.c_int, [vp, C.c_int32, vp, vp, vp]),
+    "dis_engine_step": (C.c_int, [vp, C.c_int32, vp, C.c_int32, vp, vp, vp]),
     "dis_engine_last_logits": (C.c_int, [vp, vp, C.c_int32]),
     "dis_engine_last_logprobs": (C.c_int, [vp, C.c_int32, vp, vp]),
     "dis_engine_profile_decode": (C.c_int, [vp, C.c_int32, vp, vp, vp, vp, vp]),
@@ -109,6 +110,8 @@ PROTOTYPES = {
     "dis_serving_step": (C.c_int, [vp, C.POINTER(ServingEvent), C.c_int32, i32p]),
     "dis_serving_step_at": (C.c_int, [vp, C.c_double, C.POINTER(ServingEvent), C.c_int32, i32p]),
     "dis_serving_depth": (C.c_int, [vp, C.POINTER(QueueDepth)]),
+    "dis_serving_set_prefill_budget": (C.c_int, [vp, C.c_int32]),
+    "dis_serving_plan_step": (C.c_int, [C.c_int32, vp, C.c_int32, C.c_int32, vp]),
     "dis_serving_debug_pop": (C.c_int, [vp, C.c_int32, vp, i32p]),
     "dis_engine_prefix_stats": (C.c_int, [vp, C.POINTER(PrefixStats)]),
     "dis_prefix_index_create": (C.c_int, [C.c_int32, C.c_int64, C.POINTER(vp)]),

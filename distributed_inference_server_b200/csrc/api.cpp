@@ -80,6 +80,17 @@ int dis_engine_decode(dis_engine *e, int32_t n, const int32_t *slots, uint32_t *
   LOCKED(e);
   return e->eng.decode(n, slots, out_tokens, out_finish);
 }
+int dis_engine_step(dis_engine *e, int32_t n, const int32_t *slots, int32_t max_prefill_tokens, uint32_t *out_tokens,
+                    int32_t *out_finish, int32_t *out_produced) {
+  if (int rc = guard_null(e)) return rc;
+  LOCKED(e);
+  return e->eng.step_mixed(n, slots, max_prefill_tokens, out_tokens, out_finish, out_produced);
+}
+int dis_serving_plan_step(int32_t n, const int32_t *remaining_prompt, int32_t budget, int32_t cap, int32_t *take) {
+  if (n < 0 || (n > 0 && (!remaining_prompt || !take))) return DIS_ERR_INVALID_ARGUMENT;
+  dis::plan_mixed_step(n, remaining_prompt, budget, cap, take);
+  return DIS_OK;
+}
 int dis_engine_profile_decode(dis_engine *e, int32_t n, const int32_t *slots, uint32_t *out_tokens, int32_t *out_finish,
                               float *class_ms, int32_t *class_launches) {
   if (int rc = guard_null(e)) return rc;

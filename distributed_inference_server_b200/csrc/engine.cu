@@ -215,6 +215,13 @@ int Engine::init(const dis_engine_config *c) {
   use_pdl = !(c->flags & DIS_FLAG_NO_PDL);
   if (const char *g = getenv("DIS_GEMM_PERSIST")) use_persist = atoi(g) != 0;
   if (const char *g = getenv("DIS_GEMV_MAX_T")) gemv_max_t = std::max(0, std::min(kGemvMaxT, atoi(g)));
+  // Measurement aid, never set in production: DIS_DEBUG_SKIP=norm,attn,... leaves those kernel classes out of the
+  // decode step (its results are then garbage) so that step time with and without a class gives the class's marginal
+  // cost INSIDE the graph, where programmatic dependent launch overlaps neighbours and ncu's isolated times mislead.
+  if (const char *g = getenv("DIS_DEBUG_SKIP")) {
+    const char *names[] = {"norm", "qkv", "rope", "attn", "oproj", "gateup", "down"};
+    for (int i = 0; i < 7; i++) if (strstr(g, names[i])) skip_mask |= 1u << i;
+  }
   // ---- tensor parallel communicator
   if (tp_size > 1) {
     std::string err;
@@ -280,11 +287,13 @@ int Engine::tp_import(const uint8_t *handles) {
   // measured at batch 64, H = 4096, ms per step (one-shot / fenced two-shot / flag-in-data two-shot):
   //   TP=2  3.44 / 3.76 / 3.28      TP=4  2.80 / 3.00 / 2.64      TP=8  2.88 / 2.67 / 2.42
   // The choice is fixed per engine (the kernels lay the symmetric buffer out differently).
-  peers.two_shot = m.hidden % (4 * tp_size) == 0 ? 2 : 0;
+  const bool blocks_ok = m.hidden % (4 * tp_size) == 0;
+  peers.two_shot = blocks_ok ? ((m.hidden / tp_size) % 128 == 0 ? 3 : 2) : 0;
   if (const char *e = getenv("DIS_TP_EXCHANGE")) {
     if (!strcmp(e, "oneshot")) peers.two_shot = 0;
-    else if (!strcmp(e, "twoshot") && m.hidden % (4 * tp_size) == 0) peers.two_shot = 1;
-    else if (!strcmp(e, "ll") && m.hidden % (4 * tp_size) == 0) peers.two_shot = 2;
+    else if (!strcmp(e, "twoshot") && blocks_ok) peers.two_shot = 1;
+    else if (!strcmp(e, "ll") && blocks_ok) peers.two_shot = 2;
+    else if (!strcmp(e, "wide") && blocks_ok && (m.hidden / tp_size) % 128 == 0) peers.two_shot = 3;
   }
   tp_custom = true;
   return DIS_OK;
@@ -476,6 +485,7 @@ int Engine::seq_add(const uint32_t *prompt, int n, const dis_sampling_params *p,
   for (int i = 0; i < hit; i++) h_page_table[(size_t)slot * max_pages + i] = s.pages[(size_t)i];
   if (hit) pt_dirty = true;
   s.cached = hit * page_size;
+  s.prefill_pos = s.cached;
   if (!ensure_pages(s, slot, n + 1)) { release_pages(s); return fail(DIS_ERR_OUT_OF_MEMORY, "seq_add: out of KV pages"); }
   s.used = true;
   s.prompt.assign(prompt, prompt + n);
@@ -616,6 +626,7 @@ cudaError_t Engine::enqueue_layers(int T, int n_splits) {
   // kernel-level calls on this host thread must not inherit it
   struct PdlOff { ~PdlOff() { pdl_enabled() = false; } } pdl_off;
   pend_ptr = nullptr; pend_count = 0; pend_str = 0; pend_needs_ar = false;
+  auto skip = [&](int cls) { return n_qblocks == 0 && tp_size == 1 && (skip_mask >> cls) & 1u; };
   const uint32_t *tokens = cur_meta->d<uint32_t>(cur_meta->o_tokens);
   const int *pos = cur_meta->d<int>(cur_meta->o_pos), *ptrow = cur_meta->d<int>(cur_meta->o_ptrow), *ctx = cur_meta->d<int>(cur_meta->o_ctx);
   // a projection output becomes "pending": the next norm kernel adds it to the residual
@@ -635,12 +646,13 @@ cudaError_t Engine::enqueue_layers(int T, int n_splits) {
       kernel_launches++;
     } else {
       pdl_enabled() = pdl_ok;
-      RET_CUDA(consume_pending(attn_norm + (size_t)l * H, nullptr, T, T));
+      if (!skip(P_NORM)) RET_CUDA(consume_pending(attn_norm + (size_t)l * H, nullptr, T, T));
     }
     pdl_enabled() = pdl_ok;
     int s_qkv = 1;
     prof_mark(P_QKV);
-    RET_CUDA(linear_partial(xn_map, xn, wqkv_map, wqkv, l * nqkv_l, T, nqkv_l, H, &s_qkv));
+    if (!skip(P_QKV)) RET_CUDA(linear_partial(xn_map, xn, wqkv_map, wqkv, l * nqkv_l, T, nqkv_l, H, &s_qkv));
+    else s_qkv = gemm_pick_split_k(T, nqkv_l, H);
     uint16_t *pool = kv_pool + (size_t)l * kv_layer_stride;
     if (n_qblocks > 0) {
       prof_mark(P_ROPE);
@@ -655,17 +667,18 @@ cudaError_t Engine::enqueue_layers(int T, int n_splits) {
     } else {
       // decode: RoPE + KV write live inside the attention kernel (one kernel boundary less per layer)
       prof_mark(P_ATTN);
-      RET_CUDA(launch_attn_decode_fused(kv_map, (long long)l * kv_rows_per_layer, pool, partial, s_qkv, (long long)T * nqkv_l,
+      if (!skip(P_ATTN)) RET_CUDA(launch_attn_decode_fused(kv_map, (long long)l * kv_rows_per_layer, pool, partial, s_qkv, (long long)T * nqkv_l,
                                         pos, rope_cos, rope_sin, d_page_table, max_pages, ptrow, ctx, attn, attn_scratch,
                                         n_splits, T, nh_l, nkv_l, d, page_size, stream));
       kernel_launches += n_splits > 1 ? 2 : 1;
     }
     int s_o = 1;
     prof_mark(P_OPROJ);
-    RET_CUDA(linear_partial(attn_map, attn, wo_map, wo, l * H, T, H, qd_l, &s_o));
+    if (!skip(P_OPROJ)) RET_CUDA(linear_partial(attn_map, attn, wo_map, wo, l * H, T, H, qd_l, &s_o));
+    else s_o = gemm_pick_split_k(T, H, qd_l);
     RET_CUDA(set_pending(s_o));
     prof_mark(P_NORM);
-    RET_CUDA(consume_pending(mlp_norm + (size_t)l * H, nullptr, T, T));
+    if (!skip(P_NORM)) RET_CUDA(consume_pending(mlp_norm + (size_t)l * H, nullptr, T, T));
     prof_mark(P_GATEUP);
     if (gemv) {
       RET_CUDA(launch_gemv_silu(xn, wgu + (size_t)l * 2 * inter_l * H, act, T, inter_l, H, stream));
@@ -684,13 +697,14 @@ cudaError_t Engine::enqueue_layers(int T, int n_splits) {
       RET_CUDA(launch_gemm_partial(wgu_map128, xn_map[tile_index(T)], partial, T, 2 * inter_l, H, l * 2 * inter_l, sgu, stream));
       RET_CUDA(launch_silu_mul_reduce(partial, sgu, (long long)T * 2 * inter_l, act, T, inter_l, stream));
       kernel_launches += 2;
-    } else {
+    } else if (!skip(P_GATEUP)) {
       RET_CUDA(launch_gemm_silu(wgu_map, xn_map[tile_index(T)], act, T, inter_l, H, l * 2 * inter_l, gemm_pick_tile_rows(inter_l), stream));
       kernel_launches++;
     }
     int s_d = 1;
     prof_mark(P_DOWN);
-    RET_CUDA(linear_partial(act_map, act, wdown_map, wdown, l * H, T, H, inter_l, &s_d));
+    if (!skip(P_DOWN)) RET_CUDA(linear_partial(act_map, act, wdown_map, wdown, l * H, T, H, inter_l, &s_d));
+    else s_d = gemm_pick_split_k(T, H, inter_l);
     RET_CUDA(set_pending(s_d));
   }
   pdl_enabled() = false;
@@ -771,7 +785,7 @@ int Engine::prefill(int n, const int *slots, uint32_t *out_tokens, int *out_fini
   cur_meta = &meta_pre;
   struct MetaReset { Engine *e; ~MetaReset() { e->cur_meta = &e->meta_dec; e->n_qblocks = 0; } } meta_reset{this};
   // flatten (sequence, position) pairs and cut them into chunks of at most cap_tokens
-  int si = 0, sp = seqs[(size_t)slots[0]].cached;  // next sequence index / position inside it (behind its cached prefix)
+  int si = 0, sp = seqs[(size_t)slots[0]].prefill_pos;  // next sequence index / position inside it (behind what is cached already)
   bool all_greedy = true;
   for (int i = 0; i < n; i++) all_greedy = all_greedy && seqs[(size_t)slots[i]].temperature <= 0.f;
   while (si < n) {
@@ -806,7 +820,7 @@ int Engine::prefill(int n, const int *slots, uint32_t *out_tokens, int *out_fini
         owners.push_back(si);
         R++;
         si++;
-        sp = si < n ? seqs[(size_t)slots[si]].cached : 0;
+        sp = si < n ? seqs[(size_t)slots[si]].prefill_pos : 0;
       }
     }
     n_qblocks = QB;
@@ -838,10 +852,142 @@ int Engine::prefill(int n, const int *slots, uint32_t *out_tokens, int *out_fini
   for (int i = 0; i < n; i++) {
     Sequence &s = seqs[(size_t)slots[i]];
     s.len = (int)s.prompt.size();
+    s.prefill_pos = s.len;
     s.prefilled = true;
     pages_ix.commit(s.prompt.data(), s.len / page_size, s.pages);  // full prompt pages become reusable (no-op when off)
     finish_check(s, out_tokens[i]);
     out_finish[i] = s.finish;
+  }
+  return DIS_OK;
+}
+
+// ------------------------------------------------------------------------------------ mixed step
+// How one forward pass is shared between running sequences and prompts that are still being read (chunked prefill,
+// SURVEY.md §8 row f1): every decode row gets its one token; the remaining room -- at most `budget` prompt tokens and
+// never more than `cap` tokens in the pass -- goes to the unfinished prompts IN LIST ORDER, so an earlier request
+// (the admission queue's order: priority lane, then arrival) is never overtaken by a later one.  Pure function:
+// exported as dis_serving_plan_step so that the rule is property-tested without a GPU.
+void plan_mixed_step(int n, const int *remaining_prompt, int budget, int cap, int *take) {
+  int decode_rows = 0;
+  for (int i = 0; i < n; i++) decode_rows += remaining_prompt[i] <= 0 ? 1 : 0;
+  long long room = std::max(0, std::min(budget, cap - decode_rows));
+  for (int i = 0; i < n; i++) {
+    if (remaining_prompt[i] <= 0) { take[i] = 1; continue; }
+    const int t = (int)std::min<long long>(remaining_prompt[i], room);
+    take[i] = t;
+    room -= t;
+  }
+}
+
+// One forward pass over decode rows and prompt chunks together.  A listed sequence that is already prefilled
+// contributes its last sampled token (exactly what dis_engine_decode would do); one that is not contributes the next
+// chunk of its prompt, and samples its first token in the pass that finishes the prompt.  out_produced[i] = 1 where
+// out_tokens[i] holds a new token.  The pass runs the prefill kernels: a decode row is a one-token query block.
+int Engine::step_mixed(int n, const int *slots, int max_prefill_tokens, uint32_t *out_tokens, int *out_finish, int *out_produced) {
+  if (shut) return fail(DIS_ERR_SHUTDOWN, "engine is shut down");
+  if (!loaded) return fail(DIS_ERR_MODEL_NOT_LOADED, "model not loaded");
+  if (n <= 0 || n > max_batch || !slots || !out_tokens || !out_finish || !out_produced) return fail(DIS_ERR_INVALID_ARGUMENT, "step: bad argument");
+  const uint64_t stamp = ++call_stamp;
+  for (int i = 0; i < n; i++) {
+    if (slots[i] < 0 || slots[i] >= max_batch || !seqs[(size_t)slots[i]].used) return fail(DIS_ERR_INVALID_ARGUMENT, "step: no such sequence");
+    if (slot_stamp[(size_t)slots[i]] == stamp) return fail(DIS_ERR_INVALID_ARGUMENT, "step: duplicate slot");
+    slot_stamp[(size_t)slots[i]] = stamp;
+  }
+  ENG_CUDA(cudaSetDevice(cfg.device));
+  // rows that cannot run fail alone (Property 22, design.md:812-816)
+  std::vector<int> remaining((size_t)n), take((size_t)n);
+  std::vector<char> live((size_t)n, 0);
+  std::vector<int> idx;
+  for (int i = 0; i < n; i++) {
+    Sequence &s = seqs[(size_t)slots[i]];
+    out_tokens[i] = 0; out_produced[i] = 0; out_finish[i] = s.finish;
+    if (s.finish != DIS_FINISH_NONE) continue;
+    if (s.prefilled && (s.len + 1 > m.max_ctx || !ensure_pages(s, slots[i], s.len + 1))) { s.finish = DIS_FINISH_FAILED; out_finish[i] = s.finish; continue; }
+    live[(size_t)i] = 1;
+    idx.push_back(i);
+  }
+  if (idx.empty()) { last_rows = 0; return DIS_OK; }
+  std::vector<int> rem_live, take_live(idx.size());
+  for (int i : idx) { const Sequence &s = seqs[(size_t)slots[i]]; rem_live.push_back(s.prefilled ? 0 : (int)s.prompt.size() - s.prefill_pos); }
+  plan_mixed_step((int)idx.size(), rem_live.data(), max_prefill_tokens > 0 ? max_prefill_tokens : cap_tokens, cap_tokens, take_live.data());
+  ENG_CUDA(cudaEventRecord(ev0, stream));
+  cur_meta = &meta_pre;
+  struct MetaReset { Engine *e; ~MetaReset() { e->cur_meta = &e->meta_dec; e->n_qblocks = 0; } } meta_reset{this};
+  int T = 0, R = 0, QB = 0;
+  bool all_greedy = true;
+  std::vector<int> owners;  // logits row -> position in the caller's list
+  for (size_t k = 0; k < idx.size(); k++) {
+    const int i = idx[k];
+    Sequence &s = seqs[(size_t)slots[i]];
+    const int tk = take_live[k];
+    if (tk <= 0) continue;  // no room for this prompt in this pass
+    const bool dec = s.prefilled;
+    const int p0 = dec ? s.len : s.prefill_pos;
+    for (int j = 0; j < tk; j++) {
+      cur_meta->h<uint32_t>(cur_meta->o_tokens)[T + j] = dec ? s.last_token : s.prompt[(size_t)(p0 + j)];
+      cur_meta->h<int>(cur_meta->o_pos)[T + j] = p0 + j;
+      cur_meta->h<int>(cur_meta->o_ptrow)[T + j] = slots[i];
+      cur_meta->h<int>(cur_meta->o_ctx)[T + j] = p0 + j + 1;
+    }
+    for (int j = 0; j < tk; j += 16) {
+      cur_meta->h<int>(cur_meta->o_qb_tok0)[QB] = T + j;
+      cur_meta->h<int>(cur_meta->o_qb_len)[QB] = std::min(16, tk - j);
+      cur_meta->h<int>(cur_meta->o_qb_pos0)[QB] = p0 + j;
+      cur_meta->h<int>(cur_meta->o_qb_ptrow)[QB] = slots[i];
+      QB++;
+    }
+    T += tk;
+    const bool ends = dec || p0 + tk == (int)s.prompt.size();
+    if (ends) {
+      cur_meta->h<int>(cur_meta->o_rowmap)[R] = T - 1;
+      cur_meta->h<float>(cur_meta->o_temp)[R] = s.temperature;
+      cur_meta->h<float>(cur_meta->o_topp)[R] = s.top_p;
+      cur_meta->h<unsigned long long>(cur_meta->o_seed)[R] = s.seed;
+      cur_meta->h<unsigned long long>(cur_meta->o_step)[R] = (unsigned long long)s.generated;
+      all_greedy = all_greedy && s.temperature <= 0.f;
+      owners.push_back(i);
+      R++;
+    }
+  }
+  if (T == 0) { last_rows = 0; return DIS_OK; }
+  n_qblocks = QB;
+  last_T = T;
+  rowmap_identity = false;
+  ENG_CUDA(upload_step(T, R));
+  ENG_CUDA(enqueue_layers(T, 1));
+  if (R > 0) {
+    ENG_CUDA(enqueue_head(R, all_greedy));
+    ENG_CUDA(cudaMemcpyAsync(h_out_tokens, d_out_tokens, (size_t)(max_batch + R) * 4, cudaMemcpyDeviceToHost, stream));
+  } else if (pend_needs_ar) {
+    ENG_CUDA(consume_pending(final_norm, nullptr, T, T));  // keep the exchange count per pass even (see prefill)
+  }
+  ENG_CUDA(cudaEventRecord(ev1, stream));
+  ENG_CUDA(cudaEventSynchronize(ev1));
+  float ms = 0.f;
+  ENG_CUDA(cudaEventElapsedTime(&ms, ev0, ev1));
+  last_step_ms = ms;
+  last_rows = R;
+  // advance the sequences
+  int r = 0;
+  for (size_t k = 0; k < idx.size(); k++) {
+    const int i = idx[k];
+    Sequence &s = seqs[(size_t)slots[i]];
+    const int tk = take_live[k];
+    if (tk <= 0) continue;
+    if (s.prefilled) s.len += 1;
+    else {
+      s.prefill_pos += tk;
+      if (s.prefill_pos < (int)s.prompt.size()) continue;  // more chunks to come
+      s.len = (int)s.prompt.size();
+      s.prefilled = true;
+      pages_ix.commit(s.prompt.data(), s.len / page_size, s.pages);
+    }
+    out_tokens[i] = h_out_tokens[r];
+    s.last_logprob = reinterpret_cast<const float *>(h_out_tokens + max_batch)[r];
+    finish_check(s, h_out_tokens[r]);
+    out_finish[i] = s.finish;
+    out_produced[i] = 1;
+    r++;
   }
   return DIS_OK;
 }

@@ -33,6 +33,7 @@ struct Sequence {
   std::vector<uint32_t> prompt;
   std::vector<uint32_t> gen;  // sampled tokens (kept only while the prefix cache is on)
   int cached = 0;          // leading prompt tokens whose K/V came from the prefix cache
+  int prefill_pos = 0;     // prompt tokens whose K/V are in the cache already (prefix hit + chunks run so far)
   int len = 0;             // tokens whose K/V are in the cache
   uint32_t last_token = 0;  // sampled, not yet in the cache
   float last_logprob = 0.f; // log-probability of last_token (TokenEvent.logprob)
@@ -59,6 +60,8 @@ struct StepMeta {
   template <class T_> T_ *h(size_t off) { return reinterpret_cast<T_ *>(host + off); }
   template <class T_> T_ *d(size_t off) { return reinterpret_cast<T_ *>(dev + off); }
 };
+
+void plan_mixed_step(int n, const int *remaining_prompt, int budget, int cap, int *take);
 
 struct Engine {
   dis_engine_config cfg{};
@@ -97,6 +100,7 @@ struct Engine {
   TmaMap kv_map;  // the whole pool as [rows][head_dim]
   bool use_pdl = true;  // programmatic dependent launch between the kernels of a step
   bool use_persist = true;  // prefill-sized projections through the persistent GEMM (DIS_GEMM_PERSIST=0: A/B runs)
+  unsigned skip_mask = 0;  // DIS_DEBUG_SKIP (measurement only): kernel classes left out of the step, bit = ProfClass
   int gemv_max_t = 1;   // steps of at most this many tokens take the GEMV path; from 2 tokens the tcgen05 path is faster (3.03 vs 4.09 ms per step). DIS_GEMV_MAX_T overrides, for A/B runs
   PrefixIndex pages_ix;  // page allocator; with DIS_FLAG_PREFIX_CACHE also the prefix index (row f2)
   int *d_page_table = nullptr, *h_page_table = nullptr;
@@ -155,6 +159,7 @@ struct Engine {
   int seq_remove(int slot);
   int prefill(int n, const int *slots, uint32_t *out_tokens, int *out_finish);
   int decode(int n, const int *slots, uint32_t *out_tokens, int *out_finish);
+  int step_mixed(int n, const int *slots, int max_prefill_tokens, uint32_t *out_tokens, int *out_finish, int *out_produced);
   int last_logits_host(float *host, int rows);
   int last_logprobs(int n, const int *slots, float *out);
   int status(dis_worker_status *out);

@@ -13,7 +13,8 @@
 //   tp_add_rmsnorm_kernel     one-shot push, one flag hop                       (tp-1)   * T*H*4 bytes per rank
 //   tp_add_rmsnorm2_kernel    reduce-scatter + all-gather of column blocks      2(tp-1)/tp * T*H*4, two flag hops
 //   tp_add_rmsnorm_ll_kernel  the same two hops with the flag inside the data   4(tp-1)/tp * T*H*4, no fence, no flag
-//                             (DEFAULT: 3.28 / 2.64 / 2.42 ms per step at TP = 2 / 4 / 8, batch 64)
+//                             (round 1 default: 3.28 / 2.64 / 2.42 ms per step at TP = 2 / 4 / 8, batch 64)
+//   tp_add_rmsnorm_wide_kernel  the ll protocol on a (row, column block) grid that covers every SM (see below)
 //
 // The first is a one-shot all-reduce: every rank sends (tp-1) * T * H * 4 bytes; no NVLink round trip is on the
 // critical path (stores are fire-and-forget, polling and reads are local).  Synchronisation is per ROW (a
@@ -339,6 +340,130 @@ tp_add_rmsnorm_ll_kernel(TpPeers peers, float *__restrict__ x, const float *__re
   }
 }
 
+// Wide-grid variant of the flag-in-data exchange (two_shot == 3, the default where it applies): the same two hops, but
+// one CTA per (row, column block) instead of one per row, so that at TP=8 a 64-row exchange runs on 512 small CTAs
+// spread over every SM instead of 64 CTAs of 1024 threads that first walk 8-9 split-K slices of a whole row.
+//   CTA (t, c), c = the owner rank of columns [c*Hs, (c+1)*Hs), one float4 per thread:
+//     hop 1   sum the split-K slices of its 4 columns; c != me: send them to rank c's RS area, flag in the data
+//     c == me sum the tp contributions IN RANK ORDER + residual, send the finished block to every peer's AG area
+//             (hop 2), reduce the block's sum of squares and send that too: one 8-byte {value, epoch} word per
+//             (owner, row) in the area the fenced kernels use for their flags
+//     c != me take the finished block from the AG area as it arrives
+//     all     total sum of squares = the tp block sums added in rank order (every rank, every CTA: same bits),
+//             RMSNorm of its 4 columns.
+// The sum of squares is associated differently from the row kernels (per block, then over blocks), so this variant
+// is deterministic and identical on every rank but NOT bit-identical to the other three.
+// No CTA waits for a CTA of its own GPU that might not be resident yet, except for the block sum of its own rank's
+// owner CTA: owner CTAs have the lowest block indices, and the launcher only uses this kernel when the whole grid is
+// co-resident anyway (a CTA that has not started has not sent its hop-1 data, which a peer's owner CTA waits for).
+__device__ __forceinline__ void st_ll1(uint32_t *p, float v, uint32_t e) {
+  asm volatile("st.global.v2.u32 [%0], {%1,%2};" ::"l"(p), "r"(__float_as_uint(v)), "r"(e) : "memory");
+}
+__device__ __forceinline__ float ld_ll1(const uint32_t *p, uint32_t e) {
+  uint32_t a, f;
+  long long spins = 0;
+  do {
+    asm volatile("ld.volatile.global.v2.u32 {%0,%1}, [%2];" : "=r"(a), "=r"(f) : "l"(p) : "memory");
+    if (++spins > (1ll << 27)) __trap();
+  } while (f != e);
+  return __uint_as_float(a);
+}
+
+__global__ void __launch_bounds__(1024)
+tp_add_rmsnorm_wide_kernel(TpPeers peers, float *__restrict__ x, const float *__restrict__ partial, int n_partial,
+                           long long partial_stride, const float *__restrict__ gain, uint16_t *__restrict__ xn,
+                           const uint32_t *__restrict__ step_ptr, uint32_t idx, int parity, int H, float eps) {
+  __shared__ float red[32];
+  __shared__ float s_inv;
+  const int t = blockIdx.x;
+  const int me = peers.rank, tp = peers.tp, cap = peers.cap_rows;
+  const int c = (int)((blockIdx.y + (unsigned)me) % (unsigned)tp);  // blockIdx.y == 0: this rank's own block (scheduled first)
+  pdl_launch_dependents();
+  pdl_wait();
+  const uint32_t epoch = *step_ptr * 256u + idx;
+  const int Hs = H / tp;
+  const int j = threadIdx.x * 4;          // column inside the block
+  const int col = c * Hs + j;
+  const size_t ag_base = (size_t)4 * cap * H;
+  const size_t blk = (((size_t)parity * tp + me) * cap + t) * (size_t)Hs * 2;  // block written by this rank, row t (pairs)
+
+  // ---- hop 1: split-K reduce of these 4 columns
+  float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+  {
+    const float *pp = partial + (size_t)t * H + col;
+#pragma unroll 4
+    for (int s = 0; s < n_partial; s++) {
+      const float4 p = *reinterpret_cast<const float4 *>(pp + (size_t)s * partial_stride);
+      v.x += p.x; v.y += p.y; v.z += p.z; v.w += p.w;
+    }
+  }
+  float4 a;
+  if (c != me) {
+    float *dst = peers.data[c] + blk + (size_t)j * 2;
+    st_ll(dst, v.x, v.y, epoch);
+    st_ll(dst + 4, v.z, v.w, epoch);
+    // the finished block comes back from its owner
+    const float *src = peers.data[me] + ag_base + (((size_t)parity * tp + c) * cap + t) * (size_t)Hs * 2 + (size_t)j * 2;
+    ld_ll(src, epoch, a.x, a.y);
+    ld_ll(src + 4, epoch, a.z, a.w);
+  } else {
+    a = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int r = 0; r < tp; r++) {
+      float4 w;
+      if (r == me) w = v;
+      else {
+        const float *src = peers.data[me] + (((size_t)parity * tp + r) * cap + t) * (size_t)Hs * 2 + (size_t)j * 2;
+        ld_ll(src, epoch, w.x, w.y);
+        ld_ll(src + 4, epoch, w.z, w.w);
+      }
+      a.x += w.x; a.y += w.y; a.z += w.z; a.w += w.w;
+    }
+    const float4 xv = *reinterpret_cast<const float4 *>(x + (size_t)t * H + col);
+    a.x += xv.x; a.y += xv.y; a.z += xv.z; a.w += xv.w;
+    for (int r = 0; r < tp; r++)
+      if (r != me) {
+        float *dst = peers.data[r] + ag_base + blk + (size_t)j * 2;
+        st_ll(dst, a.x, a.y, epoch);
+        st_ll(dst + 4, a.z, a.w, epoch);
+      }
+    // this block's sum of squares, to everybody (this rank included)
+    const float ssb = tp_block_sum(sumsq4(0.f, a), red);
+    const size_t w = (((size_t)parity * tp + me) * cap + t) * 2;
+    if ((int)threadIdx.x < tp) st_ll1(peers.flags[threadIdx.x] + w, ssb, epoch);
+  }
+  *reinterpret_cast<float4 *>(x + (size_t)t * H + col) = a;
+  // ---- total sum of squares: the tp block sums in rank order
+  if (threadIdx.x == 0) {
+    float ss = 0.f;
+    for (int o = 0; o < tp; o++) ss += ld_ll1(peers.flags[me] + (((size_t)parity * tp + o) * cap + t) * 2, epoch);
+    s_inv = rsqrtf(ss / (float)H + eps);
+  }
+  __syncthreads();
+  const float inv = s_inv;
+  const float4 g = *reinterpret_cast<const float4 *>(gain + col);
+  uint2 o;
+  o.x = float2_to_bf16x2(a.x * inv * g.x, a.y * inv * g.y);
+  o.y = float2_to_bf16x2(a.z * inv * g.z, a.w * inv * g.w);
+  *reinterpret_cast<uint2 *>(xn + (size_t)t * H + col) = o;
+}
+
+// whether the wide-grid kernel may be used for T rows: every CTA of the grid must be resident at once
+static bool tp_wide_fits(const TpPeers &peers, int T, int H) {
+  const int Hs = H / peers.tp;
+  if (H % peers.tp != 0 || Hs % 128 != 0 || Hs / 4 > 1024) return false;
+  static int per_sm_cache[33] = {0};  // by threads / 32
+  const int threads = Hs / 4;
+  int &per_sm = per_sm_cache[threads / 32];
+  if (per_sm == 0) {
+    int n = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, tp_add_rmsnorm_wide_kernel, threads, 0) != cudaSuccess || n <= 0) { cudaGetLastError(); return false; }
+    per_sm = n;
+  }
+  int dev = 0, sms = kNumSMs;
+  if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  return (long long)T * peers.tp <= (long long)per_sm * sms;
+}
+
 cudaError_t launch_tp_add_rmsnorm(const TpPeers &peers, float *x, const float *partial, int n_partial,
                                   long long partial_stride, const float *gain, uint16_t *xn, const uint32_t *step_ptr,
                                   uint32_t idx, int parity, int T, int H, float eps, cudaStream_t st) {
@@ -347,7 +472,11 @@ cudaError_t launch_tp_add_rmsnorm(const TpPeers &peers, float *x, const float *p
   if (H % 4 != 0) { set_last_error("tp_add_rmsnorm: H must be a multiple of 4"); return cudaErrorInvalidValue; }
   int threads = (H / 4 + 31) / 32 * 32;
   threads = threads > 1024 ? 1024 : threads;
-  if (peers.two_shot == 2) {
+  if (peers.two_shot == 3 && tp_wide_fits(peers, T, H)) {
+    return launch_k(tp_add_rmsnorm_wide_kernel, dim3(T, peers.tp), dim3(H / peers.tp / 4), 0, st, peers, x, partial, n_partial,
+                    partial_stride, gain, xn, step_ptr, idx, parity, H, eps);
+  }
+  if (peers.two_shot >= 2) {
     if (H % (4 * peers.tp) != 0) { set_last_error("tp_add_rmsnorm: the LL exchange needs H % (4 * tp) == 0"); return cudaErrorInvalidValue; }
     const size_t smem2 = (size_t)H * sizeof(float);
     if (smem2 > 48 * 1024) DIS_CUDA_TRY(cudaFuncSetAttribute(tp_add_rmsnorm_ll_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));

@@ -7,9 +7,10 @@
 //                      :198-226 remove_expired, :235-249 watermarks; defaults :24-33) -- a new implementation,
 //                      with an explicit clock so that it can be tested without sleeping.
 //   ContinuousBatcher  the scheduler the reference only has as a window batcher in its spec (design.md:227-267,
-//                      requirements.md:45-48): between decode steps it admits queued requests into free
-//                      engine slots (KV pages permitting), prefills the newcomers, decodes everybody, retires
-//                      finished sequences and reports one event per token (TokenEvent, models.rs:268-288).
+//                      requirements.md:45-48): every step admits queued requests into free engine slots (KV pages
+//                      permitting) and runs ONE forward pass in which every running sequence decodes a token and
+//                      the admitted prompts advance by a bounded chunk (dis_engine_step), retires finished
+//                      sequences and reports one event per token (TokenEvent, models.rs:268-288).
 #include <algorithm>
 #include <chrono>
 #include <cstring>
@@ -117,8 +118,7 @@ struct dis_serving {
   std::deque<dis_serving_event> pending;
   std::mutex mu;
   int32_t max_active = 0;
-  int32_t prefill_budget = 8192;  // prompt tokens admitted per scheduler step
-  bool decode_next = false;       // after a prefill step the running sequences get a decode step before the next admission
+  int32_t prefill_budget = 2048;  // prompt tokens read per scheduler step (beside one token for every running sequence)
   std::string last_error;
   explicit dis_serving(const dis_queue_config &c) : cfg(c), queue(c) {}
 };
@@ -179,6 +179,13 @@ int dis_serving_submit_at(dis_serving *s, const uint8_t request_id[16], const ui
 int dis_serving_submit(dis_serving *s, const uint8_t request_id[16], const uint32_t *prompt, int32_t n_prompt,
                        const dis_sampling_params *params, int32_t priority) {
   return dis_serving_submit_at(s, request_id, prompt, n_prompt, params, priority, steady_now());
+}
+
+int dis_serving_set_prefill_budget(dis_serving *s, int32_t tokens) {
+  if (!s || tokens < 1) return DIS_ERR_INVALID_ARGUMENT;
+  std::lock_guard<std::mutex> lk(s->mu);
+  s->prefill_budget = tokens;
+  return DIS_OK;
 }
 
 int dis_serving_depth(dis_serving *s, dis_queue_depth *out) {
@@ -243,81 +250,68 @@ static int step_impl(dis_serving *s, double now_s, bool clock_injected, dis_serv
   for (auto &q : expired) emit(s, q.id, DIS_EVENT_EXPIRED, 0, 0, DIS_FINISH_FAILED, (int32_t)q.prompt.size(), (now_s - q.enqueued_at) * 1e3);
   if (!s->eng) return drain(s, events, cap, n_events);
 
-  // 2. admission: free slots, High -> Normal -> Low, a bounded number of prompt tokens per step
-  std::vector<Active> fresh;
-  if (!(s->decode_next && !s->active.empty())) {
-    int budget = s->prefill_budget;
-    Queued q;
-    while ((int32_t)(s->active.size() + fresh.size()) < s->max_active && budget > 0 && s->queue.pop(&q)) {
-      dis_sampling_params p = q.params;
-      p.stop_tokens = q.stop_tokens.empty() ? nullptr : q.stop_tokens.data();
-      p.stop_lens = q.stop_lens.empty() ? nullptr : q.stop_lens.data();
-      p.n_stop = (int32_t)q.stop_lens.size();
-      int32_t slot = -1;
-      const int rc = dis_engine_seq_add(s->eng, q.prompt.data(), (int32_t)q.prompt.size(), &p, &slot);
-      if (rc == DIS_ERR_OUT_OF_MEMORY && (!s->active.empty() || !fresh.empty())) {
-        s->queue.push_front(std::move(q));  // wait for running sequences to free KV pages / slots
-        break;
-      }
-      if (rc == DIS_ERR_MODEL_NOT_LOADED || rc == DIS_ERR_SHUTDOWN) { s->queue.push_front(std::move(q)); s->last_error = dis_engine_last_error(s->eng); return rc; }
-      if (rc != DIS_OK) {  // a bad request fails alone (Property 22, design.md:812-816)
-        emit(s, q.id, DIS_EVENT_DONE, 0, 0, DIS_FINISH_FAILED, (int32_t)q.prompt.size(), (now_s - q.enqueued_at) * 1e3);
-        continue;
-      }
-      budget -= (int)q.prompt.size();
-      fresh.push_back(Active{q.id, slot, 0, (int32_t)q.prompt.size(), q.enqueued_at});
+  // 2. admission: free slots, High -> Normal -> Low; a request is admitted when the engine can reserve its KV pages
+  Queued q;
+  while ((int32_t)s->active.size() < s->max_active && s->queue.pop(&q)) {
+    dis_sampling_params p = q.params;
+    p.stop_tokens = q.stop_tokens.empty() ? nullptr : q.stop_tokens.data();
+    p.stop_lens = q.stop_lens.empty() ? nullptr : q.stop_lens.data();
+    p.n_stop = (int32_t)q.stop_lens.size();
+    int32_t slot = -1;
+    const int rc = dis_engine_seq_add(s->eng, q.prompt.data(), (int32_t)q.prompt.size(), &p, &slot);
+    if (rc == DIS_ERR_OUT_OF_MEMORY && !s->active.empty()) {
+      s->queue.push_front(std::move(q));  // wait for running sequences to free KV pages / slots
+      break;
     }
+    if (rc == DIS_ERR_MODEL_NOT_LOADED || rc == DIS_ERR_SHUTDOWN) { s->queue.push_front(std::move(q)); s->last_error = dis_engine_last_error(s->eng); return rc; }
+    if (rc != DIS_OK) {  // a bad request fails alone (Property 22, design.md:812-816)
+      emit(s, q.id, DIS_EVENT_DONE, 0, 0, DIS_FINISH_FAILED, (int32_t)q.prompt.size(), (now_s - q.enqueued_at) * 1e3);
+      continue;
+    }
+    s->active.push_back(Active{q.id, slot, 0, (int32_t)q.prompt.size(), q.enqueued_at});
   }
-  auto retire = [&](std::vector<Active> &set, const std::vector<uint32_t> &toks, const std::vector<int32_t> &fin) {
+  if (s->active.empty()) return drain(s, events, cap, n_events);
+  // 3. ONE forward pass for everybody: each running sequence decodes a token and, in the same pass, the prompts still
+  // being read advance by up to prefill_budget tokens in admission order (chunked prefill).  Running sequences are
+  // never stalled behind a long prompt, and a prompt is never starved by the running ones.
+  std::vector<int32_t> slots, fin(s->active.size()), produced(s->active.size());
+  std::vector<uint32_t> toks(s->active.size());
+  for (auto &a : s->active) slots.push_back(a.slot);
+  const int rc = dis_engine_step(s->eng, (int32_t)slots.size(), slots.data(), s->prefill_budget, toks.data(), fin.data(), produced.data());
+  if (rc != DIS_OK) {
+    // the pass failed as a whole: sequences that have not produced anything yet get their DONE/FAILED event, so no
+    // request id vanishes; the others stay (the caller sees the error and decides)
+    s->last_error = dis_engine_last_error(s->eng);
     std::vector<Active> keep;
-    for (size_t i = 0; i < set.size(); i++) {
-      Active a = set[i];
-      if (fin[i] == DIS_FINISH_FAILED) {  // produced no token
-        emit(s, a.id, DIS_EVENT_DONE, 0, a.produced, DIS_FINISH_FAILED, a.prompt_tokens, 0.0);
-        dis_engine_seq_remove(s->eng, a.slot);
-        continue;
-      }
-      float lp = 0.f;
-      dis_engine_last_logprobs(s->eng, 1, &a.slot, &lp);
-      // under the injected clock of the *_at variants the step's own duration is not visible: TTFT = time queued
-      const double t_first = clock_injected ? now_s : steady_now();
-      emit(s, a.id, DIS_EVENT_TOKEN, toks[i], a.produced, fin[i], a.prompt_tokens, a.produced == 0 ? (t_first - a.enqueued_at) * 1e3 : 0.0, lp);
-      a.produced++;
-      if (fin[i] != DIS_FINISH_NONE) {
-        emit(s, a.id, DIS_EVENT_DONE, 0, a.produced, fin[i], a.prompt_tokens, 0.0);
-        dis_engine_seq_remove(s->eng, a.slot);
-      } else keep.push_back(a);
+    for (auto &a : s->active) {
+      if (a.produced > 0) { keep.push_back(a); continue; }
+      dis_engine_seq_remove(s->eng, a.slot);
+      emit(s, a.id, DIS_EVENT_DONE, 0, 0, DIS_FINISH_FAILED, a.prompt_tokens, (now_s - a.enqueued_at) * 1e3);
     }
-    set.swap(keep);
-  };
-  if (!fresh.empty()) {
-    // 3. prefill the newcomers: their first token
-    std::vector<int32_t> slots, fin(fresh.size());
-    std::vector<uint32_t> toks(fresh.size());
-    for (auto &a : fresh) slots.push_back(a.slot);
-    const int rc = dis_engine_prefill(s->eng, (int32_t)slots.size(), slots.data(), toks.data(), fin.data());
-    if (rc != DIS_OK) {
-      // the step failed as a whole: every newcomer gets its DONE/FAILED event, so no request id vanishes
-      s->last_error = dis_engine_last_error(s->eng);
-      for (auto &a : fresh) {
-        dis_engine_seq_remove(s->eng, a.slot);
-        emit(s, a.id, DIS_EVENT_DONE, 0, 0, DIS_FINISH_FAILED, a.prompt_tokens, (now_s - a.enqueued_at) * 1e3);
-      }
-      return rc;
-    }
-    retire(fresh, toks, fin);
-    s->active.insert(s->active.end(), fresh.begin(), fresh.end());
-    s->decode_next = true;
-  } else if (!s->active.empty()) {
-    // 4. one decode step for everybody
-    std::vector<int32_t> slots, fin(s->active.size());
-    std::vector<uint32_t> toks(s->active.size());
-    for (auto &a : s->active) slots.push_back(a.slot);
-    const int rc = dis_engine_decode(s->eng, (int32_t)slots.size(), slots.data(), toks.data(), fin.data());
-    if (rc != DIS_OK) { s->last_error = dis_engine_last_error(s->eng); return rc; }
-    retire(s->active, toks, fin);
-    s->decode_next = false;
+    s->active.swap(keep);
+    return rc;
   }
+  std::vector<Active> keep;
+  for (size_t i = 0; i < s->active.size(); i++) {
+    Active a = s->active[i];
+    if (fin[i] == DIS_FINISH_FAILED && !produced[i]) {  // produced no token in this pass
+      emit(s, a.id, DIS_EVENT_DONE, 0, a.produced, DIS_FINISH_FAILED, a.prompt_tokens, 0.0);
+      dis_engine_seq_remove(s->eng, a.slot);
+      continue;
+    }
+    if (!produced[i]) { keep.push_back(a); continue; }  // its prompt is still being read
+    float lp = 0.f;
+    dis_engine_last_logprobs(s->eng, 1, &a.slot, &lp);
+    // under the injected clock of the *_at variants the step's own duration is not visible: TTFT = time queued
+    const double t_first = clock_injected ? now_s : steady_now();
+    emit(s, a.id, DIS_EVENT_TOKEN, toks[i], a.produced, fin[i], a.prompt_tokens, a.produced == 0 ? (t_first - a.enqueued_at) * 1e3 : 0.0, lp);
+    a.produced++;
+    if (fin[i] != DIS_FINISH_NONE) {
+      emit(s, a.id, DIS_EVENT_DONE, 0, a.produced, fin[i], a.prompt_tokens, 0.0);
+      dis_engine_seq_remove(s->eng, a.slot);
+    } else keep.push_back(a);
+  }
+  s->active.swap(keep);
   return drain(s, events, cap, n_events);
 }
 

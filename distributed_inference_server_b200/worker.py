@@ -241,6 +241,16 @@ class Engine:
     def decode(self, slots):
         return self._step(self.lib.dis_engine_decode, slots)
 
+    def step(self, slots, max_prefill_tokens: int = 0):
+        """One mixed pass (dis_engine_step): (tokens, finish, produced) per listed sequence."""
+        s = np.ascontiguousarray(slots, dtype=np.int32)
+        toks = np.zeros(len(s), np.uint32)
+        fin = np.zeros(len(s), np.int32)
+        prod = np.zeros(len(s), np.int32)
+        self._check(self.lib.dis_engine_step(self.h, len(s), s.ctypes.data, int(max_prefill_tokens), toks.ctypes.data,
+                                             fin.ctypes.data, prod.ctypes.data))
+        return toks, fin, prod
+
     def profile_decode(self, slots):
         """One eager decode step timed per kernel class: (tokens, finish, {class: (ms, launches)})."""
         s = np.ascontiguousarray(slots, dtype=np.int32)
@@ -460,6 +470,10 @@ class ContinuousBatcher:
             raise QueueFull()
         if rc != B.OK:
             raise WorkerError(_KIND.get(rc, WorkerError.InferenceFailed), "submit")
+
+    def set_prefill_budget(self, tokens: int) -> None:
+        if self.lib.dis_serving_set_prefill_budget(self.h, int(tokens)) != B.OK:
+            raise ValueError("prefill budget must be >= 1")
 
     def cancel(self, request_id) -> bool:
         """Client disconnect (requirements.md:85); False if the request is neither queued nor running."""

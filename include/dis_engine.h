@@ -153,6 +153,15 @@ DIS_API int dis_engine_prefill(dis_engine *e, int32_t n, const int32_t *slots, u
 /* One decode step: each listed sequence consumes its last sampled token and yields the next. */
 DIS_API int dis_engine_decode(dis_engine *e, int32_t n, const int32_t *slots, uint32_t *out_tokens,
                               int32_t *out_finish);
+/* One forward pass shared by running sequences and prompts that are still being read (chunked prefill; SURVEY.md §8
+ * row f1; the reference's batcher is a 50 ms window batcher in its spec only, design.md:227-267).  A listed sequence
+ * that has been prefilled decodes one token exactly as in dis_engine_decode; one that has not advances through its
+ * prompt by a chunk -- all unfinished prompts together get at most max_prefill_tokens tokens (0 = the engine's
+ * max_step_tokens), handed out in list order -- and samples its first token in the pass that reaches the prompt's
+ * end.  out_produced[i] = 1 where out_tokens[i] / out_finish[i] carry a new token.  dis_engine_prefill and
+ * dis_engine_decode remain the one-kind-per-call entry points; the three can be mixed on one engine. */
+DIS_API int dis_engine_step(dis_engine *e, int32_t n, const int32_t *slots, int32_t max_prefill_tokens,
+                            uint32_t *out_tokens, int32_t *out_finish, int32_t *out_produced);
 /* dis_engine_decode run eagerly with a CUDA event before every kernel class (no reference counterpart;
  * it is how bench.py times the dominant kernel on the stream it runs on).  class_ms / class_launches
  * have DIS_PROF_COUNT entries: device milliseconds and launches per class for this one step. */
@@ -215,7 +224,8 @@ DIS_API int dis_worker_infer(dis_engine *e, int32_t n, const uint32_t *input_ids
  * is on, back-pressure switched on above high_watermark and off below low_watermark, requests older than
  * request_timeout_s expired; defaults (cfg == NULL) are queue.rs:24-33.  The batcher replaces the spec's
  * 50 ms window batcher (design.md:227-267): every dis_serving_step admits queued requests into free engine
- * slots (KV pages permitting) and prefills them, or runs one decode step for all running sequences, and
+ * slots (KV pages permitting) and runs one forward pass in which the running sequences decode a token and the admitted
+ * prompts advance by a bounded chunk (dis_engine_step), and
  * reports one event per generated token (TokenEvent, models.rs:268-288).  engine == NULL gives a queue-only
  * object (admission logic without a GPU).  The *_at variants take the clock as an argument. */
 typedef enum dis_priority { DIS_PRIORITY_LOW = 0, DIS_PRIORITY_NORMAL = 1, DIS_PRIORITY_HIGH = 2 } dis_priority;
@@ -249,6 +259,13 @@ DIS_API int dis_serving_cancel(dis_serving *s, const uint8_t request_id[16]);
 DIS_API int dis_serving_step(dis_serving *s, dis_serving_event *events, int32_t cap, int32_t *n_events);
 DIS_API int dis_serving_step_at(dis_serving *s, double now_s, dis_serving_event *events, int32_t cap, int32_t *n_events);
 DIS_API int dis_serving_depth(dis_serving *s, dis_queue_depth *out);
+/* Prompt tokens read per scheduler step beside the running sequences' decode rows (default 2048): the knob between
+ * time-to-first-token of waiting requests and inter-token latency of running ones. */
+DIS_API int dis_serving_set_prefill_budget(dis_serving *s, int32_t tokens);
+/* The rule dis_engine_step uses to share a pass, as a pure function (no engine, no GPU) so that it can be property-
+ * tested: remaining_prompt[i] <= 0 marks a decode row (take[i] = 1); the other entries receive, in list order, as
+ * much of their remaining prompt as still fits into min(budget, cap - decode rows) tokens. */
+DIS_API int dis_serving_plan_step(int32_t n, const int32_t *remaining_prompt, int32_t budget, int32_t cap, int32_t *take);
 DIS_API int dis_serving_debug_pop(dis_serving *s, int32_t max, uint8_t *ids /* [max][16] */, int32_t *n);
 
 /* ---- prefix KV reuse -------------------------------------------------------- *

@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """Turn gpurun_out/ ncu artefacts into small, tracked summaries under profiles/.
 
-    python scripts/summarize_profile.py <tag> <round-prefix>
+    python scripts/summarize_profile.py <tag> <round-prefix> [index of the sample_kernel launch that ends the decode step]
 
 reads gpurun_out/launches_<tag>.csv (ncu --metrics gpu__time_duration.sum launch list) and
 gpurun_out/prof_<tag>.ncu-rep (ncu --set full of the dominant kernel), writes
@@ -30,7 +30,9 @@ with open(os.path.join(out, f"{pref}_launches.csv"), "w", newline="") as f:
 # the last decode step = everything after the last-but-one sample_kernel
 names = [r[ix["Kernel Name"]] for r in data]
 samples = [i for i, n in enumerate(names) if n.startswith("sample_kernel")]
-step = data[samples[-2] + 1: samples[-1] + 1] if len(samples) >= 2 else data
+# which sample_kernel ends the decode step to summarise (bench.py's order: batch prefill, W+K decode steps, then TTFT runs)
+k = int(sys.argv[3]) if len(sys.argv) > 3 else len(samples) - 1
+step = data[samples[k - 1] + 1: samples[k] + 1] if len(samples) >= 2 else data
 tot = sum(float(r[ix["Metric Value"]]) for r in step)
 agg = collections.OrderedDict()
 for r in step:

@@ -104,3 +104,30 @@ def test_request_ids_are_16_byte_uuids_and_cancel_removes_a_queued_request():
     ev = q.step(now=0.0)
     assert [(e[0], e[1], e[4], e[5]) for e in ev] == [(ids[1], B.EVENT_DONE, B.FINISH_STOP, 3)]
     assert q.debug_pop(5) == [ids[0], ids[2]]
+
+
+@settings(max_examples=200, deadline=None)
+@given(st.lists(st.integers(-3, 9000), min_size=0, max_size=80), st.integers(1, 9000), st.integers(1, 9000))
+def test_mixed_step_plan_is_fair_and_bounded(remaining, budget, cap):
+    """dis_serving_plan_step, the rule by which dis_engine_step shares one forward pass (chunked prefill): every running
+    sequence gets its one token whatever the prompts need; prompt tokens never exceed the budget nor the room the pass
+    has left; they are handed out in list (= admission) order, so a later prompt reads nothing unless every earlier one
+    was served in full; and no room is wasted while a prompt still wants tokens."""
+    import ctypes as C
+    import numpy as np
+    lib = B.load()
+    n = len(remaining)
+    rem = np.array(remaining, np.int32)
+    take = np.full(n, -7, np.int32)
+    assert lib.dis_serving_plan_step(n, rem.ctypes.data, budget, cap, take.ctypes.data) == B.OK
+    dec = rem <= 0
+    assert (take[dec] == 1).all()
+    pre = take[~dec]
+    assert (pre >= 0).all() and (pre <= rem[~dec]).all()
+    room = max(0, min(budget, cap - int(dec.sum())))
+    assert int(pre.sum()) <= room
+    want = rem[~dec]
+    short = np.nonzero(pre < want)[0]
+    if len(short):
+        assert (pre[short[0] + 1:] == 0).all()          # nobody behind a partly served prompt reads anything
+        assert int(pre.sum()) == room                   # and the room was used up
