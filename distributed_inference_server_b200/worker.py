@@ -441,6 +441,9 @@ class ContinuousBatcher:
             b = bytes(request_id)
             if len(b) != 16:
                 raise ValueError("request id must be 16 bytes")
+        elif isinstance(request_id, str):
+            import hashlib
+            b = hashlib.blake2b(request_id.encode(), digest_size=16).digest()
         else:
             b = int(request_id).to_bytes(16, "little")
         self._ids.setdefault(b, request_id)
