@@ -615,24 +615,46 @@ def run_serving(args):
     eng.load_synthetic(0); eng.finalize()
     cb = ContinuousBatcher(eng, max_active=n_req, high_watermark=4 * n_req, low_watermark=2 * n_req, max_queue_size=8 * n_req,
                            request_timeout_s=3600.0)
+    if args.prefill_budget:
+        cb.set_prefill_budget(args.prefill_budget)
     torch.cuda.synchronize()
     t0 = time.perf_counter()
     for i, p in enumerate(prompts):
         cb.submit(i, p, InferenceParams(new, 0.0))
-    res = cb.run_until_idle()
+    # drive the scheduler; every token event is stamped with the host clock of the step that produced it
+    tok_t = {i: [] for i in range(n_req)}
+    finish = {}
+    n_steps = 0
+    while True:
+        evs = cb.step()
+        now = time.perf_counter()
+        n_steps += 1
+        for rid, kind, tok, idx, fin, ptoks, waited in evs:
+            if kind == B.EVENT_TOKEN:
+                tok_t[rid].append(now)
+            elif kind == B.EVENT_DONE:
+                finish[rid] = fin
+        d = cb.depth()
+        if d.total == 0 and d.active == 0 and not evs:
+            break
     torch.cuda.synchronize()
     wall = time.perf_counter() - t0
-    gen = sum(len(r["tokens"]) for r in res.values())
-    ttft = sorted(r["ttft_ms"] for r in res.values() if r["ttft_ms"] is not None)
+    gen = sum(len(v) for v in tok_t.values())
+    ttft = sorted((v[0] - t0) * 1e3 for v in tok_t.values() if v)
+    itl = sorted((b - a) * 1e3 for v in tok_t.values() for a, b in zip(v, v[1:]))
     st = eng.status()
+    pct = lambda xs, q: xs[min(len(xs) - 1, int(q * len(xs)))] if xs else None
     line = {"metric": "aggregate decode tokens/s, continuous batching", "value": gen / wall, "unit": "tokens/s", "n_gpus": 1,
             "higher_is_better": True, "dtype": "bf16", "data": "synthetic",
-            "config": {"workload": f"BASELINE configs[4]: Llama-3-8B bf16, continuous batching, {n_req} concurrent requests, "
+            "config": {"workload": f"BASELINE configs[4]: Llama-3-8B bf16, continuous batching, {n_req} concurrent requests (all submitted at t = 0), "
                                    f"prompt lengths log-uniform in [128, 8192] (mean {int(lens.mean())}), {new} new tokens each"
-                                   + (f" [REDUCED DEPTH {args.layers} layers]" if args.layers else "")},
-            "requests": n_req, "completed": sum(1 for r in res.values() if r["finish"] == B.FINISH_LENGTH),
-            "generated_tokens": gen, "prompt_tokens": int(lens.sum()), "wall_s": wall,
-            "ttft_ms_p50": ttft[len(ttft) // 2] if ttft else None, "ttft_ms_max": ttft[-1] if ttft else None,
+                                   + (f" [REDUCED DEPTH {args.layers} layers]" if args.layers else ""),
+                       "scheduler": "one forward pass per step: every running sequence decodes a token, admitted prompts advance by at most "
+                                    f"prefill_budget = {args.prefill_budget or 'library default (4096)'} tokens in admission order (dis_engine_step)"},
+            "requests": n_req, "completed": sum(1 for f in finish.values() if f == B.FINISH_LENGTH),
+            "generated_tokens": gen, "prompt_tokens": int(lens.sum()), "wall_s": wall, "scheduler_steps": n_steps,
+            "ttft_ms_p50": pct(ttft, 0.5), "ttft_ms_max": ttft[-1] if ttft else None,
+            "inter_token_ms_p50": pct(itl, 0.5), "inter_token_ms_p99": pct(itl, 0.99), "inter_token_ms_max": itl[-1] if itl else None,
             "total_tokens_per_s_incl_prompt": (gen + int(lens.sum())) / wall, "kv_pages": st.kv_pages_total,
             "gpu_launches": int(st.kernel_launches)}
     print(json.dumps(line))
@@ -712,6 +734,7 @@ def main():
     ap.add_argument("--workload", default="decode", choices=["decode", "serving", "prefix"], help="serving = BASELINE configs[4]; prefix = TTFT with prefix KV reuse (row f2)")
     ap.add_argument("--model", default="8b", choices=["8b", "70b"], help="70b = BASELINE configs[3] (TP=8, batch 32)")
     ap.add_argument("--requests", type=int, default=256)
+    ap.add_argument("--prefill-budget", type=int, default=0, help="serving: prompt tokens read per scheduler step (0 = library default)")
     ap.add_argument("--shard-of", type=int, default=1, help="diagnostic: run one rank's shard of a TP=N model on one GPU, no exchange")
     ap.add_argument("--new-tokens", type=int, default=128)
     ap.add_argument("--settle-steps", type=int, default=48,

@@ -118,7 +118,7 @@ struct dis_serving {
   std::deque<dis_serving_event> pending;
   std::mutex mu;
   int32_t max_active = 0;
-  int32_t prefill_budget = 2048;  // prompt tokens read per scheduler step (beside one token for every running sequence)
+  int32_t prefill_budget = 4096;  // prompt tokens read per scheduler step (beside one token for every running sequence)
   std::string last_error;
   explicit dis_serving(const dis_queue_config &c) : cfg(c), queue(c) {}
 };

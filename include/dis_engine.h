@@ -259,7 +259,7 @@ DIS_API int dis_serving_cancel(dis_serving *s, const uint8_t request_id[16]);
 DIS_API int dis_serving_step(dis_serving *s, dis_serving_event *events, int32_t cap, int32_t *n_events);
 DIS_API int dis_serving_step_at(dis_serving *s, double now_s, dis_serving_event *events, int32_t cap, int32_t *n_events);
 DIS_API int dis_serving_depth(dis_serving *s, dis_queue_depth *out);
-/* Prompt tokens read per scheduler step beside the running sequences' decode rows (default 2048): the knob between
+/* Prompt tokens read per scheduler step beside the running sequences' decode rows (default 4096): the knob between
  * time-to-first-token of waiting requests and inter-token latency of running ones. */
 DIS_API int dis_serving_set_prefill_budget(dis_serving *s, int32_t tokens);
 /* The rule dis_engine_step uses to share a pass, as a pure function (no engine, no GPU) so that it can be property-
