@@ -228,8 +228,12 @@ int dis_k_attn_prefill(const uint16_t *q, const uint16_t *kv_pool, int64_t n_pag
   dis::TmaMap map;
   cudaError_t e = dis::make_kv_map(&map, kv_pool, (long long)n_pages * 2 * n_kv * page_size, d, page_size);
   if (e != cudaSuccess) return k_ret(e);
-  return k_ret(dis::launch_attn_prefill(map, 0, q, page_table, max_pages, qb_tok0, qb_len, qb_pos0, qb_ptrow, out, n_blocks,
-                                        n_heads, n_kv, d, page_size, (cudaStream_t)stream));
+  auto fn = dis::attn_prefill_uses_tc(n_heads, n_kv, d) ? dis::launch_attn_prefill_tc : dis::launch_attn_prefill;
+  return k_ret(fn(map, 0, q, page_table, max_pages, qb_tok0, qb_len, qb_pos0, qb_ptrow, out, n_blocks, n_heads, n_kv, d, page_size,
+                  (cudaStream_t)stream));
+}
+int dis_k_attn_prefill_block_tokens(int32_t n_heads, int32_t n_kv, int32_t d) {
+  return dis::attn_prefill_block_tokens(n_heads, n_kv, d);
 }
 int dis_k_sample(const float *logits, int64_t ld, int32_t T, int32_t V, const float *temperature, const float *top_p,
                  const uint64_t *seeds, const uint64_t *steps, uint32_t *out_tokens, float *out_logprob, void *stream) {

@@ -213,6 +213,8 @@ int Engine::init(const dis_engine_config *c) {
   seqs.resize((size_t)max_batch);
   slot_stamp.assign((size_t)max_batch, 0);
   use_pdl = !(c->flags & DIS_FLAG_NO_PDL);
+  pf_block = attn_prefill_block_tokens(nh_l, nkv_l, m.head_dim);
+  pf_tc = attn_prefill_uses_tc(nh_l, nkv_l, m.head_dim);
   if (const char *g = getenv("DIS_GEMM_PERSIST")) use_persist = atoi(g) != 0;
   if (const char *g = getenv("DIS_GEMV_MAX_T")) gemv_max_t = std::max(0, std::min(kGemvMaxT, atoi(g)));
   // Measurement aid, never set in production: DIS_DEBUG_SKIP=norm,attn,... leaves those kernel classes out of the
@@ -659,7 +661,7 @@ cudaError_t Engine::enqueue_layers(int T, int n_splits) {
       RET_CUDA(launch_rope_kv_write(partial, s_qkv, (long long)T * nqkv_l, q, pool, d_page_table, max_pages, ptrow, pos,
                                     rope_cos, rope_sin, T, nh_l, nkv_l, d, page_size, stream));
       prof_mark(P_ATTN);
-      RET_CUDA(launch_attn_prefill(kv_map, (long long)l * kv_rows_per_layer, q, d_page_table, max_pages,
+      RET_CUDA((pf_tc ? launch_attn_prefill_tc : launch_attn_prefill)(kv_map, (long long)l * kv_rows_per_layer, q, d_page_table, max_pages,
                                    cur_meta->d<int>(cur_meta->o_qb_tok0), cur_meta->d<int>(cur_meta->o_qb_len),
                                    cur_meta->d<int>(cur_meta->o_qb_pos0), cur_meta->d<int>(cur_meta->o_qb_ptrow), attn,
                                    n_qblocks, nh_l, nkv_l, d, page_size, stream));
@@ -802,9 +804,9 @@ int Engine::prefill(int n, const int *slots, uint32_t *out_tokens, int *out_fini
         cur_meta->h<int>(cur_meta->o_ctx)[T + k] = sp + k + 1;
       }
       // query blocks of up to 16 consecutive tokens for the prefill attention kernel
-      for (int k = 0; k < take; k += 16) {
+      for (int k = 0; k < take; k += pf_block) {
         cur_meta->h<int>(cur_meta->o_qb_tok0)[QB] = T + k;
-        cur_meta->h<int>(cur_meta->o_qb_len)[QB] = std::min(16, take - k);
+        cur_meta->h<int>(cur_meta->o_qb_len)[QB] = std::min(pf_block, take - k);
         cur_meta->h<int>(cur_meta->o_qb_pos0)[QB] = sp + k;
         cur_meta->h<int>(cur_meta->o_qb_ptrow)[QB] = slots[si];
         QB++;
@@ -929,9 +931,9 @@ int Engine::step_mixed(int n, const int *slots, int max_prefill_tokens, uint32_t
       cur_meta->h<int>(cur_meta->o_ptrow)[T + j] = slots[i];
       cur_meta->h<int>(cur_meta->o_ctx)[T + j] = p0 + j + 1;
     }
-    for (int j = 0; j < tk; j += 16) {
+    for (int j = 0; j < tk; j += pf_block) {
       cur_meta->h<int>(cur_meta->o_qb_tok0)[QB] = T + j;
-      cur_meta->h<int>(cur_meta->o_qb_len)[QB] = std::min(16, tk - j);
+      cur_meta->h<int>(cur_meta->o_qb_len)[QB] = std::min(pf_block, tk - j);
       cur_meta->h<int>(cur_meta->o_qb_pos0)[QB] = p0 + j;
       cur_meta->h<int>(cur_meta->o_qb_ptrow)[QB] = slots[i];
       QB++;

@@ -109,6 +109,8 @@ struct Engine {
   StepMeta meta_dec, meta_pre;      // decode steps / prefill chunks
   StepMeta *cur_meta = &meta_dec;
   int n_qblocks = 0;                // > 0 while a prefill chunk is being enqueued
+  int pf_block = 16;                // tokens per prefill query block (attn_prefill_block_tokens)
+  bool pf_tc = false;               // prefill attention on the tcgen05 kernel (head_dim 128, GQA group 4 or 8)
   std::vector<Sequence> seqs;
   std::vector<uint64_t> slot_stamp;  // duplicate-slot detection in O(n): stamp of the last call that listed the slot
   uint64_t call_stamp = 0;

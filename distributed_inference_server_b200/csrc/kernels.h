@@ -76,6 +76,15 @@ cudaError_t launch_attn_prefill(const TmaMap &kv_map, long long row0, const uint
                                 const int *qb_ptrow, uint16_t *out, int n_blocks, int n_heads, int n_kv, int d,
                                 int page_size, cudaStream_t st);
 
+// k_attn_prefill_tc.cu : the same contract on tcgen05 / TMEM for head_dim 128 and GQA groups of 4 or 8; query blocks
+// hold up to attn_prefill_block_tokens() tokens (128 / G there, 16 on the mma.sync kernel)
+bool attn_prefill_uses_tc(int n_heads, int n_kv, int d);
+int attn_prefill_block_tokens(int n_heads, int n_kv, int d);
+cudaError_t launch_attn_prefill_tc(const TmaMap &kv_map, long long row0, const uint16_t *q, const int *page_table,
+                                   int max_pages, const int *qb_tok0, const int *qb_len, const int *qb_pos0,
+                                   const int *qb_ptrow, uint16_t *out, int n_blocks, int n_heads, int n_kv, int d,
+                                   int page_size, cudaStream_t st);
+
 // k_gemm_tcgen05.cu
 cudaError_t make_tma_map_2d(TmaMap *out, const void *base, uint64_t rows, uint64_t cols, uint32_t box_rows);
 int gemm_token_tile(int T);  // 32 / 64 / 128: the UMMA N used for T tokens

@@ -362,9 +362,13 @@ DIS_API int dis_k_attn_paged_static(const uint16_t *q, const uint16_t *kv_pool, 
                                     const int32_t *page_table, int32_t max_pages, const int32_t *pt_row,
                                     const int32_t *ctx, uint16_t *out, int32_t n_splits, int32_t T, int32_t n_heads,
                                     int32_t n_kv, int32_t d, int32_t page_size, void *stream);
-/* Prefill attention: query block b is the qb_len[b] (<= 16) consecutive tokens [qb_tok0[b], ..) of the flattened
+/* Prefill attention: query block b is the qb_len[b] consecutive tokens [qb_tok0[b], ..) of the flattened
  * batch, at positions qb_pos0[b].. of the sequence with page-table row qb_ptrow[b]; causal over keys [0, pos].
- * The block's own K/V must already be in the pages.  q / out are [tokens][nh*d] bf16. */
+ * The block's own K/V must already be in the pages.  q / out are [tokens][nh*d] bf16.
+ * qb_len[b] <= dis_k_attn_prefill_block_tokens(n_heads, n_kv, d): 128 / (n_heads / n_kv) where the tcgen05 / TMEM
+ * kernel applies (head_dim 128, 4 or 8 query heads per kv head: S = Q K^T and P V as tcgen05.mma over 128 query rows,
+ * k_attn_prefill_tc.cu), 16 on the mma.sync kernel that serves every other geometry. */
+DIS_API int dis_k_attn_prefill_block_tokens(int32_t n_heads, int32_t n_kv, int32_t d);
 DIS_API int dis_k_attn_prefill(const uint16_t *q, const uint16_t *kv_pool, int64_t n_pages, const int32_t *page_table,
                                int32_t max_pages, const int32_t *qb_tok0, const int32_t *qb_len,
                                const int32_t *qb_pos0, const int32_t *qb_ptrow, uint16_t *out, int32_t n_blocks,

@@ -1,11 +1,11 @@
 #!/bin/bash
-# Round-2 tensor-parallel session: usage scripts/gpu_r2_tp.sh N  (run under gpurun --gpus N)
+# Round-2 tensor-parallel session: usage scripts/gpu_r2_tp.sh N [notest]  (run under gpurun --gpus N)
 set -u
 N=${1:-2}
 mkdir -p gpurun_out
 O=gpurun_out
 nvidia-smi topo -m > $O/r2tp${N}_topo.txt 2>&1
-timeout 900 python -m pytest tests/test_tp_gpu.py -m gpu -q -x -k "tp$N or (not tp2 and not tp4 and not tp8)" --durations=5 > $O/r2tp${N}_pytest.log 2>&1; echo "pytest rc=$?"
+[ "${2:-}" = notest ] || timeout 900 python -m pytest tests/test_tp_gpu.py -m gpu -q -x -k "tp$N or (not tp2 and not tp4 and not tp8)" --durations=5 > $O/r2tp${N}_pytest.log 2>&1; echo "pytest rc=$?"
 tail -8 $O/r2tp${N}_pytest.log
 run() { # tag, extra args
   tag=$1; shift

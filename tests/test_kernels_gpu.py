@@ -292,9 +292,18 @@ def test_attention_long_context_tiles():
         assert np.abs(host(out)[0] - ref).max() <= 2 * BF16_ULP * np.abs(ref).max() + 1e-5
 
 
-@pytest.mark.parametrize("d,nh,nkv,page_size", [(128, 8, 2, 64), (64, 8, 2, 16), (128, 8, 1, 32), (64, 2, 2, 64)])
-def test_attention_prefill_blocks(d, nh, nkv, page_size):
-    """Causal attention of 16-token query blocks over the paged cache vs the oracle, ragged sequences."""
+@pytest.mark.parametrize("d,nh,nkv,page_size", [(128, 8, 2, 64), (64, 8, 2, 16), (128, 8, 1, 32), (64, 2, 2, 64), (128, 4, 1, 16),
+                                                 (128, 16, 2, 32)])
+@pytest.mark.parametrize("short_blocks", [False, True], ids=["full-blocks", "short-blocks"])
+def test_attention_prefill_blocks(d, nh, nkv, page_size, short_blocks):
+    """Causal attention of query blocks over the paged cache vs the oracle, ragged sequences.  Blocks hold up to
+    dis_k_attn_prefill_block_tokens tokens: 32 / 16 on the tcgen05 kernel (head_dim 128 with 4 / 8 query heads per kv
+    head), 16 on the mma.sync kernel; short-blocks cuts them at 5 tokens (mostly padding rows, as the decode rows of a
+    mixed step are)."""
+    BT = lib().dis_k_attn_prefill_block_tokens(nh, nkv, d)
+    assert BT == (128 // (nh // nkv) if d == 128 and nh // nkv in (4, 8) else 16)
+    if short_blocks:
+        BT = 5
     rng = np.random.default_rng(d + nh + nkv + page_size)
     seq_lens = [1, 15, 16, 17, 70, 200]
     n_pages = 32
@@ -312,8 +321,8 @@ def test_attention_prefill_blocks(d, nh, nkv, page_size):
     q_flat, tok0, qlen, pos0, ptrow, ref = [], [], [], [], [], []
     t = 0
     for s, n in enumerate(seq_lens):
-        for p0 in range(starts[s], n, 16):
-            ln = min(16, n - p0)
+        for p0 in range(starts[s], n, BT):
+            ln = min(BT, n - p0)
             tok0.append(t); qlen.append(ln); pos0.append(p0); ptrow.append(s)
             for i in range(ln):
                 q_flat.append(Q[s][p0 + i])
@@ -344,9 +353,11 @@ def test_attention_prefill_full_size_against_torch():
     pt[0, :pages_per[0]] = perm[:pages_per[0]]; pt[1, :pages_per[1]] = perm[pages_per[0]:pages_per[0] + pages_per[1]]
     pool = torch.randn((n_pages, 2, nkv, ps, d), device=DEV, generator=g).to(torch.bfloat16)
     tok0, qlen, pos0, ptrow, t = [], [], [], [], 0
+    BT = lib().dis_k_attn_prefill_block_tokens(nh, nkv, d)      # 32: the tcgen05 kernel's 128 query rows = 32 tokens x 4 heads
+    assert BT == 32
     for s in range(2):
-        for p0 in range(starts[s], lens[s], 16):
-            ln = min(16, lens[s] - p0)
+        for p0 in range(starts[s], lens[s], BT):
+            ln = min(BT, lens[s] - p0)
             tok0.append(t); qlen.append(ln); pos0.append(p0); ptrow.append(s); t += ln
     q = torch.randn((t, nh * d), device=DEV, generator=g).to(torch.bfloat16)
     out = torch.empty((t, nh * d), dtype=torch.bfloat16, device=DEV)
