@@ -910,7 +910,19 @@ int Engine::step_mixed(int n, const int *slots, int max_prefill_tokens, uint32_t
   }
   if (idx.empty()) { last_rows = 0; return DIS_OK; }
   std::vector<int> rem_live, take_live(idx.size());
-  for (int i : idx) { const Sequence &s = seqs[(size_t)slots[i]]; rem_live.push_back(s.prefilled ? 0 : (int)s.prompt.size() - s.prefill_pos); }
+  bool any_prompt = false;
+  for (int i : idx) {
+    const Sequence &s = seqs[(size_t)slots[i]];
+    rem_live.push_back(s.prefilled ? 0 : (int)s.prompt.size() - s.prefill_pos);
+    any_prompt = any_prompt || !s.prefilled;
+  }
+  if (!any_prompt) {
+    // nothing but running sequences: this is a plain decode step -- the CUDA-graph path with the fused decode attention
+    const int rc = decode(n, slots, out_tokens, out_finish);
+    if (rc != DIS_OK) return rc;
+    for (int i = 0; i < n; i++) out_produced[i] = live[(size_t)i] && out_finish[i] != DIS_FINISH_FAILED ? 1 : 0;
+    return DIS_OK;
+  }
   plan_mixed_step((int)idx.size(), rem_live.data(), max_prefill_tokens > 0 ? max_prefill_tokens : cap_tokens, cap_tokens, take_live.data());
   ENG_CUDA(cudaEventRecord(ev0, stream));
   cur_meta = &meta_pre;
