@@ -56,6 +56,9 @@ extern "C" {
     pub fn dis_engine_seq_remove(e: *mut dis_engine, slot: i32) -> c_int;
     pub fn dis_engine_prefill(e: *mut dis_engine, n: i32, slots: *const i32, out_tokens: *mut u32, out_finish: *mut i32) -> c_int;
     pub fn dis_engine_decode(e: *mut dis_engine, n: i32, slots: *const i32, out_tokens: *mut u32, out_finish: *mut i32) -> c_int;
+    /// One forward pass for running sequences (a decode row each) and unfinished prompts (a bounded chunk, in list order).
+    pub fn dis_engine_step(e: *mut dis_engine, n: i32, slots: *const i32, max_prefill_tokens: i32, out_tokens: *mut u32,
+                           out_finish: *mut i32, out_produced: *mut i32) -> c_int;
     /// TokenEvent::Token.logprob (crates/core/src/models.rs:272-277) of each listed sequence's newest token.
     pub fn dis_engine_last_logprobs(e: *mut dis_engine, n: i32, slots: *const i32, out_logprobs: *mut f32) -> c_int;
     pub fn dis_engine_status(e: *mut dis_engine, out: *mut dis_worker_status) -> c_int;

@@ -133,6 +133,9 @@ fn run_batch(e: *mut sys::dis_engine, batch: InferenceBatch) -> Result<BatchResu
             else { sys::dis_engine_decode(e, run.len() as i32, slots.as_ptr(), toks.as_mut_ptr(), fin.as_mut_ptr()) }
         };
         if rc != sys::DIS_OK { return Err(err(rc, e)); }
+        // TokenEvent::Token.logprob (crates/core/src/models.rs:276): computed by the sampler kernel, copied back with the ids
+        let mut lps = vec![0f32; run.len()];
+        unsafe { sys::dis_engine_last_logprobs(e, run.len() as i32, slots.as_ptr(), lps.as_mut_ptr()) };
         for (j, &k) in run.iter().enumerate() {
             let l = &mut live[k];
             match finish(fin[j]) {
@@ -141,7 +144,7 @@ fn run_batch(e: *mut sys::dis_engine, batch: InferenceBatch) -> Result<BatchResu
             }
             // 2./3. one TokenEvent::Token per token; a closed stream means the client went away (requirements.md:85)
             if let Some(tx) = &batch.requests[l.index].stream_tx {
-                let ev = TokenEvent::Token { token: toks[j].to_string(), index: l.tokens.len() - 1, logprob: None };
+                let ev = TokenEvent::Token { token: toks[j].to_string(), index: l.tokens.len() - 1, logprob: Some(lps[j]) };
                 if tx.blocking_send(ev).is_err() { l.done = Some(FinishReason::Stop); }
             }
         }
