@@ -90,6 +90,10 @@ struct Engine {
   uint32_t *cand_tok = nullptr, *cand_tok_all = nullptr;
   float *cand_sum = nullptr, *cand_sum_all = nullptr;  // sum exp(z - max) over the rank's vocabulary slice (logprob)
   uint16_t *xn = nullptr, *q = nullptr, *attn = nullptr, *act = nullptr;
+  float *x_alt = nullptr;   // second residual buffer of the norm-fused batch-1 GEMV path (kGemvMaxT rows)
+  bool gemv_fuse_norm = true;  // DIS_GEMV_FUSE_NORM=0: separate norm kernels on the GEMV path (A/B runs)
+  bool gfuse = false;          // the step being enqueued runs the norm-fused GEMV path
+  float *gx_cur = nullptr, *gx_next = nullptr;  // its residual ping-pong
   size_t partial_elems = 0, attn_scratch_elems = 0;
   TmaMap xn_map[4], attn_map[4], act_map[4];  // box rows 32 / 64 / 128 / 256
   uint32_t *d_out_tokens = nullptr, *h_out_tokens = nullptr;

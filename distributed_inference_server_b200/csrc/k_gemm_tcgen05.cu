@@ -20,6 +20,8 @@
 // Algorithmic bytes per launch = 2*N*K (weights) + 2*T*K (activations) + 4*S*T*N (partials) or 2*T*I.
 #include <cuda.h>
 
+#include <cstdlib>
+
 #include "kernels.h"
 #include "ptx.cuh"
 
@@ -52,7 +54,7 @@ template <int BN, bool kDual>
 __global__ void __launch_bounds__(kGemmThreads)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_constant__ CUtensorMap x_map,
                     float *__restrict__ out_partial, uint16_t *__restrict__ out_act, int T, int N, int K,
-                    int w_row0, int up_row_off, int kb_per_split, int tile_rows, int n_stages) {
+                    int w_row0, int up_row_off, int kb_per_split, int tile_rows, int n_stages, int early_tma) {
   using Cfg = GemmCfg<BN, kDual>;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -78,6 +80,14 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_cons
   const int kb0 = blockIdx.z * kb_per_split;
   const int kb1 = min(num_kb, kb0 + kb_per_split);
 
+  const int pre = min(kb1 - kb0, n_stages);
+  auto issue_weights = [&]() {
+    for (int i = 0; i < pre; i++) {
+      mbar_expect_tx(full_bar(i), stage_tx);
+      tma_load_2d(a_tile(i), &w_map, (kb0 + i) * kBK, w_row0 + n0, full_bar(i), kEvictFirst);
+      if (kDual) tma_load_2d(a2_tile(i), &w_map, (kb0 + i) * kBK, w_row0 + up_row_off + n0, full_bar(i), kEvictFirst);
+    }
+  };
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&w_map);
     tma_prefetch_desc(&x_map);
@@ -85,6 +95,10 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_cons
     mbar_init(tmem_full_bar, 1);
     fence_barrier_init();
     fence_proxy_async();
+    // Weights depend neither on the previous kernel nor on this CTA's TMEM allocation: the thread that has just
+    // initialised the barriers can fill the ring with weight tiles at once, before the CTA-wide barrier below
+    // (DIS_GEMM_EARLY_TMA=0 keeps the round-1 order for A/B runs)
+    if (early_tma) issue_weights();
   }
   if (warp == 1) tmem_alloc<Cfg::kTmemCols>(tmem_slot);
   tc_fence_before();
@@ -99,12 +113,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_cons
     if (lane == 0) {
       // Weights do not depend on the previous kernel: fill the ring with weight tiles first, and only
       // then wait for the producer of the activations (programmatic dependent launch).
-      const int pre = min(kb1 - kb0, n_stages);
-      for (int i = 0; i < pre; i++) {
-        mbar_expect_tx(full_bar(i), stage_tx);
-        tma_load_2d(a_tile(i), &w_map, (kb0 + i) * kBK, w_row0 + n0, full_bar(i), kEvictFirst);
-        if (kDual) tma_load_2d(a2_tile(i), &w_map, (kb0 + i) * kBK, w_row0 + up_row_off + n0, full_bar(i), kEvictFirst);
-      }
+      if (!early_tma) issue_weights();
       pdl_wait();
       for (int i = 0; i < pre; i++) tma_load_2d(b_tile(i), &x_map, (kb0 + i) * kBK, t0, full_bar(i), kEvictLast);
       int s = pre == n_stages ? 0 : pre;
@@ -260,8 +269,10 @@ static cudaError_t gemm_launch(const TmaMap &w_map, const TmaMap &x_map, float *
   stages = stages > per ? (per < 2 ? 2 : per) : stages;  // never more stages than k-blocks
   const int smem = Cfg::smem_bytes(stages, tile_rows);
   if (smem > kMaxDynSmem) { set_last_error("gemm: tile does not fit shared memory"); return cudaErrorInvalidValue; }
+  static int early = -1;
+  if (early < 0) { const char *e = getenv("DIS_GEMM_EARLY_TMA"); early = (e && atoi(e) == 0) ? 0 : 1; }
   return launch_k(kern, grid, dim3(kGemmThreads), (size_t)smem, st, *reinterpret_cast<const CUtensorMap *>(&w_map),
-                  *reinterpret_cast<const CUtensorMap *>(&x_map), out, act, T, N, K, w_row0, up_off, per, tile_rows, stages);
+                  *reinterpret_cast<const CUtensorMap *>(&x_map), out, act, T, N, K, w_row0, up_off, per, tile_rows, stages, early);
 }
 
 cudaError_t launch_gemm_partial(const TmaMap &w_map, const TmaMap &x_map, float *out, int T, int N, int K,
