@@ -119,7 +119,6 @@ int Engine::init(const dis_engine_config *c) {
   const size_t widest = std::max<size_t>(std::max<size_t>(nqkv_l, H), inter_l <= 4096 ? (size_t)2 * inter_l : 0);
   partial_elems = std::max(cap * widest, (size_t)16 * 128 * widest);
   ENG_CUDA(dev_alloc(&x, cap * H, &bytes_allocated));
-  ENG_CUDA(dev_alloc(&x_alt, (size_t)kGemvMaxT * H, &bytes_allocated));
   ENG_CUDA(dev_alloc(&xn, cap * H, &bytes_allocated));
   ENG_CUDA(dev_alloc(&q, cap * qd_l, &bytes_allocated));
   ENG_CUDA(dev_alloc(&attn, cap * qd_l, &bytes_allocated));
@@ -218,7 +217,6 @@ int Engine::init(const dis_engine_config *c) {
   pf_tc = attn_prefill_uses_tc(nh_l, nkv_l, m.head_dim);
   if (const char *g = getenv("DIS_GEMM_PERSIST")) use_persist = atoi(g) != 0;
   if (const char *g = getenv("DIS_GEMV_MAX_T")) gemv_max_t = std::max(0, std::min(kGemvMaxT, atoi(g)));
-  if (const char *g = getenv("DIS_GEMV_FUSE_NORM")) gemv_fuse_norm = atoi(g) != 0;
   // Measurement aid, never set in production: DIS_DEBUG_SKIP=norm,attn,... leaves those kernel classes out of the
   // decode step (its results are then garbage) so that step time with and without a class gives the class's marginal
   // cost INSIDE the graph, where programmatic dependent launch overlaps neighbours and ncu's isolated times mislead.
@@ -312,7 +310,7 @@ Engine::~Engine() {
   for (int r = 0; r < kTpMaxRanks; r++) if (peer_base[r]) cudaIpcCloseMemHandle(peer_base[r]);
   void *ptrs[] = {embed, wqkv, wo, wgu, wdown, lm_head, attn_norm, mlp_norm, final_norm, x, partial, logits, ar_buf,
                   attn_scratch, full_logits, gather_buf, cand_val, cand_val_all, cand_tok, cand_tok_all, cand_sum, cand_sum_all, xn, q, attn,
-                  act, x_alt, d_out_tokens, kv_pool, d_page_table, rope_cos, rope_sin, meta_dec.dev, meta_pre.dev, sym};
+                  act, d_out_tokens, kv_pool, d_page_table, rope_cos, rope_sin, meta_dec.dev, meta_pre.dev, sym};
   for (void *p : ptrs) if (p) cudaFree(p);
   if (h_out_tokens) cudaFreeHost(h_out_tokens);
   if (h_page_table) cudaFreeHost(h_page_table);
@@ -631,13 +629,6 @@ cudaError_t Engine::enqueue_layers(int T, int n_splits) {
   struct PdlOff { ~PdlOff() { pdl_enabled() = false; } } pdl_off;
   pend_ptr = nullptr; pend_count = 0; pend_str = 0; pend_needs_ar = false;
   auto skip = [&](int cls) { return n_qblocks == 0 && tp_size == 1 && (skip_mask >> cls) & 1u; };
-  // batch-1 GEMV path: the residual add + RMSNorm in front of the QKV, gate-up and lm_head projections is computed
-  // inside the GEMV (k_gemv.cu); the residual alternates between x and x_alt, projection outputs between the two halves
-  // of `partial`, because every CTA of such a GEMV reads the old residual and the pending output while CTA 0 / the
-  // epilogues write the new ones
-  gfuse = gemv && gemv_fuse_norm && T == 1 && tp_size == 1 && n_qblocks == 0 && skip_mask == 0;
-  gx_cur = x; gx_next = x_alt;
-  float *const part_b = partial + partial_elems / 2;
   const uint32_t *tokens = cur_meta->d<uint32_t>(cur_meta->o_tokens);
   const int *pos = cur_meta->d<int>(cur_meta->o_pos), *ptrow = cur_meta->d<int>(cur_meta->o_ptrow), *ctx = cur_meta->d<int>(cur_meta->o_ctx);
   // a projection output becomes "pending": the next norm kernel adds it to the residual
@@ -657,18 +648,12 @@ cudaError_t Engine::enqueue_layers(int T, int n_splits) {
       kernel_launches++;
     } else {
       pdl_enabled() = pdl_ok;
-      if (!gfuse && !skip(P_NORM)) RET_CUDA(consume_pending(attn_norm + (size_t)l * H, nullptr, T, T));
+      if (!skip(P_NORM)) RET_CUDA(consume_pending(attn_norm + (size_t)l * H, nullptr, T, T));
     }
     pdl_enabled() = pdl_ok;
     int s_qkv = 1;
     prof_mark(P_QKV);
-    if (gfuse && l > 0) {
-      RET_CUDA(launch_gemv_norm(gx_cur, pend_ptr, pend_count, pend_str, attn_norm + (size_t)l * H, m.rms_eps, gx_next,
-                                wqkv + (size_t)l * nqkv_l * H, partial, nqkv_l, H, stream));
-      std::swap(gx_cur, gx_next);
-      pend_ptr = nullptr; pend_count = 0;
-      kernel_launches++;
-    } else if (!skip(P_QKV)) RET_CUDA(linear_partial(xn_map, xn, wqkv_map, wqkv, l * nqkv_l, T, nqkv_l, H, &s_qkv));
+    if (!skip(P_QKV)) RET_CUDA(linear_partial(xn_map, xn, wqkv_map, wqkv, l * nqkv_l, T, nqkv_l, H, &s_qkv));
     else s_qkv = gemm_pick_split_k(T, nqkv_l, H);
     uint16_t *pool = kv_pool + (size_t)l * kv_layer_stride;
     if (n_qblocks > 0) {
@@ -691,25 +676,13 @@ cudaError_t Engine::enqueue_layers(int T, int n_splits) {
     }
     int s_o = 1;
     prof_mark(P_OPROJ);
-    if (gfuse) {
-      RET_CUDA(launch_gemv(attn, wo + (size_t)l * H * qd_l, part_b, T, H, qd_l, stream));
-      kernel_launches++;
-      pend_ptr = part_b; pend_count = 1; pend_str = 0;
-    } else {
-      if (!skip(P_OPROJ)) RET_CUDA(linear_partial(attn_map, attn, wo_map, wo, l * H, T, H, qd_l, &s_o));
-      else s_o = gemm_pick_split_k(T, H, qd_l);
-      RET_CUDA(set_pending(s_o));
-    }
+    if (!skip(P_OPROJ)) RET_CUDA(linear_partial(attn_map, attn, wo_map, wo, l * H, T, H, qd_l, &s_o));
+    else s_o = gemm_pick_split_k(T, H, qd_l);
+    RET_CUDA(set_pending(s_o));
     prof_mark(P_NORM);
-    if (!gfuse && !skip(P_NORM)) RET_CUDA(consume_pending(mlp_norm + (size_t)l * H, nullptr, T, T));
+    if (!skip(P_NORM)) RET_CUDA(consume_pending(mlp_norm + (size_t)l * H, nullptr, T, T));
     prof_mark(P_GATEUP);
-    if (gfuse) {
-      RET_CUDA(launch_gemv_norm_silu(gx_cur, pend_ptr, pend_count, pend_str, mlp_norm + (size_t)l * H, m.rms_eps, gx_next,
-                                     wgu + (size_t)l * 2 * inter_l * H, act, inter_l, H, stream));
-      std::swap(gx_cur, gx_next);
-      pend_ptr = nullptr; pend_count = 0;
-      kernel_launches++;
-    } else if (gemv) {
+    if (gemv) {
       RET_CUDA(launch_gemv_silu(xn, wgu + (size_t)l * 2 * inter_l * H, act, T, inter_l, H, stream));
       kernel_launches += (uint64_t)((T + kGemvMaxT - 1) / kGemvMaxT);
     } else if (use_persist && gemm_use_persist(T, inter_l, true)) {
@@ -732,12 +705,6 @@ cudaError_t Engine::enqueue_layers(int T, int n_splits) {
     }
     int s_d = 1;
     prof_mark(P_DOWN);
-    if (gfuse) {
-      RET_CUDA(launch_gemv(act, wdown + (size_t)l * H * inter_l, part_b, T, H, inter_l, stream));
-      kernel_launches++;
-      pend_ptr = part_b; pend_count = 1; pend_str = 0;
-      continue;
-    }
     if (!skip(P_DOWN)) RET_CUDA(linear_partial(act_map, act, wdown_map, wdown, l * H, T, H, inter_l, &s_d));
     else s_d = gemm_pick_split_k(T, H, inter_l);
     RET_CUDA(set_pending(s_d));
@@ -750,14 +717,10 @@ cudaError_t Engine::enqueue_layers(int T, int n_splits) {
 cudaError_t Engine::enqueue_head(int R, bool all_greedy) {
   const int H = m.hidden;
   prof_mark(P_HEAD_NORM);
-  if (!(gfuse && rowmap_identity)) RET_CUDA(consume_pending(final_norm, rowmap_identity ? nullptr : cur_meta->d<int>(cur_meta->o_rowmap), R, last_T));
+  RET_CUDA(consume_pending(final_norm, rowmap_identity ? nullptr : cur_meta->d<int>(cur_meta->o_rowmap), R, last_T));
   const bool gemv = (cfg.flags & DIS_FLAG_FORCE_GEMV) || R <= gemv_max_t;
   prof_mark(P_LM_HEAD);
-  if (gfuse && rowmap_identity) {
-    RET_CUDA(launch_gemv_norm(gx_cur, pend_ptr, pend_count, pend_str, final_norm, m.rms_eps, gx_next, lm_head, logits, vocab_l, H, stream));
-    pend_ptr = nullptr; pend_count = 0;
-    kernel_launches++;
-  } else if (gemv) { RET_CUDA(launch_gemv(xn, lm_head, logits, R, vocab_l, H, stream)); kernel_launches += (uint64_t)((R + kGemvMaxT - 1) / kGemvMaxT); }
+  if (gemv) { RET_CUDA(launch_gemv(xn, lm_head, logits, R, vocab_l, H, stream)); kernel_launches += (uint64_t)((R + kGemvMaxT - 1) / kGemvMaxT); }
   else { RET_CUDA(launch_gemm_partial(lm_map, xn_map[tile_index(R)], logits, R, vocab_l, H, 0, 1, stream)); kernel_launches++; }
   prof_mark(P_SAMPLE);
   const float *temp = cur_meta->d<float>(cur_meta->o_temp), *topp = cur_meta->d<float>(cur_meta->o_topp);

@@ -90,10 +90,6 @@ struct Engine {
   uint32_t *cand_tok = nullptr, *cand_tok_all = nullptr;
   float *cand_sum = nullptr, *cand_sum_all = nullptr;  // sum exp(z - max) over the rank's vocabulary slice (logprob)
   uint16_t *xn = nullptr, *q = nullptr, *attn = nullptr, *act = nullptr;
-  float *x_alt = nullptr;   // second residual buffer of the norm-fused batch-1 GEMV path (kGemvMaxT rows)
-  bool gemv_fuse_norm = true;  // DIS_GEMV_FUSE_NORM=0: separate norm kernels on the GEMV path (A/B runs)
-  bool gfuse = false;          // the step being enqueued runs the norm-fused GEMV path
-  float *gx_cur = nullptr, *gx_next = nullptr;  // its residual ping-pong
   size_t partial_elems = 0, attn_scratch_elems = 0;
   TmaMap xn_map[4], attn_map[4], act_map[4];  // box rows 32 / 64 / 128 / 256
   uint32_t *d_out_tokens = nullptr, *h_out_tokens = nullptr;
@@ -105,7 +101,7 @@ struct Engine {
   bool use_pdl = true;  // programmatic dependent launch between the kernels of a step
   bool use_persist = true;  // prefill-sized projections through the persistent GEMM (DIS_GEMM_PERSIST=0: A/B runs)
   unsigned skip_mask = 0;  // DIS_DEBUG_SKIP (measurement only): kernel classes left out of the step, bit = ProfClass
-  int gemv_max_t = 1;   // steps of at most this many tokens take the GEMV path; from 2 tokens the tcgen05 path is faster (3.03 vs 4.09 ms per step). DIS_GEMV_MAX_T overrides, for A/B runs
+  int gemv_max_t = 0;   // steps of at most this many tokens take the GEMV path.  0: the tcgen05 path is faster at every T (T = 1: 3.06 vs 3.18 ms per step, T = 2: 3.03 vs 4.09); DIS_GEMV_MAX_T / DIS_FLAG_FORCE_GEMV select the GEMV
   PrefixIndex pages_ix;  // page allocator; with DIS_FLAG_PREFIX_CACHE also the prefix index (row f2)
   int *d_page_table = nullptr, *h_page_table = nullptr;
   bool pt_dirty = true;

@@ -13,6 +13,7 @@
 //
 // With n_splits > 1 every split writes (m, l, unnormalised o) to scratch and a combine pass merges
 // them (flash-decoding); that keeps all 148 SMs busy at batch 1.
+#include <cstdlib>
 #include <mutex>
 
 #include "../../include/dis_engine.h"
@@ -86,7 +87,7 @@ __global__ void __launch_bounds__(kAttnThreads, 2)
 attn_paged_kernel(const __grid_constant__ CUtensorMap kv_map, long long row0, const AttnRope rope, const uint16_t *__restrict__ q,
                   const int *__restrict__ page_table, int max_pages, const int *__restrict__ pt_row,
                   const int *__restrict__ ctx_len, uint16_t *__restrict__ out, float *__restrict__ scratch,
-                  int n_splits, int T, int n_heads, int n_kv, int page_shift) {
+                  int n_splits, int T, int n_heads, int n_kv, int page_shift, int n_stages) {
   using Cfg = AttnCfg<D>;
   constexpr int KS = D / 16;  // k-steps of the QK^T MMA
   constexpr int NT = D / 8;   // n-tiles of the P.V MMA
@@ -94,7 +95,7 @@ attn_paged_kernel(const __grid_constant__ CUtensorMap kv_map, long long row0, co
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;  // 128B swizzle atoms are 1024-byte aligned
   uint8_t *smem = smem_raw + (smem_base - smem_u32(smem_raw));
-  const uint32_t bar_base = smem_base + Cfg::kStages * Cfg::kStageBytes;
+  const uint32_t bar_base = smem_base + n_stages * Cfg::kStageBytes;
   auto full_bar = [&](int s) { return bar_base + 8u * s; };
 
   const int t = blockIdx.z;
@@ -106,7 +107,7 @@ attn_paged_kernel(const __grid_constant__ CUtensorMap kv_map, long long row0, co
 
   if (threadIdx.x == 0) {
     tma_prefetch_desc(&kv_map);
-    for (int s = 0; s < Cfg::kStages; s++) mbar_init(full_bar(s), 1);
+    for (int s = 0; s < n_stages; s++) mbar_init(full_bar(s), 1);
     fence_barrier_init();
     fence_proxy_async();
   }
@@ -146,7 +147,7 @@ attn_paged_kernel(const __grid_constant__ CUtensorMap kv_map, long long row0, co
   };
 
   if (threadIdx.x == 0) {
-    for (int s = 0; s < Cfg::kStages - 1; s++)
+    for (int s = 0; s < n_stages - 1; s++)
       if (s < n_tiles) load_tile(s, s);
   }
 
@@ -215,11 +216,11 @@ attn_paged_kernel(const __grid_constant__ CUtensorMap kv_map, long long row0, co
   for (int tile = 0; tile < n_tiles; tile++) {
     __syncthreads();  // everyone is done with the stage consumed last iteration
     if (threadIdx.x == 0) {
-      const int nt = tile + Cfg::kStages - 1;
-      if (nt < n_tiles) load_tile(nt, nt % Cfg::kStages);
+      const int nt = tile + n_stages - 1;
+      if (nt < n_tiles) load_tile(nt, nt % n_stages);
     }
-    const int stage = tile % Cfg::kStages;
-    mbar_wait(full_bar(stage), (uint32_t)(tile / Cfg::kStages) & 1u);
+    const int stage = tile % n_stages;
+    mbar_wait(full_bar(stage), (uint32_t)(tile / n_stages) & 1u);
     const uint32_t ks_addr = smem_base + stage * Cfg::kStageBytes;
     const uint32_t vs_addr = ks_addr + Cfg::kHalves * Cfg::kHalfBytes;
     const int tile_len = min(kAttnTile, end - (begin + tile * kAttnTile));
@@ -546,9 +547,18 @@ static cudaError_t attn_launch(const TmaMap &kv_map, long long row0, const AttnR
   dim3 grid(n_splits, n_kv, T);
   static DeviceOnce once;
   DIS_CUDA_TRY(once.run([&] { return cudaFuncSetAttribute(attn_paged_kernel<D, G>, cudaFuncAttributeMaxDynamicSharedMemorySize, AttnCfg<D>::kSmemBytes); }));
-  DIS_CUDA_TRY(launch_k(attn_paged_kernel<D, G>, grid, dim3(kAttnThreads), AttnCfg<D>::kSmemBytes, st,
+  // ring depth: fewer stages leave shared memory for the NEXT kernel's CTAs to become resident (and prefetch their
+  // weights) while this one is still streaming; DIS_ATTN_STAGES overrides (A/B runs), 2 <= stages <= AttnCfg::kStages
+  static int stages = 0;
+  if (stages == 0) {
+    const char *e = getenv("DIS_ATTN_STAGES");
+    stages = e ? atoi(e) : AttnCfg<D>::kStages;
+    stages = stages < 2 ? 2 : (stages > AttnCfg<D>::kStages ? AttnCfg<D>::kStages : stages);
+  }
+  const int smem = stages * AttnCfg<D>::kStageBytes + 1024 + 64;
+  DIS_CUDA_TRY(launch_k(attn_paged_kernel<D, G>, grid, dim3(kAttnThreads), (size_t)smem, st,
                         *reinterpret_cast<const CUtensorMap *>(&kv_map), row0, rope, q, page_table, max_pages, pt_row, ctx, out,
-                        scratch, n_splits, T, n_heads, n_kv, page_shift));
+                        scratch, n_splits, T, n_heads, n_kv, page_shift, stages));
   if (n_splits > 1)
     DIS_CUDA_TRY(launch_k(attn_combine_kernel<D>, dim3(n_heads, T), dim3(D), 0, st, (const float *)scratch, out, n_splits, T, n_heads));
   return cudaSuccess;

@@ -263,7 +263,15 @@ static cudaError_t gemm_launch(const TmaMap &w_map, const TmaMap &x_map, float *
   // more CTAs than SMs: leave room for two per SM (one CTA's epilogue overlaps the other's stream, and under PDL
   // the next kernel's CTA can prefetch beside this one); otherwise one CTA per SM gets the whole shared memory
   const long long ctas = (long long)grid.x * grid.y * grid.z;
-  const int budget = (ctas > kNumSMs && BN <= 128 && Cfg::kTmemCols <= 256) ? 110 * 1024 : 220 * 1024;
+  // DIS_GEMM_SMEM_KB2 / DIS_GEMM_SMEM_KB1 (A/B runs): shared memory per CTA when two / one CTA per SM is intended; a
+  // smaller ring leaves room for the NEXT kernel's CTAs to become resident and prefetch their weights meanwhile
+  static int kb2 = 0, kb1 = 0;
+  if (kb2 == 0) {
+    const char *e2 = getenv("DIS_GEMM_SMEM_KB2"), *e1 = getenv("DIS_GEMM_SMEM_KB1");
+    kb2 = e2 ? atoi(e2) : 110; kb1 = e1 ? atoi(e1) : 220;
+    kb2 = kb2 < 48 ? 48 : (kb2 > 110 ? 110 : kb2); kb1 = kb1 < 64 ? 64 : (kb1 > 220 ? 220 : kb1);
+  }
+  const int budget = (ctas > kNumSMs && BN <= 128 && Cfg::kTmemCols <= 256) ? kb2 * 1024 : kb1 * 1024;
   int stages = (budget - Cfg::smem_bytes(0, tile_rows)) / Cfg::stage_bytes(tile_rows);
   stages = stages > kMaxStages ? kMaxStages : (stages < 2 ? 2 : stages);
   stages = stages > per ? (per < 2 ? 2 : per) : stages;  // never more stages than k-blocks

@@ -32,8 +32,15 @@ __device__ __forceinline__ float dot8(const uint4 &w, const uint4 &x) {
 // kept full across row groups -- 4.15 ms per step: the per-item bookkeeping and a barrier per row group cost more
 // issue slots than the CTA turnover they remove; 4 rows x depth 4 -- 3.62 ms (fewer CTAs resident); this kernel as ONE
 // wave of CTAs each walking ~13 row groups (so that the dependent kernel is released at once) -- 4.18 ms: without
-// loads in flight across the group boundary the memory pipe idles during every reduction.  The tcgen05 path at
-// T = 1 takes 3.06 ms against this kernel's 3.17 (same box, alternating runs).
+// loads in flight across the group boundary the memory pipe idles during every reduction.  Round 2: the residual add +
+// RMSNorm in front of the QKV / gate-up / lm_head GEMV folded INTO the GEMV (every CTA rebuilds the 8 KB normalised
+// activation for itself from x + the pending output, which removes both norm kernels of a layer) -- 5.46 ms per step
+// against 3.18: 32 KB of L2 reads, two block barriers and an rsqrt in front of every one of 768-16032 short CTAs cost far
+// more than the two 4 us kernels they replace.  The tcgen05 path at T = 1 takes 3.06 ms against this kernel's 3.18 (same
+// box, alternating runs: profiles/r2_bench_b1_*.json): TMA keeps ~200 KB per SM in flight without registers or issue
+// slots and one wave of CTAs has no turnover, where this kernel stages its loads in registers (256 B per lane) and pays a
+// reduction tail per 8 rows.  The engine therefore uses the tcgen05 path from T = 1 by default; this kernel stays
+// selectable (DIS_FLAG_FORCE_GEMV, DIS_GEMV_MAX_T) and parity-tested.
 // kSilu: rows n < N are gate rows, rows N + n the matching up rows; output bf16 act[t][n].
 template <int kT, bool kSilu, int kW = kGemvW, int kDepthT = kGemvDepth>
 __global__ void __launch_bounds__(kGemvWarps * 32, (kT == 1 && kW * kDepthT <= 8) ? 3 : 2)
@@ -111,140 +118,6 @@ gemv_kernel(const uint16_t *__restrict__ X, const uint16_t *__restrict__ W, floa
       else out[(size_t)t * N + n] = g;
     }
   }
-}
-
-// Batch-1 GEMV with the residual add + RMSNorm that precedes it folded in (round 2): at one token the whole normalised
-// activation is 8 KB, so EVERY CTA rebuilds it for itself -- v = x + pending projection output (its split-K slices),
-// sum of squares, bf16(v * rsqrt * gain) into shared memory -- while its first weight loads are already in flight, and
-// the two norm kernels of a layer (4 us each in the graph, two grid-to-grid hand-offs) disappear.  CTA 0 also writes the
-// new residual to x_out, a DIFFERENT buffer from x_in (other CTAs are still reading x_in); likewise the GEMV's output must
-// not alias `pend`.  Same arithmetic as add_rmsnorm_kernel + gemv_kernel<1, ...> except for the association of the sum of
-// squares (256 threads x 4 groups here, 1024 x 1 there).
-template <bool kSilu, int kW>
-__global__ void __launch_bounds__(kGemvWarps * 32, 3)
-gemv_norm_kernel(const float *__restrict__ x_in, const float *__restrict__ pend, int n_pend, long long pend_stride,
-                 const float *__restrict__ gain, float eps, float *__restrict__ x_out, const uint16_t *__restrict__ W,
-                 float *__restrict__ out, uint16_t *__restrict__ act, int N, int K) {
-  constexpr int kRows = kSilu ? kW / 2 : kW;
-  extern __shared__ __align__(16) uint8_t gsm[];
-  float *vs = reinterpret_cast<float *>(gsm);                  // [K] fp32: x + pending
-  uint16_t *xs = reinterpret_cast<uint16_t *>(gsm + (size_t)K * 4);  // [K] bf16: the normalised activation
-  __shared__ float part[kGemvWarps][kW];
-  __shared__ float red[32];
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int n0 = blockIdx.x * kRows;
-  pdl_launch_dependents();
-  const uint16_t *wrow[kW];
-#pragma unroll
-  for (int r = 0; r < kRows; r++) {
-    const int n = min(n0 + r, N - 1);
-    wrow[r] = W + (size_t)n * K;
-    if (kSilu) wrow[kRows + r] = W + (size_t)(N + n) * K;
-  }
-  constexpr int kChunk = 256, kStride = kChunk * kGemvWarps;
-  const int k0 = warp * kChunk + lane * 8;
-  uint4 w[kGemvDepth][kW];
-#pragma unroll
-  for (int d = 0; d < kGemvDepth; d++) {
-    const int k = k0 + d * kStride;
-#pragma unroll
-    for (int r = 0; r < kW; r++) w[d][r] = k < K ? ld_stream_16(wrow[r] + k) : make_uint4(0u, 0u, 0u, 0u);
-  }
-  pdl_wait();
-  // ---- residual add + RMSNorm of the one token (the same order of operations as add_rmsnorm_kernel)
-  float ss = 0.f;
-  for (int i = threadIdx.x * 4; i < K; i += kGemvWarps * 32 * 4) {
-    float4 v = *reinterpret_cast<const float4 *>(x_in + i);
-#pragma unroll 4
-    for (int s = 0; s < n_pend; s++) {
-      const float4 p = *reinterpret_cast<const float4 *>(pend + (size_t)s * pend_stride + i);
-      v.x += p.x; v.y += p.y; v.z += p.z; v.w += p.w;
-    }
-    *reinterpret_cast<float4 *>(vs + i) = v;
-    if (blockIdx.x == 0) *reinterpret_cast<float4 *>(x_out + i) = v;
-    ss += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
-  }
-  ss = warp_sum(ss);
-  if (lane == 0) red[warp] = ss;
-  __syncthreads();
-  {
-    float r = lane < kGemvWarps ? red[lane] : 0.f;
-    ss = warp_sum(r);
-  }
-  const float inv = rsqrtf(ss / (float)K + eps);
-  for (int i = threadIdx.x * 4; i < K; i += kGemvWarps * 32 * 4) {
-    const float4 v = *reinterpret_cast<const float4 *>(vs + i);
-    const float4 g = *reinterpret_cast<const float4 *>(gain + i);
-    uint2 o;
-    o.x = float2_to_bf16x2(v.x * inv * g.x, v.y * inv * g.y);
-    o.y = float2_to_bf16x2(v.z * inv * g.z, v.w * inv * g.w);
-    *reinterpret_cast<uint2 *>(xs + i) = o;
-  }
-  __syncthreads();
-  float acc[kW];
-#pragma unroll
-  for (int r = 0; r < kW; r++) acc[r] = 0.f;
-  for (int kb = k0; kb < K; kb += kGemvDepth * kStride) {
-#pragma unroll
-    for (int d = 0; d < kGemvDepth; d++) {
-      const int k = kb + d * kStride;
-      uint4 cur[kW];
-#pragma unroll
-      for (int r = 0; r < kW; r++) cur[r] = w[d][r];
-      const int kn = k + kGemvDepth * kStride;
-      if (kn < K) {
-#pragma unroll
-        for (int r = 0; r < kW; r++) w[d][r] = ld_stream_16(wrow[r] + kn);
-      }
-      if (k < K) {
-        const uint4 x = *reinterpret_cast<const uint4 *>(xs + k);
-#pragma unroll
-        for (int r = 0; r < kW; r++) acc[r] += dot8(cur[r], x);
-      }
-    }
-  }
-#pragma unroll
-  for (int r = 0; r < kW; r++) {
-    const float v = warp_sum(acc[r]);
-    if (lane == 0) part[warp][r] = v;
-  }
-  __syncthreads();
-  if (threadIdx.x < kRows) {
-    const int r = threadIdx.x, n = n0 + r;
-    if (n < N) {
-      float g = 0.f, u = 0.f;
-#pragma unroll
-      for (int q = 0; q < kGemvWarps; q++) {
-        g += part[q][r];
-        if (kSilu) u += part[q][kRows + r];
-      }
-      if (kSilu) act[n] = float_to_bf16_bits((g / (1.0f + expf(-g))) * u);
-      else out[n] = g;
-    }
-  }
-}
-
-template <bool kSilu>
-static cudaError_t gemv_norm_dispatch(const float *x_in, const float *pend, int n_pend, long long pend_stride, const float *gain,
-                                      float eps, float *x_out, const uint16_t *W, float *out, uint16_t *act, int N, int K,
-                                      cudaStream_t st) {
-  if (K % 8 != 0 || K % 4 != 0) { set_last_error("gemv_norm: K must be a multiple of 8"); return cudaErrorInvalidValue; }
-  if (x_in == x_out || (const void *)pend == (const void *)out) { set_last_error("gemv_norm: x_out must not alias x_in, nor out the pending input"); return cudaErrorInvalidValue; }
-  const size_t smem = (size_t)K * 6;
-  auto kern = gemv_norm_kernel<kSilu, 8>;
-  if (smem > 48 * 1024) DIS_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  const int r1 = kSilu ? 4 : 8;
-  return launch_k(kern, dim3((N + r1 - 1) / r1), dim3(kGemvWarps * 32), smem, st, x_in, pend, n_pend, pend_stride, gain, eps, x_out,
-                  W, out, act, N, K);
-}
-
-cudaError_t launch_gemv_norm(const float *x_in, const float *pend, int n_pend, long long pend_stride, const float *gain, float eps,
-                             float *x_out, const uint16_t *W, float *out, int N, int K, cudaStream_t st) {
-  return gemv_norm_dispatch<false>(x_in, pend, n_pend, pend_stride, gain, eps, x_out, W, out, nullptr, N, K, st);
-}
-cudaError_t launch_gemv_norm_silu(const float *x_in, const float *pend, int n_pend, long long pend_stride, const float *gain,
-                                  float eps, float *x_out, const uint16_t *Wgu, uint16_t *act, int I, int K, cudaStream_t st) {
-  return gemv_norm_dispatch<true>(x_in, pend, n_pend, pend_stride, gain, eps, x_out, Wgu, nullptr, act, I, K, st);
 }
 
 template <bool kSilu>

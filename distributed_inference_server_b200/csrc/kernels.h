@@ -56,12 +56,6 @@ constexpr int kGemvMaxT = 4;
 cudaError_t launch_gemv(const uint16_t *X, const uint16_t *W, float *out, int T, int N, int K, cudaStream_t st);
 cudaError_t launch_gemv_silu(const uint16_t *X, const uint16_t *Wgu, uint16_t *act, int T, int I, int K,
                              cudaStream_t st);
-// one token, with the preceding residual add + RMSNorm folded in: v = x_in + sum of n_pend slices of pend, x_out = v
-// (x_out != x_in), activation = bf16(v * rsqrt(mean v^2 + eps) * gain); out / act must not alias pend
-cudaError_t launch_gemv_norm(const float *x_in, const float *pend, int n_pend, long long pend_stride, const float *gain, float eps,
-                             float *x_out, const uint16_t *W, float *out, int N, int K, cudaStream_t st);
-cudaError_t launch_gemv_norm_silu(const float *x_in, const float *pend, int n_pend, long long pend_stride, const float *gain,
-                                  float eps, float *x_out, const uint16_t *Wgu, uint16_t *act, int I, int K, cudaStream_t st);
 
 // k_attn_paged.cu
 size_t attn_scratch_elems(int T, int n_heads, int d, int n_splits);
