@@ -345,17 +345,15 @@ tp_add_rmsnorm_ll_kernel(TpPeers peers, float *__restrict__ x, const float *__re
 // spread over every SM instead of 64 CTAs of 1024 threads that first walk 8-9 split-K slices of a whole row.
 //   CTA (t, c), c = the owner rank of columns [c*Hs, (c+1)*Hs), one float4 per thread:
 //     hop 1   sum the split-K slices of its 4 columns; c != me: send them to rank c's RS area, flag in the data
-//     c == me sum the tp contributions IN RANK ORDER + residual, send the finished block to every peer's AG area
-//             (hop 2), reduce the block's sum of squares and send that too: one 8-byte {value, epoch} word per
-//             (owner, row) in the area the fenced kernels use for their flags
+//     c == me sum the tp contributions IN RANK ORDER + residual, send the finished block to every peer's AG area (hop 2)
 //     c != me take the finished block from the AG area as it arrives
-//     all     total sum of squares = the tp block sums added in rank order (every rank, every CTA: same bits),
-//             RMSNorm of its 4 columns.
+//     all     reduce the block's sum of squares and publish it in THIS GPU's memory (one 8-byte {value, epoch} word per
+//             (block, row) in the area the fenced kernels use for their flags); total = the tp block sums added in
+//             block order (every rank, every CTA: same bits); RMSNorm of its 4 columns.
 // The sum of squares is associated differently from the row kernels (per block, then over blocks), so this variant
 // is deterministic and identical on every rank but NOT bit-identical to the other three.
-// No CTA waits for a CTA of its own GPU that might not be resident yet, except for the block sum of its own rank's
-// owner CTA: owner CTAs have the lowest block indices, and the launcher only uses this kernel when the whole grid is
-// co-resident anyway (a CTA that has not started has not sent its hop-1 data, which a peer's owner CTA waits for).
+// A CTA waits for the block sums of the other CTAs of its row on its own GPU, and a peer's owner CTA waits for the hop-1
+// data of every CTA here: the launcher only uses this kernel when the whole grid is co-resident.
 __device__ __forceinline__ void st_ll1(uint32_t *p, float v, uint32_t e) {
   asm volatile("st.global.v2.u32 [%0], {%1,%2};" ::"l"(p), "r"(__float_as_uint(v)), "r"(e) : "memory");
 }
@@ -426,16 +424,17 @@ tp_add_rmsnorm_wide_kernel(TpPeers peers, float *__restrict__ x, const float *__
         st_ll(dst, a.x, a.y, epoch);
         st_ll(dst + 4, a.z, a.w, epoch);
       }
-    // this block's sum of squares, to everybody (this rank included)
-    const float ssb = tp_block_sum(sumsq4(0.f, a), red);
-    const size_t w = (((size_t)parity * tp + me) * cap + t) * 2;
-    if ((int)threadIdx.x < tp) st_ll1(peers.flags[threadIdx.x] + w, ssb, epoch);
   }
   *reinterpret_cast<float4 *>(x + (size_t)t * H + col) = a;
-  // ---- total sum of squares: the tp block sums in rank order
+  // ---- sum of squares of the row: every CTA reduces ITS block (the finished values are the same bits on every rank,
+  // so no NVLink traffic is needed for this), publishes the block sum in this GPU's own memory as one 8-byte
+  // {value, epoch} word, and adds the tp block sums of its row in block order
+  const float ssb = tp_block_sum(sumsq4(0.f, a), red);
   if (threadIdx.x == 0) {
+    uint32_t *mine = peers.flags[me] + (((size_t)parity * tp + c) * cap + t) * 2;
+    st_ll1(mine, ssb, epoch);
     float ss = 0.f;
-    for (int o = 0; o < tp; o++) ss += ld_ll1(peers.flags[me] + (((size_t)parity * tp + o) * cap + t) * 2, epoch);
+    for (int o = 0; o < tp; o++) ss += o == c ? ssb : ld_ll1(peers.flags[me] + (((size_t)parity * tp + o) * cap + t) * 2, epoch);
     s_inv = rsqrtf(ss / (float)H + eps);
   }
   __syncthreads();

@@ -24,4 +24,4 @@ P
 }
 run wide
 run ll --tp-exchange ll --no-parity
-if [ "$N" = 8 ]; then run 70b --model 70b --no-parity; fi
+if [ "$N" = 8 ]; then run 70b_ll --model 70b --no-parity --tp-exchange ll; run 70b_wide --model 70b --no-parity --tp-exchange wide; fi
