@@ -77,6 +77,7 @@ u16p, u32p, i32p, f32p, u64p, vp = (C.POINTER(C.c_uint16), C.POINTER(C.c_uint32)
 # name -> (restype, argtypes): every symbol include/dis_engine.h declares
 PROTOTYPES = {
     "dis_abi_version": (C.c_int, []),
+    "dis_build_id": (C.c_char_p, []),
     "dis_engine_create": (C.c_int, [C.POINTER(EngineConfig), C.POINTER(vp)]),
     "dis_engine_destroy": (C.c_int, [vp]),
     "dis_last_error": (C.c_char_p, []),

@@ -121,6 +121,9 @@ typedef struct dis_engine dis_engine;
 
 /* ---- lifecycle: InferenceWorker::initialize / shutdown (design.md:337,339) --------------------- */
 DIS_API int dis_abi_version(void);
+/* sha256 prefix over the sources, headers and compiler flags this binary was built from (distributed_inference_server_b200/
+ * build.py source_id()); lets a host or a test refuse a stale library.  No reference counterpart. */
+DIS_API const char *dis_build_id(void);
 DIS_API int dis_engine_create(const dis_engine_config *cfg, dis_engine **out);
 DIS_API int dis_engine_destroy(dis_engine *e);
 /* Global message for failures that have no handle yet (create). */

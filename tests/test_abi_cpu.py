@@ -82,3 +82,10 @@ def test_build_recipes_list_the_same_sources():
         block = text[text.index("let files = ["):]
         block = block[:block.index("];")]
         assert re.findall(r'"([\w.]+\.(?:cu|cpp))"', block) == want, path
+
+
+def test_library_was_built_from_the_current_sources():
+    """Binary provenance: libdis_engine.so is git-ignored yet travels to the GPU box, so it must say what it was built
+    from -- dis_build_id() is the hash of every source, header and compiler flag, and has to match the tree."""
+    from distributed_inference_server_b200 import build as b
+    assert B.load().dis_build_id().decode() == b.source_id()
