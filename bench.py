@@ -597,7 +597,7 @@ def run_ours(args):
             line["config"]["workload"] += f" [REDUCED DEPTH {args.layers} layers: not a valid headline number]"
         if world > 1:
             line["config"]["tp_exchange"] = "NCCL all-reduce" if args.nccl_allreduce else (
-                "fused peer-memory exchange (k_tp.cu), " + (args.tp_exchange if args.tp_exchange != "auto" else "wide (flag-in-data two-shot, one CTA per row and column block)"))
+                "fused peer-memory exchange (k_tp.cu), " + (args.tp_exchange if args.tp_exchange != "auto" else ("wide (flag-in-data two-shot, one CTA per row and column block)" if shape.hidden > 4096 else "ll (flag-in-data two-shot, one CTA per row)")))
         if args.shard_of > 1:
             line["config"]["workload"] += f" [DIAGNOSTIC: one rank's shard of TP={args.shard_of}, no exchange: not a headline number]"
     eng.close()
@@ -756,7 +756,7 @@ def main():
     ap.add_argument("--no-pdl", action="store_true", help="disable programmatic dependent launch (A/B)")
     ap.add_argument("--nccl-allreduce", action="store_true", help="TP: use NCCL instead of the fused peer-memory exchange (A/B)")
     ap.add_argument("--tp-exchange", choices=["auto", "oneshot", "twoshot", "ll", "wide"], default="auto",
-                    help="TP: peer-memory exchange kernel (auto = wide: reduce-scatter + all-gather with flag-in-data stores on a (row, column block) grid)")
+                    help="TP: peer-memory exchange kernel (auto = ll, the flag-in-data row kernel, up to hidden 4096; wide, the same protocol on a (row, column block) grid, above)")
     ap.add_argument("--workload", default="decode", choices=["decode", "serving", "prefix"], help="serving = BASELINE configs[4]; prefix = TTFT with prefix KV reuse (row f2)")
     ap.add_argument("--model", default="8b", choices=["8b", "70b"], help="70b = BASELINE configs[3] (TP=8, batch 32)")
     ap.add_argument("--requests", type=int, default=256)

@@ -288,14 +288,19 @@ int Engine::tp_import(const uint8_t *handles) {
   // one-shot (tp-1)*T*H*4 bytes and one flag hop, or two-shot 2*(tp-1)/tp*T*H*4 bytes and two hops
   // measured at batch 64, H = 4096, ms per step (one-shot / fenced two-shot / flag-in-data two-shot):
   //   TP=2  3.44 / 3.76 / 3.28      TP=4  2.80 / 3.00 / 2.64      TP=8  2.88 / 2.67 / 2.42
+  // round 2, flag-in-data row kernel (ll) against the wide-grid kernel:
+  //   H = 4096 (8B, batch 64)   TP=2 2.942 / 2.941   TP=4 2.424 / 2.464   TP=8 2.390 / 2.509   -> ll
+  //   H = 8192 (70B, batch 32)  TP=8 7.986 / 7.667                                             -> wide: a row that needs two
+  //   float4 per thread in the row kernel is where spreading the local work over more CTAs starts to pay
   // The choice is fixed per engine (the kernels lay the symmetric buffer out differently).
   const bool blocks_ok = m.hidden % (4 * tp_size) == 0;
-  peers.two_shot = blocks_ok ? ((m.hidden / tp_size) % 128 == 0 ? 3 : 2) : 0;
+  const bool wide_ok = blocks_ok && (m.hidden / tp_size) % 128 == 0;
+  peers.two_shot = blocks_ok ? (wide_ok && m.hidden > 4096 ? 3 : 2) : 0;
   if (const char *e = getenv("DIS_TP_EXCHANGE")) {
     if (!strcmp(e, "oneshot")) peers.two_shot = 0;
     else if (!strcmp(e, "twoshot") && blocks_ok) peers.two_shot = 1;
     else if (!strcmp(e, "ll") && blocks_ok) peers.two_shot = 2;
-    else if (!strcmp(e, "wide") && blocks_ok && (m.hidden / tp_size) % 128 == 0) peers.two_shot = 3;
+    else if (!strcmp(e, "wide") && wide_ok) peers.two_shot = 3;
   }
   tp_custom = true;
   return DIS_OK;

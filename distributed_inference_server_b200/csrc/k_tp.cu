@@ -340,7 +340,8 @@ tp_add_rmsnorm_ll_kernel(TpPeers peers, float *__restrict__ x, const float *__re
   }
 }
 
-// Wide-grid variant of the flag-in-data exchange (two_shot == 3, the default where it applies): the same two hops, but
+// Wide-grid variant of the flag-in-data exchange (two_shot == 3; the default for hidden sizes above 4096, see the
+// measurements in Engine::tp_import): the same two hops, but
 // one CTA per (row, column block) instead of one per row, so that at TP=8 a 64-row exchange runs on 512 small CTAs
 // spread over every SM instead of 64 CTAs of 1024 threads that first walk 8-9 split-K slices of a whole row.
 //   CTA (t, c), c = the owner rank of columns [c*Hs, (c+1)*Hs), one float4 per thread:
