@@ -217,6 +217,7 @@ int Engine::init(const dis_engine_config *c) {
   pf_tc = attn_prefill_uses_tc(nh_l, nkv_l, m.head_dim);
   if (const char *g = getenv("DIS_GEMM_PERSIST")) use_persist = atoi(g) != 0;
   if (const char *g = getenv("DIS_GEMV_MAX_T")) gemv_max_t = std::max(0, std::min(kGemvMaxT, atoi(g)));
+  if (const char *g = getenv("DIS_ATTN_MAX_SPLITS")) max_attn_splits = atoi(g);
   // Measurement aid, never set in production: DIS_DEBUG_SKIP=norm,attn,... leaves those kernel classes out of the
   // decode step (its results are then garbage) so that step time with and without a class gives the class's marginal
   // cost INSIDE the graph, where programmatic dependent launch overlaps neighbours and ncu's isolated times mislead.
@@ -563,6 +564,7 @@ int Engine::pick_attn_splits(int T, int max_ctx_in_batch) const {
   int want = std::max(1, (2 * kNumSMs) / ctas);
   const int cap = std::max(1, max_ctx_in_batch / 128);
   want = std::min(std::min(want, cap), 32);
+  if (max_attn_splits > 0) want = std::min(want, max_attn_splits);  // DIS_ATTN_MAX_SPLITS (A/B runs)
   while ((size_t)T * nh_l * want * (2 + m.head_dim) > attn_scratch_elems && want > 1) want--;
   return std::max(want, 1);
 }

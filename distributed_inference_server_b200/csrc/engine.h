@@ -100,6 +100,7 @@ struct Engine {
   TmaMap kv_map;  // the whole pool as [rows][head_dim]
   bool use_pdl = true;  // programmatic dependent launch between the kernels of a step
   bool use_persist = true;  // prefill-sized projections through the persistent GEMM (DIS_GEMM_PERSIST=0: A/B runs)
+  int max_attn_splits = 0;  // DIS_ATTN_MAX_SPLITS: cap on the split-KV factor of the decode attention (0 = none)
   unsigned skip_mask = 0;  // DIS_DEBUG_SKIP (measurement only): kernel classes left out of the step, bit = ProfClass
   int gemv_max_t = 0;   // steps of at most this many tokens take the GEMV path.  0: the tcgen05 path is faster at every T (T = 1: 3.06 vs 3.18 ms per step, T = 2: 3.03 vs 4.09); DIS_GEMV_MAX_T / DIS_FLAG_FORCE_GEMV select the GEMV
   PrefixIndex pages_ix;  // page allocator; with DIS_FLAG_PREFIX_CACHE also the prefix index (row f2)
