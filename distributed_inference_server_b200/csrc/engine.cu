@@ -242,6 +242,15 @@ int Engine::init(const dis_engine_config *c) {
     const size_t flags_b = align_up((size_t)2 * 2 * tp_size * ar_cap_rows * 4, 256);  // two hops
     const size_t cand_b = align_up((size_t)2 * tp_size * ar_cap_rows * 4 * 4, 256);
     sym_bytes = data_b + flags_b + cand_b + 256;
+    // Prefill-sized passes (more rows than the decode region holds) get their own region, laid out for the fenced
+    // two-shot kernel, whose bytes on the wire are the minimum (2 (tp-1)/tp * T*H*4): such an exchange is
+    // bandwidth-bound, and fused it replaces reduce_partials + ncclAllReduce + a separate norm kernel by one kernel.
+    // DIS_TP_PREFILL_NCCL=1 keeps the NCCL path (A/B runs); hidden % (4 tp) != 0 has no column blocks to own.
+    if (cap_tokens > ar_cap_rows && m.hidden % (4 * tp_size) == 0 && !(getenv("DIS_TP_PREFILL_NCCL") && atoi(getenv("DIS_TP_PREFILL_NCCL")))) {
+      ar_cap_big = cap_tokens;
+      sym_big_off = align_up(sym_bytes, 256);
+      sym_bytes = sym_big_off + (size_t)4 * ar_cap_big * m.hidden * sizeof(float) + align_up((size_t)2 * 2 * tp_size * ar_cap_big * 4, 256);
+    }
     ENG_CUDA(dev_alloc(&sym, sym_bytes, &bytes_allocated));
     ENG_CUDA(cudaMemset(sym, 0, sym_bytes));
   }
@@ -286,6 +295,16 @@ int Engine::tp_import(const uint8_t *handles) {
   peers.rank = tp_rank;
   peers.tp = tp_size;
   peers.cap_rows = ar_cap_rows;
+  if (ar_cap_big > 0) {
+    peers_big = peers;
+    for (int r = 0; r < tp_size; r++) {
+      uint8_t *base = reinterpret_cast<uint8_t *>(peers.data[r]) + sym_big_off;
+      peers_big.data[r] = reinterpret_cast<float *>(base);
+      peers_big.flags[r] = reinterpret_cast<uint32_t *>(base + (size_t)4 * ar_cap_big * m.hidden * sizeof(float));
+    }
+    peers_big.cap_rows = ar_cap_big;
+    peers_big.two_shot = 1;
+  }
   // one-shot (tp-1)*T*H*4 bytes and one flag hop, or two-shot 2*(tp-1)/tp*T*H*4 bytes and two hops
   // measured at batch 64, H = 4096, ms per step (one-shot / fenced two-shot / flag-in-data two-shot):
   //   TP=2  3.44 / 3.76 / 3.28      TP=4  2.80 / 3.00 / 2.64      TP=8  2.88 / 2.67 / 2.42
@@ -611,7 +630,7 @@ cudaError_t Engine::consume_pending(const float *gain, const int *row_map, int r
   if (pend_needs_ar) {
     // fused exchange over peer memory: split-K reduce + all-reduce + residual + norm in one kernel
     const int idx = ar_idx++;
-    RET_CUDA(launch_tp_add_rmsnorm(peers, x, pend_ptr, pend_count, pend_str, gain, xn,
+    RET_CUDA(launch_tp_add_rmsnorm(T <= ar_cap_rows ? peers : peers_big, x, pend_ptr, pend_count, pend_str, gain, xn,
                                    cur_meta->d<uint32_t>(cur_meta->o_arstep), (uint32_t)idx, idx & 1, T, H, m.rms_eps, stream));
     kernel_launches++;
     pend_needs_ar = false; pend_ptr = nullptr; pend_count = 0;
@@ -629,7 +648,7 @@ cudaError_t Engine::consume_pending(const float *gain, const int *row_map, int r
 cudaError_t Engine::enqueue_layers(int T, int n_splits) {
   const int H = m.hidden, d = m.head_dim;
   const bool gemv = (cfg.flags & DIS_FLAG_FORCE_GEMV) || T <= gemv_max_t;
-  const bool fused_ar = tp_size > 1 && tp_custom && T <= ar_cap_rows;  // exchange over peer memory, no NCCL kernel
+  const bool fused_ar = tp_size > 1 && tp_custom && (T <= ar_cap_rows || T <= ar_cap_big);  // exchange over peer memory, no NCCL kernel
   const bool pdl_ok = use_pdl && !profiling && (tp_size == 1 || fused_ar);
   // the PDL switch is thread-local state of the launch helper: whatever way this function is left, later
   // kernel-level calls on this host thread must not inherit it

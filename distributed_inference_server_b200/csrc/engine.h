@@ -137,9 +137,11 @@ struct Engine {
   void *comm = nullptr;
   // peer-memory exchange (k_tp.cu): one symmetric allocation per rank, mapped into every peer through CUDA IPC
   uint8_t *sym = nullptr;
-  size_t sym_bytes = 0;
+  size_t sym_bytes = 0, sym_big_off = 0;
   void *peer_base[kTpMaxRanks] = {};
   TpPeers peers{};
+  TpPeers peers_big{};      // second region of the symmetric buffer: fenced two-shot exchange for prefill-sized passes
+  int ar_cap_big = 0;       // rows that region holds (0: absent, such passes go through NCCL)
   bool tp_custom = false;   // peers imported: all-reduce fused into the norm kernels
   int ar_cap_rows = 0;
   uint32_t ar_step = 0;

@@ -317,7 +317,8 @@ attn_prefill_tc2_kernel(const __grid_constant__ CUtensorMap kv_map, long long ro
   const uint32_t p_full = bar_base + 8u * 10, o_full = bar_base + 8u * 11;
   const uint32_t tmem_slot = bar_base + 8u * 12;
 
-  const int qb = blockIdx.x, kvh = blockIdx.y;
+  // later query blocks of a sequence have more key tiles: launch them first, so that the longest CTAs do not form the tail
+  const int qb = (int)gridDim.x - 1 - (int)blockIdx.x, kvh = blockIdx.y;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
   if (threadIdx.x == 0) {
@@ -445,9 +446,12 @@ attn_prefill_tc2_kernel(const __grid_constant__ CUtensorMap kv_map, long long ro
           if (tile0 + 32 + i > qp) s1[i] = 0xff800000u;
         }
       }
-      float mx = -INFINITY;
+      // four independent chains each for the maximum and the row sum: two warps per scheduler do not hide the latency of
+      // one 32-deep dependent chain (ncu: "wait" and "long scoreboard" are the top two stall reasons)
+      float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
 #pragma unroll
-      for (int i = 0; i < 32; i++) mx = fmaxf(mx, fmaxf(__uint_as_float(s0[i]), __uint_as_float(s1[i])));
+      for (int i = 0; i < 32; i++) mx4[i & 3] = fmaxf(mx4[i & 3], fmaxf(__uint_as_float(s0[i]), __uint_as_float(s1[i])));
+      const float mx = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3]));
       const float m_new = fmaxf(m_ref, mx * scale_log2);
       if (j == 0) {
         m_ref = m_new;  // finite: key 0 is visible to every query; O is first written by P_0 V_0 (accumulate off)
@@ -473,7 +477,7 @@ attn_prefill_tc2_kernel(const __grid_constant__ CUtensorMap kv_map, long long ro
         }
       }
       const float neg_m = -m_ref;
-      float ps0 = 0.f, ps1 = 0.f;
+      float ps4[4] = {0.f, 0.f, 0.f, 0.f};
       uint8_t *prow = smem + (p_base - smem_base) + (row >> 3) * 1024 + (row & 7) * 128;
 #pragma unroll
       for (int c = 0; c < 8; c++) {
@@ -483,12 +487,12 @@ attn_prefill_tc2_kernel(const __grid_constant__ CUtensorMap kv_map, long long ro
           const int i = c * 8 + e * 2;
           const float p0 = ex2_approx(fmaf(__uint_as_float(i < 32 ? s0[i] : s1[i - 32]), scale_log2, neg_m));
           const float p1 = ex2_approx(fmaf(__uint_as_float(i + 1 < 32 ? s0[i + 1] : s1[i + 1 - 32]), scale_log2, neg_m));
-          ps0 += p0; ps1 += p1;
+          ps4[e] += p0 + p1;
           pk[e] = float2_to_bf16x2(p0, p1);
         }
         *reinterpret_cast<uint4 *>(prow + ((c ^ (row & 7)) << 4)) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
       }
-      l_run += ps0 + ps1;
+      l_run += (ps4[0] + ps4[1]) + (ps4[2] + ps4[3]);
       fence_proxy_async();
       tc_fence_before();
       mbar_arrive(p_full);

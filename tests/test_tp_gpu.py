@@ -30,9 +30,10 @@ def shape_for(world):
     return SHAPE if world == 2 else SHAPE8
 
 
-def _rank(rank, world, idq, outq, prompts, n_new, temps, hq, custom, SHAPE=None, SEED=None):
+def _rank(rank, world, idq, outq, prompts, n_new, temps, hq, custom, SHAPE=None, SEED=None, step_tokens=256, env=None):
     SHAPE = SHAPE or globals()["SHAPE"]
     SEED = SEED or globals()["SEED"]
+    os.environ.update(env or {})
     if custom:  # "oneshot" / "twoshot": which peer-memory exchange kernel the engine uses (k_tp.cu)
         os.environ["DIS_TP_EXCHANGE"] = custom
     from distributed_inference_server_b200 import Engine, InferenceParams, WorkerConfig, shard_plan as SP
@@ -48,7 +49,7 @@ def _rank(rank, world, idq, outq, prompts, n_new, temps, hq, custom, SHAPE=None,
     else:
         nccl_id = idq.get(timeout=120)
     e = Engine(WorkerConfig(to_engine_shape(SHAPE), device=rank, tp_rank=rank, tp_size=world, max_batch=8, kv_pages=64,
-                            page_size=16, max_step_tokens=256, nccl_id=nccl_id))
+                            page_size=16, max_step_tokens=step_tokens, nccl_id=nccl_id))
     e.load_synthetic(SEED)
     e.finalize()
     if custom:  # fused all-reduce over peer memory: exchange the CUDA IPC handles of the symmetric buffers
@@ -80,11 +81,12 @@ def _rank(rank, world, idq, outq, prompts, n_new, temps, hq, custom, SHAPE=None,
     e.close()
 
 
-def _run(prompts, n_new, temps, custom, world=2, shape=None, seed=None):
+def _run(prompts, n_new, temps, custom, world=2, shape=None, seed=None, step_tokens=256, env=None):
     ctx = mp.get_context("spawn")
     idq, outq = ctx.Queue(), ctx.Queue()
     hq = [ctx.Queue() for _ in range(world)]
-    procs = [ctx.Process(target=_rank, args=(r, world, idq, outq, prompts, n_new, temps, hq, custom, shape, seed)) for r in range(world)]
+    procs = [ctx.Process(target=_rank, args=(r, world, idq, outq, prompts, n_new, temps, hq, custom, shape, seed, step_tokens, env))
+             for r in range(world)]
     for p in procs:
         p.start()
     res = {}
@@ -191,3 +193,31 @@ def test_tp2_64_greedy_tokens_identical_to_transformers():
     res = _run([z["prompt"].tolist()], 64, [0.0], "ll", shape=shape, seed=int(z["weight_seed"]))
     assert res[0][0] == res[1][0] == [z["greedy"].tolist()]
 
+
+
+@pytest.mark.parametrize("world", WORLDS[:2])
+def test_tp_prefill_pass_larger_than_the_decode_exchange_region(world):
+    """A prefill pass of more rows than the decode-sized exchange region holds (128 here) takes the second region of the
+    symmetric buffer and the fenced two-shot kernel instead of reduce + ncclAllReduce + norm: 330 prompt tokens in one
+    pass.  Checked against the fp32 oracle, and against the NCCL path it replaces (same additions up to the order in
+    which the ranks' partial sums meet: held to the logit tolerance, greedy ids compared with the margin rule)."""
+    shape = shape_for(world)
+    rng = np.random.default_rng(6)
+    prompts = [rng.integers(0, shape.vocab, n).tolist() for n in (160, 110, 60)]
+    n_new = 6
+    kw = dict(world=world, shape=shape, step_tokens=512)
+    fused = _run(prompts, n_new, [0.0] * 3, "ll", **kw)
+    nccl = _run(prompts, n_new, [0.0] * 3, "ll", env={"DIS_TP_PREFILL_NCCL": "1"}, **kw)
+    for r in range(1, world):
+        assert fused[0][0] == fused[r][0] and np.array_equal(fused[0][1], fused[r][1])
+    ref = O.Oracle(shape, act_round=False); ref.fill_synthetic(SEED, True)
+    want = ref.generate(prompts, 1, n_logit_steps=1)
+    scale = np.abs(want["logits"]).max()
+    assert np.abs(fused[0][1] - want["logits"][:, 0]).max() <= 2e-2 * scale
+    assert np.abs(fused[0][1] - nccl[0][1]).max() <= 2e-2 * scale
+    mimic = O.Oracle(shape, act_round=True); mimic.fill_synthetic(SEED, True)
+    w = mimic.generate(prompts, n_new, n_logit_steps=n_new)
+    for b in range(len(prompts)):
+        if fused[0][0][b] != w["tokens"][b]:
+            i = next(k for k in range(n_new) if fused[0][0][b][k] != w["tokens"][b][k])
+            assert w["margins"][b, i] <= 5e-3 * np.abs(w["logits"][b, i]).max(), (b, i)
