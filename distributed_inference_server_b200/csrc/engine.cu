@@ -242,11 +242,13 @@ int Engine::init(const dis_engine_config *c) {
     const size_t flags_b = align_up((size_t)2 * 2 * tp_size * ar_cap_rows * 4, 256);  // two hops
     const size_t cand_b = align_up((size_t)2 * tp_size * ar_cap_rows * 4 * 4, 256);
     sym_bytes = data_b + flags_b + cand_b + 256;
-    // Prefill-sized passes (more rows than the decode region holds) get their own region, laid out for the fenced
-    // two-shot kernel, whose bytes on the wire are the minimum (2 (tp-1)/tp * T*H*4): such an exchange is
-    // bandwidth-bound, and fused it replaces reduce_partials + ncclAllReduce + a separate norm kernel by one kernel.
-    // DIS_TP_PREFILL_NCCL=1 keeps the NCCL path (A/B runs); hidden % (4 tp) != 0 has no column blocks to own.
-    if (cap_tokens > ar_cap_rows && m.hidden % (4 * tp_size) == 0 && !(getenv("DIS_TP_PREFILL_NCCL") && atoi(getenv("DIS_TP_PREFILL_NCCL")))) {
+    // Prefill-sized passes (more rows than the decode region holds) go through reduce_partials + ncclAllReduce + the norm
+    // kernel.  DIS_TP_PREFILL_FUSED=1 gives them their own region of the symmetric buffer and the fenced two-shot kernel
+    // instead (one kernel, minimum bytes on the wire: 2 (tp-1)/tp * T*H*4) -- parity-green (tests/test_tp_gpu.py) but
+    // measured SLOWER: TTFT of 64 x 512 tokens at TP=2 451 ms against 323 ms with NCCL.  One 1024-thread CTA per row with
+    // two release fences (an NVLink round trip each) moves 296 rows per ~25 us; a bandwidth-bound exchange of 8192 rows
+    // wants a few persistent CTAs streaming many rows each, which this kernel is not.  Kept as an opt-in for that work.
+    if (cap_tokens > ar_cap_rows && m.hidden % (4 * tp_size) == 0 && getenv("DIS_TP_PREFILL_FUSED") && atoi(getenv("DIS_TP_PREFILL_FUSED"))) {
       ar_cap_big = cap_tokens;
       sym_big_off = align_up(sym_bytes, 256);
       sym_bytes = sym_big_off + (size_t)4 * ar_cap_big * m.hidden * sizeof(float) + align_up((size_t)2 * 2 * tp_size * ar_cap_big * 4, 256);

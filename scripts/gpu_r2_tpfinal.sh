@@ -17,12 +17,4 @@ try:
 except Exception as ex:
     print("  failed:", ex); print(open(sys.argv[1].replace(".json",".err")).read()[-2500:])
 P
-DIS_TP_PREFILL_NCCL=1 timeout 900 $L bench.py --gpus $N --steps 20 --warmup 5 --no-parity > $O/r2tpf${N}_bench_ncclprefill.json 2> $O/r2tpf${N}_bench_ncclprefill.err; echo "bench (NCCL prefill) rc=$?"
-python - $O/r2tpf${N}_bench_ncclprefill.json <<'P'
-import json,sys
-try:
-    d=json.loads(open(sys.argv[1]).read().strip().splitlines()[-1]); print("  NCCL prefill: ttft", d.get("ttft_ms_p50"), round(d["value"]), "tok/s")
-except Exception as ex:
-    print("  failed:", ex)
-P
 timeout 900 $L bench.py --impl reference --gpus $N --steps 5 --warmup 1 > $O/r2tpf${N}_ref.json 2> $O/r2tpf${N}_ref.err; echo "ref rc=$?"; cut -c1-300 $O/r2tpf${N}_ref.json

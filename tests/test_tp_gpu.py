@@ -197,17 +197,18 @@ def test_tp2_64_greedy_tokens_identical_to_transformers():
 
 @pytest.mark.parametrize("world", WORLDS[:2])
 def test_tp_prefill_pass_larger_than_the_decode_exchange_region(world):
-    """A prefill pass of more rows than the decode-sized exchange region holds (128 here) takes the second region of the
-    symmetric buffer and the fenced two-shot kernel instead of reduce + ncclAllReduce + norm: 330 prompt tokens in one
-    pass.  Checked against the fp32 oracle, and against the NCCL path it replaces (same additions up to the order in
-    which the ranks' partial sums meet: held to the logit tolerance, greedy ids compared with the margin rule)."""
+    """DIS_TP_PREFILL_FUSED=1: a prefill pass of more rows than the decode-sized exchange region holds (128 here) takes the
+    second region of the symmetric buffer and the fenced two-shot kernel instead of reduce + ncclAllReduce + norm (the
+    default, which is faster: see Engine::init): 330 prompt tokens in one pass.  Checked against the fp32 oracle, and
+    against the NCCL path (same additions up to the order in which the ranks' partial sums meet: held to the logit
+    tolerance, greedy ids compared with the margin rule)."""
     shape = shape_for(world)
     rng = np.random.default_rng(6)
     prompts = [rng.integers(0, shape.vocab, n).tolist() for n in (160, 110, 60)]
     n_new = 6
     kw = dict(world=world, shape=shape, step_tokens=512)
-    fused = _run(prompts, n_new, [0.0] * 3, "ll", **kw)
-    nccl = _run(prompts, n_new, [0.0] * 3, "ll", env={"DIS_TP_PREFILL_NCCL": "1"}, **kw)
+    fused = _run(prompts, n_new, [0.0] * 3, "ll", env={"DIS_TP_PREFILL_FUSED": "1"}, **kw)
+    nccl = _run(prompts, n_new, [0.0] * 3, "ll", **kw)
     for r in range(1, world):
         assert fused[0][0] == fused[r][0] and np.array_equal(fused[0][1], fused[r][1])
     ref = O.Oracle(shape, act_round=False); ref.fill_synthetic(SEED, True)
