@@ -618,9 +618,11 @@ cudaError_t Engine::linear_partial(const TmaMap *xmaps, const uint16_t *xptr, co
 cudaError_t Engine::allreduce_partials(int split, int T) {
   const long long n = (long long)T * m.hidden;
   prof_mark(P_ALLREDUCE);
-  RET_CUDA(launch_reduce_partials(partial, split, n, ar_buf, n, stream));
-  kernel_launches += 2;
-  const int r = nccl->AllReduce(ar_buf, ar_buf, (size_t)n, /*ncclFloat32*/ 7, /*ncclSum*/ 0, comm, stream);
+  const float *src = ar_buf;
+  if (split == 1) src = partial;  // prefill-sized GEMMs do not split K: NCCL reads the projection output where it lies
+  else { RET_CUDA(launch_reduce_partials(partial, split, n, ar_buf, n, stream)); kernel_launches++; }
+  kernel_launches++;
+  const int r = nccl->AllReduce(src, ar_buf, (size_t)n, /*ncclFloat32*/ 7, /*ncclSum*/ 0, comm, stream);
   if (r != 0) { set_last_error(std::string("ncclAllReduce: ") + nccl->GetErrorString(r)); return cudaErrorUnknown; }
   return cudaSuccess;
 }
@@ -925,7 +927,6 @@ int Engine::step_mixed(int n, const int *slots, int max_prefill_tokens, uint32_t
   }
   ENG_CUDA(cudaSetDevice(cfg.device));
   // rows that cannot run fail alone (Property 22, design.md:812-816)
-  std::vector<int> remaining((size_t)n), take((size_t)n);
   std::vector<char> live((size_t)n, 0);
   std::vector<int> idx;
   for (int i = 0; i < n; i++) {
@@ -957,7 +958,6 @@ int Engine::step_mixed(int n, const int *slots, int max_prefill_tokens, uint32_t
   struct MetaReset { Engine *e; ~MetaReset() { e->cur_meta = &e->meta_dec; e->n_qblocks = 0; } } meta_reset{this};
   int T = 0, R = 0, QB = 0;
   bool all_greedy = true;
-  std::vector<int> owners;  // logits row -> position in the caller's list
   for (size_t k = 0; k < idx.size(); k++) {
     const int i = idx[k];
     Sequence &s = seqs[(size_t)slots[i]];
@@ -987,7 +987,6 @@ int Engine::step_mixed(int n, const int *slots, int max_prefill_tokens, uint32_t
       cur_meta->h<unsigned long long>(cur_meta->o_seed)[R] = s.seed;
       cur_meta->h<unsigned long long>(cur_meta->o_step)[R] = (unsigned long long)s.generated;
       all_greedy = all_greedy && s.temperature <= 0.f;
-      owners.push_back(i);
       R++;
     }
   }
