@@ -1072,8 +1072,26 @@ int Engine::decode(int n, const int *slots, uint32_t *out_tokens, int *out_finis
     max_ctx_b = std::max(max_ctx_b, s.len + 1);
     live.push_back(i);
   }
-  const int T = (int)live.size();
-  if (T == 0) { last_rows = 0; return DIS_OK; }
+  const int T_live = (int)live.size();
+  if (T_live == 0) { last_rows = 0; return DIS_OK; }
+  // One CUDA graph exists per (rows, attention splits): a batch that drains one sequence at a time would capture a new
+  // graph at every size.  Above 8 rows the step is padded to the next multiple of 8 with copies of the last live row
+  // (same slot, token and position: the copies recompute and rewrite exactly the same K/V row and their tokens are
+  // ignored), so at most max_batch / 8 + 8 sizes are ever captured.
+  int T = T_live;
+  if (T > 8 && !(cfg.flags & DIS_FLAG_NO_GRAPH) && !profiling) T = std::min((T + 7) / 8 * 8, max_batch);
+  for (int r = T_live; r < T; r++) {
+    const int q = T_live - 1;
+    cur_meta->h<uint32_t>(cur_meta->o_tokens)[r] = cur_meta->h<uint32_t>(cur_meta->o_tokens)[q];
+    cur_meta->h<int>(cur_meta->o_pos)[r] = cur_meta->h<int>(cur_meta->o_pos)[q];
+    cur_meta->h<int>(cur_meta->o_ptrow)[r] = cur_meta->h<int>(cur_meta->o_ptrow)[q];
+    cur_meta->h<int>(cur_meta->o_ctx)[r] = cur_meta->h<int>(cur_meta->o_ctx)[q];
+    cur_meta->h<int>(cur_meta->o_rowmap)[r] = r;
+    cur_meta->h<float>(cur_meta->o_temp)[r] = cur_meta->h<float>(cur_meta->o_temp)[q];
+    cur_meta->h<float>(cur_meta->o_topp)[r] = cur_meta->h<float>(cur_meta->o_topp)[q];
+    cur_meta->h<unsigned long long>(cur_meta->o_seed)[r] = cur_meta->h<unsigned long long>(cur_meta->o_seed)[q];
+    cur_meta->h<unsigned long long>(cur_meta->o_step)[r] = cur_meta->h<unsigned long long>(cur_meta->o_step)[q];
+  }
   const int n_splits = pick_attn_splits(T, max_ctx_b);
   last_T = T;
   rowmap_identity = true;
@@ -1116,8 +1134,8 @@ int Engine::decode(int n, const int *slots, uint32_t *out_tokens, int *out_finis
   float ms = 0.f;
   ENG_CUDA(cudaEventElapsedTime(&ms, ev0, ev1));
   last_step_ms = ms;
-  last_rows = T;
-  for (int r = 0; r < T; r++) {
+  last_rows = T_live;
+  for (int r = 0; r < T_live; r++) {
     const int i = live[(size_t)r];
     Sequence &s = seqs[(size_t)slots[i]];
     s.len += 1;  // the consumed token is now in the cache

@@ -87,7 +87,7 @@ __global__ void __launch_bounds__(kAttnThreads, 2)
 attn_paged_kernel(const __grid_constant__ CUtensorMap kv_map, long long row0, const AttnRope rope, const uint16_t *__restrict__ q,
                   const int *__restrict__ page_table, int max_pages, const int *__restrict__ pt_row,
                   const int *__restrict__ ctx_len, uint16_t *__restrict__ out, float *__restrict__ scratch,
-                  int n_splits, int T, int n_heads, int n_kv, int page_shift, int n_stages, int full_ring) {
+                  int n_splits, int T, int n_heads, int n_kv, int page_shift, int n_stages) {
   using Cfg = AttnCfg<D>;
   constexpr int KS = D / 16;  // k-steps of the QK^T MMA
   constexpr int NT = D / 8;   // n-tiles of the P.V MMA
@@ -146,12 +146,11 @@ attn_paged_kernel(const __grid_constant__ CUtensorMap kv_map, long long row0, co
     }
   };
 
-  // full_ring: every stage is filled up front -- nothing consumes a tile before the RoPE prologue below is over, so the
-  // whole ring can be in flight across griddepcontrol.wait; otherwise (round 1) one stage is kept back for the refill
-  // at the top of iteration 0
-  const int ahead = full_ring ? n_stages : n_stages - 1;
+  // One stage is kept back for the refill at the top of iteration 0.  Filling the whole ring up front (nothing consumes a
+  // tile before the RoPE prologue is over) was measured in round 2: 3.491 / 3.495 against 3.531 / 3.479 ms per step at
+  // batch 32, 4.269 against 4.253 at batch 64 -- no gain, not kept.
   if (threadIdx.x == 0) {
-    for (int s = 0; s < ahead; s++)
+    for (int s = 0; s < n_stages - 1; s++)
       if (s < n_tiles) load_tile(s, s);
   }
 
@@ -219,8 +218,8 @@ attn_paged_kernel(const __grid_constant__ CUtensorMap kv_map, long long row0, co
   const int wtok = warp * 16;  // this warp's token slice inside a tile
   for (int tile = 0; tile < n_tiles; tile++) {
     __syncthreads();  // everyone is done with the stage consumed last iteration
-    if (threadIdx.x == 0 && (!full_ring || tile >= 1)) {  // full_ring: the stage consumed in iteration tile - 1 is free now
-      const int nt = tile + ahead - (full_ring ? 1 : 0);
+    if (threadIdx.x == 0) {
+      const int nt = tile + n_stages - 1;
       if (nt < n_tiles) load_tile(nt, nt % n_stages);
     }
     const int stage = tile % n_stages;
@@ -559,12 +558,10 @@ static cudaError_t attn_launch(const TmaMap &kv_map, long long row0, const AttnR
     stages = e ? atoi(e) : AttnCfg<D>::kStages;
     stages = stages < 2 ? 2 : (stages > AttnCfg<D>::kStages ? AttnCfg<D>::kStages : stages);
   }
-  static int full_ring = -1;
-  if (full_ring < 0) { const char *e = getenv("DIS_ATTN_FULL_RING"); full_ring = (e && atoi(e) == 0) ? 0 : 1; }
   const int smem = stages * AttnCfg<D>::kStageBytes + 1024 + 64;
   DIS_CUDA_TRY(launch_k(attn_paged_kernel<D, G>, grid, dim3(kAttnThreads), (size_t)smem, st,
                         *reinterpret_cast<const CUtensorMap *>(&kv_map), row0, rope, q, page_table, max_pages, pt_row, ctx, out,
-                        scratch, n_splits, T, n_heads, n_kv, page_shift, stages, full_ring));
+                        scratch, n_splits, T, n_heads, n_kv, page_shift, stages));
   if (n_splits > 1)
     DIS_CUDA_TRY(launch_k(attn_combine_kernel<D>, dim3(n_heads, T), dim3(D), 0, st, (const float *)scratch, out, n_splits, T, n_heads));
   return cudaSuccess;
