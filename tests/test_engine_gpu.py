@@ -398,3 +398,34 @@ def test_sampling_reproducible_and_close_to_oracle():
         assert abs(lps[step] - want_lp) <= 1e-3 * max(1.0, abs(want_lp)), (step, lps[step], want_lp)
     assert off <= 1, off
     e.close()
+
+
+def test_decode_batch_padded_to_graph_bucket_changes_nothing():
+    """Above 8 rows a decode step is padded to the next multiple of 8 with copies of its last row, so that the CUDA-graph
+    cache holds a few sizes instead of one per batch size.  13 running sequences (padded to 16) must produce exactly the
+    tokens and logits of the eager engine, which does not pad, and the oracle's tokens; afterwards 5 of them are dropped
+    (8 rows: no padding) and the rest go on unchanged."""
+    shape = O.ModelShape(2048, 512, 3, 8, 2, 64, 1408, 512)
+    rng = np.random.default_rng(21)
+    prompts = [rng.integers(0, shape.vocab, int(n)).tolist() for n in rng.integers(3, 70, 13)]
+    outs = []
+    for flags in (0, B.FLAG_NO_GRAPH):
+        e = make_engine(shape, seed=77, flags=flags, max_batch=16, kv_pages=160)
+        P = InferenceParams(max_tokens=40, temperature=0.0)
+        slots = [e.seq_add(p, P) for p in prompts]
+        toks = [list(map(int, e.prefill(slots)[0]))]
+        logits = []
+        for _ in range(6):
+            toks.append(list(map(int, e.decode(slots)[0])))
+            logits.append(e.last_logits(len(slots)))
+        for s in slots[8:]:
+            e.seq_remove(s)
+        for _ in range(4):
+            toks.append(list(map(int, e.decode(slots[:8])[0])) + [None] * 5)
+        outs.append((toks, logits))
+        e.close()
+    assert outs[0][0] == outs[1][0]
+    assert all(np.array_equal(a, b) for a, b in zip(outs[0][1], outs[1][1]))
+    mimic = O.Oracle(shape, act_round=True); mimic.fill_synthetic(77, True)
+    got = [[step[b] for step in outs[0][0][:7]] for b in range(13)]
+    assert_greedy_matches(got, mimic, prompts, 7, "bucket-padded")
