@@ -305,7 +305,7 @@ int Engine::tp_import(const uint8_t *handles) {
       peers_big.flags[r] = reinterpret_cast<uint32_t *>(base + (size_t)4 * ar_cap_big * m.hidden * sizeof(float));
     }
     peers_big.cap_rows = ar_cap_big;
-    peers_big.two_shot = 1;
+    peers_big.two_shot = getenv("DIS_TP_PREFILL_ROWKERNEL") && atoi(getenv("DIS_TP_PREFILL_ROWKERNEL")) ? 1 : 4;
   }
   // one-shot (tp-1)*T*H*4 bytes and one flag hop, or two-shot 2*(tp-1)/tp*T*H*4 bytes and two hops
   // measured at batch 64, H = 4096, ms per step (one-shot / fenced two-shot / flag-in-data two-shot):

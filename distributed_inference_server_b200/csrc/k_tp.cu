@@ -464,6 +464,109 @@ static bool tp_wide_fits(const TpPeers &peers, int T, int H) {
   return (long long)T * peers.tp <= (long long)per_sm * sms;
 }
 
+// Streaming variant for prefill-sized passes (two_shot == 4): the exchange of thousands of rows is bandwidth-bound, so
+// instead of one CTA per row with two release fences each (an NVLink round trip per fence: 8192 rows cost 451 ms of TTFT
+// against NCCL's 323 at TP=2), a grid of resident CTAs -- one 1024-thread CTA per SM -- each takes every G-th row and goes through the
+// two-shot schedule ONCE for all of its rows:
+//   phase A  for each of its rows: sum the split-K slices, store each column block into its owner's RS area (plain
+//            16-byte stores over NVLink; the own block into the local RS area); then ONE barrier + release flag per peer
+//   phase B  wait for the peers' phase-A flags of the same CTA index (every rank walks the same rows in the same CTA);
+//            for each row: the tp contributions of the own block IN RANK ORDER + residual -> x, and into every peer's
+//            AG area; then one barrier + release flag per peer
+//   phase C  wait for the phase-B flags; for each row: the finished blocks out of the AG area, x, RMSNorm -> bf16.
+// Bytes on the wire 2 (tp-1)/tp * T*H*4 as in the fenced two-shot kernel, the same additions in the same order (bit-
+// identical to it), two flag flights per CTA instead of per row.  Flags: peers.flags[rank][phase][parity][source][CTA].
+__global__ void __launch_bounds__(1024, 1)
+tp_add_rmsnorm_stream_kernel(TpPeers peers, float *__restrict__ x, const float *__restrict__ partial, int n_partial,
+                             long long partial_stride, const float *__restrict__ gain, uint16_t *__restrict__ xn,
+                             const uint32_t *__restrict__ step_ptr, uint32_t idx, int parity, int T, int H, float eps) {
+  __shared__ float red[32];
+  pdl_launch_dependents();
+  pdl_wait();
+  const uint32_t epoch = *step_ptr * 256u + idx;
+  const int me = peers.rank, tp = peers.tp, cap = peers.cap_rows;
+  const int Hs = H / tp, G = (int)gridDim.x, c = (int)blockIdx.x;
+  const size_t ag_base = (size_t)2 * cap * H;
+  auto rs_slot = [&](int src, int t) { return (((size_t)parity * tp + src) * cap + t) * (size_t)Hs; };
+  auto flag_at = [&](int phase, int src) { return (((size_t)phase * 2 + parity) * tp + src) * (size_t)cap + c; };
+  const int step = blockDim.x * 4;
+
+  // ---- phase A
+  for (int t = c; t < T; t += G) {
+    for (int i = threadIdx.x * 4; i < H; i += step) {
+      float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+      const float *pp = partial + (size_t)t * H + i;
+#pragma unroll 4
+      for (int s = 0; s < n_partial; s++) {
+        const float4 p = *reinterpret_cast<const float4 *>(pp + (size_t)s * partial_stride);
+        v.x += p.x; v.y += p.y; v.z += p.z; v.w += p.w;
+      }
+      const int owner = i / Hs;
+      *reinterpret_cast<float4 *>(peers.data[owner] + rs_slot(me, t) + (i - owner * Hs)) = v;  // NVLink store unless owner == me
+    }
+  }
+  __syncthreads();  // the release below is cumulative over the stores the barrier ordered before it
+  if ((int)threadIdx.x < tp && (int)threadIdx.x != me) {
+    st_release_sys(peers.flags[threadIdx.x] + flag_at(0, me), epoch);
+    wait_flag_sys(peers.flags[me] + flag_at(0, threadIdx.x), epoch);
+  }
+  __syncthreads();
+  // ---- phase B: (row, 4 columns of the own block) items over all threads
+  {
+    const int per_row = Hs / 4;
+    const int rows_here = c < T ? (T - 1 - c) / G + 1 : 0;
+    for (int item = threadIdx.x; item < rows_here * per_row; item += blockDim.x) {
+      const int t = c + (item / per_row) * G, j = (item % per_row) * 4;
+      float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
+      for (int r = 0; r < tp; r++) {
+        const float4 v = ld_volatile_f4(peers.data[me] + rs_slot(r, t) + j);
+        a.x += v.x; a.y += v.y; a.z += v.z; a.w += v.w;
+      }
+      float *xp = x + (size_t)t * H + me * Hs + j;
+      const float4 xv = *reinterpret_cast<const float4 *>(xp);
+      a.x += xv.x; a.y += xv.y; a.z += xv.z; a.w += xv.w;
+      *reinterpret_cast<float4 *>(xp) = a;
+      for (int r = 0; r < tp; r++)
+        if (r != me) *reinterpret_cast<float4 *>(peers.data[r] + ag_base + rs_slot(me, t) + j) = a;  // NVLink store
+    }
+  }
+  __syncthreads();
+  if ((int)threadIdx.x < tp && (int)threadIdx.x != me) {
+    st_release_sys(peers.flags[threadIdx.x] + flag_at(1, me), epoch);
+    wait_flag_sys(peers.flags[me] + flag_at(1, threadIdx.x), epoch);
+  }
+  __syncthreads();
+  // ---- phase C
+  extern __shared__ float row[];  // [H] when a thread owns more than one float4
+  const bool single = H <= step;
+  for (int t = c; t < T; t += G) {
+    float ss = 0.f;
+    float4 keep = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int i = threadIdx.x * 4; i < H; i += step) {
+      const int owner = i / Hs;
+      float4 a;
+      if (owner == me) a = *reinterpret_cast<const float4 *>(x + (size_t)t * H + i);
+      else {
+        a = ld_volatile_f4(peers.data[me] + ag_base + rs_slot(owner, t) + (i - owner * Hs));
+        *reinterpret_cast<float4 *>(x + (size_t)t * H + i) = a;
+      }
+      if (single) keep = a; else *reinterpret_cast<float4 *>(row + i) = a;
+      ss = sumsq4(ss, a);
+    }
+    ss = tp_block_sum(ss, red);
+    const float inv = rsqrtf(ss / (float)H + eps);
+    for (int i = threadIdx.x * 4; i < H; i += step) {
+      const float4 v = single ? keep : *reinterpret_cast<const float4 *>(row + i);
+      const float4 g = *reinterpret_cast<const float4 *>(gain + i);
+      uint2 o;
+      o.x = float2_to_bf16x2(v.x * inv * g.x, v.y * inv * g.y);
+      o.y = float2_to_bf16x2(v.z * inv * g.z, v.w * inv * g.w);
+      *reinterpret_cast<uint2 *>(xn + (size_t)t * H + i) = o;
+    }
+    __syncthreads();  // red[] and row[] are reused by the next row
+  }
+}
+
 cudaError_t launch_tp_add_rmsnorm(const TpPeers &peers, float *x, const float *partial, int n_partial,
                                   long long partial_stride, const float *gain, uint16_t *xn, const uint32_t *step_ptr,
                                   uint32_t idx, int parity, int T, int H, float eps, cudaStream_t st) {
@@ -472,6 +575,16 @@ cudaError_t launch_tp_add_rmsnorm(const TpPeers &peers, float *x, const float *p
   if (H % 4 != 0) { set_last_error("tp_add_rmsnorm: H must be a multiple of 4"); return cudaErrorInvalidValue; }
   int threads = (H / 4 + 31) / 32 * 32;
   threads = threads > 1024 ? 1024 : threads;
+  if (peers.two_shot == 4) {
+    if (H % (4 * peers.tp) != 0) { set_last_error("tp_add_rmsnorm: the streaming exchange needs H % (4 * tp) == 0"); return cudaErrorInvalidValue; }
+    int dev = 0, sms = kNumSMs;
+    if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const int grid = T < sms ? T : sms;  // every CTA must be resident: a CTA waits for the same CTA index on its peers
+    const size_t smem4 = H <= threads * 4 ? 0 : (size_t)H * sizeof(float);
+    if (smem4 > 48 * 1024) DIS_CUDA_TRY(cudaFuncSetAttribute(tp_add_rmsnorm_stream_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem4));
+    return launch_k(tp_add_rmsnorm_stream_kernel, dim3(grid), dim3(threads), smem4, st, peers, x, partial, n_partial, partial_stride,
+                    gain, xn, step_ptr, idx, parity, T, H, eps);
+  }
   if (peers.two_shot == 3 && tp_wide_fits(peers, T, H)) {
     return launch_k(tp_add_rmsnorm_wide_kernel, dim3(T, peers.tp), dim3(H / peers.tp / 4), 0, st, peers, x, partial, n_partial,
                     partial_stride, gain, xn, step_ptr, idx, parity, H, eps);

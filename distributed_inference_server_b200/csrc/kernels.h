@@ -43,7 +43,8 @@ struct TpPeers {
   uint32_t *cand_flags[kTpMaxRanks];
   int rank, tp, cap_rows;
   int two_shot;  // 0: one-shot push all-reduce, 1: reduce-scatter + all-gather over column blocks, 2: the same with flag-in-data stores,
-                 // 3: flag-in-data on a (row, column block) grid (falls back to 2 when the grid would not be co-resident)
+                 // 3: flag-in-data on a (row, column block) grid (falls back to 2 when the grid would not be co-resident),
+                 // 4: streaming two-shot for prefill-sized passes (resident CTAs, two flag flights per CTA, fenced layout)
 };
 cudaError_t launch_tp_add_rmsnorm(const TpPeers &peers, float *x, const float *partial, int n_partial,
                                   long long partial_stride, const float *gain, uint16_t *xn, const uint32_t *step_ptr,
