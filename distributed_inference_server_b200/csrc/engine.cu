@@ -242,12 +242,14 @@ int Engine::init(const dis_engine_config *c) {
     const size_t flags_b = align_up((size_t)2 * 2 * tp_size * ar_cap_rows * 4, 256);  // two hops
     const size_t cand_b = align_up((size_t)2 * tp_size * ar_cap_rows * 4 * 4, 256);
     sym_bytes = data_b + flags_b + cand_b + 256;
-    // Prefill-sized passes (more rows than the decode region holds) go through reduce_partials + ncclAllReduce + the norm
-    // kernel.  DIS_TP_PREFILL_FUSED=1 gives them their own region of the symmetric buffer and the fenced two-shot kernel
-    // instead (one kernel, minimum bytes on the wire: 2 (tp-1)/tp * T*H*4) -- parity-green (tests/test_tp_gpu.py) but
-    // measured SLOWER: TTFT of 64 x 512 tokens at TP=2 451 ms against 323 ms with NCCL.  One 1024-thread CTA per row with
-    // two release fences (an NVLink round trip each) moves 296 rows per ~25 us; a bandwidth-bound exchange of 8192 rows
-    // wants a few persistent CTAs streaming many rows each, which this kernel is not.  Kept as an opt-in for that work.
+    // Prefill-sized passes (more rows than the decode region holds) go through ncclAllReduce (reading the projection
+    // output in place when it is one slice) + the norm kernel.  DIS_TP_PREFILL_FUSED=1 gives them their own region of the
+    // symmetric buffer and a fused peer-memory exchange instead (one kernel, 2 (tp-1)/tp * T*H*4 bytes on the wire),
+    // parity-green (tests/test_tp_gpu.py, and bench.py's gate at TP=2 and 8).  Measured, TTFT of 64 x 512 tokens:
+    //   row kernel (one 1024-thread CTA per row, two release fences each)   TP=2 451 ms            NCCL 323
+    //   streaming kernel (one resident CTA per SM, two flag flights in all) TP=2 309 ms  TP=8 189  NCCL 319 / 183
+    // The streaming kernel is at the wire's bandwidth and NCCL (in-switch reduction at 8 ranks) is too: a tie at TP=2, NCCL
+    // ahead at TP=8, so NCCL stays the default for these passes; DIS_TP_PREFILL_ROWKERNEL=1 selects the row kernel.
     if (cap_tokens > ar_cap_rows && m.hidden % (4 * tp_size) == 0 && getenv("DIS_TP_PREFILL_FUSED") && atoi(getenv("DIS_TP_PREFILL_FUSED"))) {
       ar_cap_big = cap_tokens;
       sym_big_off = align_up(sym_bytes, 256);
