@@ -45,6 +45,9 @@ __device__ __forceinline__ float block_max(float v, float *sm) {
 // ------------------------------------------------------------------------------ add_rmsnorm
 // One CTA per row with H/4 threads (<= 1024): every thread owns one float4 column group per pass, so
 // the S split-K slices of a row are fetched with S independent 16-byte loads per thread in flight.
+// Measured and rejected (round 2): fetching the gain (a weight, cold in L2 once per step) BEFORE griddepcontrol.wait to
+// take its latency off the chain wait -> row loads -> reduction -> gain -> store: graph-only step 3.505 / 3.500 ms
+// against 3.492 / 3.491 (alternating runs on one box, profiles/r2_norm_early_gain_*.json) -- not faster.
 __global__ void __launch_bounds__(1024)
 add_rmsnorm_kernel(float *__restrict__ x, const uint32_t *__restrict__ tokens,
                    const uint16_t *__restrict__ embed, const float *__restrict__ partial, int n_partial,
