@@ -32,8 +32,9 @@ def pytest_collection_modifyitems(config, items):
 @pytest.fixture(autouse=True)
 def _release_device_tensors():
     yield
-    try:
-        from tests import _gpu_util
-        _gpu_util._KEEP.clear()
-    except Exception:
-        pass
+    if "tests._gpu_util" not in sys.modules:
+        return
+    _gpu_util = sys.modules["tests._gpu_util"]
+    bad = _gpu_util.check_guards()  # guard bands around every device buffer a kernel test handed to the C ABI
+    _gpu_util._KEEP.clear()
+    assert not bad, "a kernel wrote outside a buffer it was given: " + "; ".join(bad)

@@ -9,6 +9,7 @@ import pytest
 import torch
 
 from oracle import oracle as O
+from tests import _gpu_util as G
 from tests._gpu_util import (DEV, check, dev_bf16, dev_f32, dev_i32, host, lib, ptr, rand_bf16, sync)
 
 pytestmark = pytest.mark.gpu
@@ -22,7 +23,7 @@ def test_synth_bits_match_oracle():
         amp, off = C.c_float(), C.c_float()
         cfg = shape.c()
         O.lib().orc_synth_params(C.byref(cfg), kind, C.byref(amp), C.byref(off))
-        out = torch.empty(ref.size, dtype=torch.bfloat16, device=DEV)
+        out = G.empty(ref.size, dtype=torch.bfloat16, device=DEV)
         check(lib().dis_k_synth_bf16(ptr(out), ref.size, 99, kind, layer if kind in O.PER_LAYER else 0, amp.value,
                                      off.value, None))
         sync()
@@ -36,7 +37,7 @@ def test_add_rmsnorm(T, H):
     parts = rng.standard_normal((3, T, H)).astype(np.float32)
     gain = O.bf16_round(1 + 0.1 * rng.standard_normal(H).astype(np.float32))
     dx, dp, dg = dev_f32(x), dev_f32(parts), dev_f32(gain)
-    xn = torch.empty((T, H), dtype=torch.bfloat16, device=DEV)
+    xn = G.empty((T, H), dtype=torch.bfloat16, device=DEV)
     check(lib().dis_k_add_rmsnorm(ptr(dx), None, None, ptr(dp), 3, T * H, ptr(dg), ptr(xn), None, T, H, 1e-5, None))
     sync()
     xs = x + parts.sum(0)
@@ -51,8 +52,8 @@ def test_add_rmsnorm_embedding_and_rowmap():
     emb = rand_bf16(rng, (V, H), 0.02)
     toks = rng.integers(0, V, T).astype(np.uint32)
     gain = np.ones(H, np.float32)
-    dx = torch.zeros((T, H), dtype=torch.float32, device=DEV)
-    xn = torch.empty((T, H), dtype=torch.bfloat16, device=DEV)
+    dx = G.zeros((T, H), dtype=torch.float32, device=DEV)
+    xn = G.empty((T, H), dtype=torch.bfloat16, device=DEV)
     dt = torch.from_numpy(toks.astype(np.int64)).to(DEV).to(torch.int32)
     check(lib().dis_k_add_rmsnorm(ptr(dx), ptr(dt), ptr(dev_bf16(emb)), None, 0, 0, ptr(dev_f32(gain)), ptr(xn), None,
                                   T, H, 1e-5, None))
@@ -62,7 +63,7 @@ def test_add_rmsnorm_embedding_and_rowmap():
     assert np.abs(host(xn) - ref).max() <= BF16_ULP * np.abs(ref).max() * 1.01
     # row_map: compact rows, x untouched
     rows = np.array([8, 2, 5], np.int32)
-    xn2 = torch.empty((3, H), dtype=torch.bfloat16, device=DEV)
+    xn2 = G.empty((3, H), dtype=torch.bfloat16, device=DEV)
     before = host(dx).copy()
     check(lib().dis_k_add_rmsnorm(ptr(dx), None, None, None, 0, 0, ptr(dev_f32(gain)), ptr(xn2), ptr(dev_i32(rows)), 3,
                                   H, 1e-5, None))
@@ -103,7 +104,7 @@ def test_gemm_full_size_against_torch(T, N, K, silu):
     X = (torch.randn((T, K), device=DEV, generator=g)).to(torch.bfloat16)
     W = (torch.randn(((2 if silu else 1) * N, K), device=DEV, generator=g) * 0.02).to(torch.bfloat16)
     if silu:
-        act = torch.empty((T, N), dtype=torch.bfloat16, device=DEV)
+        act = G.empty((T, N), dtype=torch.bfloat16, device=DEV)
         check(lib().dis_k_gemm_silu(ptr(X), ptr(W), ptr(act), T, N, K, None))
         sync()
         gate, up = X.float() @ W[:N].float().T, X.float() @ W[N:].float().T
@@ -122,7 +123,7 @@ def test_gemm_full_size_against_torch(T, N, K, silu):
 
 def test_gemm_rejects_empty_split():
     X, W = dev_bf16(np.zeros((8, 576), np.float32)), dev_bf16(np.zeros((128, 576), np.float32))
-    out = torch.zeros((4, 8, 128), dtype=torch.float32, device=DEV)
+    out = G.zeros((4, 8, 128), dtype=torch.float32, device=DEV)
     assert lib().dis_k_gemm(ptr(X), ptr(W), ptr(out), 8, 128, 576, 4, None) != 0  # 9 k-blocks / 4 -> empty slice
 
 
@@ -132,7 +133,7 @@ def test_gemm_silu(T, I, K):
     rng = np.random.default_rng(T + I + K)
     X, Wgu = rand_bf16(rng, (T, K)), rand_bf16(rng, (2 * I, K), 0.05)
     ref = O.silu_mul(O.linear(X, Wgu[:I]), O.linear(X, Wgu[I:]), round_out=False)
-    act = torch.empty((T, I), dtype=torch.bfloat16, device=DEV)
+    act = G.empty((T, I), dtype=torch.bfloat16, device=DEV)
     check(lib().dis_k_gemm_silu(ptr(dev_bf16(X)), ptr(dev_bf16(Wgu)), ptr(act), T, I, K, None))
     sync()
     assert np.abs(host(act) - ref).max() <= BF16_ULP * np.abs(ref).max() * 1.05 + 1e-6
@@ -145,13 +146,13 @@ def test_gemv(T, N, K):
     rng = np.random.default_rng(T + N + K)
     X, W = rand_bf16(rng, (T, K)), rand_bf16(rng, (N, K), 0.05)
     ref = O.linear(X, W)
-    out = torch.empty((T, N), dtype=torch.float32, device=DEV)
+    out = G.empty((T, N), dtype=torch.float32, device=DEV)
     check(lib().dis_k_gemv(ptr(dev_bf16(X)), ptr(dev_bf16(W)), ptr(out), T, N, K, None))
     sync()
     assert np.abs(host(out) - ref).max() <= 1e-4 * np.abs(ref).max() + 1e-6
     Wgu = rand_bf16(rng, (2 * N, K), 0.05)
     refs = O.silu_mul(O.linear(X, Wgu[:N]), O.linear(X, Wgu[N:]))
-    act = torch.empty((T, N), dtype=torch.bfloat16, device=DEV)
+    act = G.empty((T, N), dtype=torch.bfloat16, device=DEV)
     check(lib().dis_k_gemv_silu(ptr(dev_bf16(X)), ptr(dev_bf16(Wgu)), ptr(act), T, N, K, None))
     sync()
     assert np.abs(host(act) - refs).max() <= BF16_ULP * np.abs(refs).max() * 1.05 + 1e-6
@@ -177,7 +178,7 @@ def test_rope_kv_write_and_attention(d, nh, nkv):
     pt, max_pages = _paged_setup(rng, n_seq, ctx_lens, nkv, d, page_size, n_pages)
     cs, sn = O.rope_table(max_ctx, d, 500000.0)
     nq, nk = nh * d, nkv * d
-    pool = torch.zeros((n_pages, 2, nkv, page_size, d), dtype=torch.bfloat16, device=DEV)
+    pool = G.zeros((n_pages, 2, nkv, page_size, d), dtype=torch.bfloat16, device=DEV)
     dpt = dev_i32(pt)
     K_hist = [np.zeros((c, nk), np.float32) for c in ctx_lens]
     V_hist = [np.zeros((c, nk), np.float32) for c in ctx_lens]
@@ -193,7 +194,7 @@ def test_rope_kv_write_and_attention(d, nh, nkv):
         summed = part[0] + part[1]
         pos = np.array([p for _, p in chunk], np.int32)
         row = np.array([s for s, _ in chunk], np.int32)
-        dq = torch.empty((T, nq), dtype=torch.bfloat16, device=DEV)
+        dq = G.empty((T, nq), dtype=torch.bfloat16, device=DEV)
         check(lib().dis_k_rope_kv_write(ptr(dev_f32(part)), 2, T * (nq + 2 * nk), ptr(dq), ptr(pool), ptr(dpt), max_pages,
                                         ptr(dev_i32(row)), ptr(dev_i32(pos)), ptr(dev_f32(cs)), ptr(dev_f32(sn)), T, nh,
                                         nkv, d, page_size, None))
@@ -220,9 +221,9 @@ def test_rope_kv_write_and_attention(d, nh, nkv):
     dq = dev_bf16(q_last)
     ref = np.stack([O.attention_one(q_last[s], K_hist[s], V_hist[s], nh, nkv, d) for s in range(n_seq)])
     for splits in (1, 3, 8):
-        out = torch.empty((n_seq, nq), dtype=torch.bfloat16, device=DEV)
+        out = G.empty((n_seq, nq), dtype=torch.bfloat16, device=DEV)
         n_scr = lib().dis_k_attn_scratch_elems(n_seq, nh, d, splits)
-        scr = torch.empty(max(n_scr, 1), dtype=torch.float32, device=DEV)
+        scr = G.empty(max(n_scr, 1), dtype=torch.float32, device=DEV)
         check(lib().dis_k_attn_paged(ptr(dq), ptr(pool), n_pages, ptr(dpt), max_pages, ptr(dev_i32(np.arange(n_seq))),
                                      ptr(dev_i32(ctx_lens)), ptr(out), ptr(scr), splits, n_seq, nh, nkv, d, page_size, None))
         sync()
@@ -249,7 +250,7 @@ def test_attention_full_size_against_torch():
     pool = torch.randn((n_pages, 2, nkv, ps, d), device=DEV, generator=g).to(torch.bfloat16)
     q = torch.randn((B, nh * d), device=DEV, generator=g).to(torch.bfloat16)
     dpt, dctx, drow = dev_i32(pt), dev_i32(ctx), dev_i32(np.arange(B))
-    ref = torch.empty((B, nh, d), dtype=torch.float32, device=DEV)
+    ref = G.empty((B, nh, d), dtype=torch.float32, device=DEV)
     for b in range(B):
         pages = torch.as_tensor(pt[b, :pages_per[b]].astype(np.int64), device=DEV)
         kv = pool[pages].float()                                   # [pages, 2, nkv, ps, d]
@@ -259,8 +260,8 @@ def test_attention_full_size_against_torch():
         p = torch.softmax(qb @ K.transpose(1, 2) / d ** 0.5, dim=-1)
         ref[b] = (p @ V).reshape(nh, d)
     for splits in (1, 4):
-        out = torch.empty((B, nh * d), dtype=torch.bfloat16, device=DEV)
-        scr = torch.empty(max(lib().dis_k_attn_scratch_elems(B, nh, d, splits), 1), dtype=torch.float32, device=DEV)
+        out = G.empty((B, nh * d), dtype=torch.bfloat16, device=DEV)
+        scr = G.empty(max(lib().dis_k_attn_scratch_elems(B, nh, d, splits), 1), dtype=torch.float32, device=DEV)
         check(lib().dis_k_attn_paged(ptr(q), ptr(pool), n_pages, ptr(dpt), max_pages, ptr(drow), ptr(dctx), ptr(out), ptr(scr),
                                      splits, B, nh, nkv, d, ps, None))
         sync()
@@ -284,8 +285,8 @@ def test_attention_long_context_tiles():
     ref = O.attention_one(q[0], K, V, nh, nkv, d)
     dpool = dev_bf16(pool)
     for splits in (1, 2, 5):
-        out = torch.empty((1, nh * d), dtype=torch.bfloat16, device=DEV)
-        scr = torch.empty(max(lib().dis_k_attn_scratch_elems(1, nh, d, splits), 1), dtype=torch.float32, device=DEV)
+        out = G.empty((1, nh * d), dtype=torch.bfloat16, device=DEV)
+        scr = G.empty(max(lib().dis_k_attn_scratch_elems(1, nh, d, splits), 1), dtype=torch.float32, device=DEV)
         check(lib().dis_k_attn_paged(ptr(dev_bf16(q)), ptr(dpool), n_pages, ptr(dev_i32(pt)), max_pages, ptr(dev_i32([0])),
                                      ptr(dev_i32([ctx])), ptr(out), ptr(scr), splits, 1, nh, nkv, d, page_size, None))
         sync()
@@ -329,7 +330,7 @@ def test_attention_prefill_blocks(d, nh, nkv, page_size, short_blocks):
                 ref.append(O.attention_one(Q[s][p0 + i], K[s][:p0 + i + 1], V[s][:p0 + i + 1], nh, nkv, d))
             t += ln
     q_flat, ref = np.stack(q_flat), np.stack(ref)
-    out = torch.empty((t, nh * d), dtype=torch.bfloat16, device=DEV)
+    out = G.empty((t, nh * d), dtype=torch.bfloat16, device=DEV)
     check(lib().dis_k_attn_prefill(ptr(dev_bf16(q_flat)), ptr(dev_bf16(pool)), n_pages, ptr(dev_i32(pt)), max_pages,
                                    ptr(dev_i32(tok0)), ptr(dev_i32(qlen)), ptr(dev_i32(pos0)), ptr(dev_i32(ptrow)), ptr(out),
                                    len(tok0), nh, nkv, d, page_size, None))
@@ -360,7 +361,7 @@ def test_attention_prefill_full_size_against_torch():
             ln = min(BT, lens[s] - p0)
             tok0.append(t); qlen.append(ln); pos0.append(p0); ptrow.append(s); t += ln
     q = torch.randn((t, nh * d), device=DEV, generator=g).to(torch.bfloat16)
-    out = torch.empty((t, nh * d), dtype=torch.bfloat16, device=DEV)
+    out = G.empty((t, nh * d), dtype=torch.bfloat16, device=DEV)
     check(lib().dis_k_attn_prefill(ptr(q), ptr(pool), n_pages, ptr(dev_i32(pt)), max_pages, ptr(dev_i32(tok0)), ptr(dev_i32(qlen)),
                                    ptr(dev_i32(pos0)), ptr(dev_i32(ptrow)), ptr(out), len(tok0), nh, nkv, d, ps, None))
     sync()
@@ -390,8 +391,8 @@ def test_sampler_argmax_and_ties():
     lg[1, [500, 90000]] = 9.0      # tie -> lowest index
     lg[2, V - 1] = 11.0            # last element
     lg[3, 0] = 11.0                # first element
-    out = torch.zeros(T, dtype=torch.int32, device=DEV)
-    lp = torch.zeros(T, dtype=torch.float32, device=DEV)
+    out = G.zeros(T, dtype=torch.int32, device=DEV)
+    lp = G.zeros(T, dtype=torch.float32, device=DEV)
     check(lib().dis_k_sample(ptr(dev_f32(lg)), V, T, V, None, None, None, None, ptr(out), ptr(lp), None))
     sync()
     ref = [O.argmax(lg[t])[0] for t in range(T)]
@@ -411,10 +412,10 @@ def test_sampler_top_p_matches_oracle(T, V):
     tps = rng.choice([0.1, 0.5, 0.9, 0.95, 1.0], T).astype(np.float32)
     seeds = rng.integers(0, 2 ** 40, T).astype(np.uint64)
     steps = rng.integers(0, 100, T).astype(np.uint64)
-    out = torch.zeros(T, dtype=torch.int32, device=DEV)
+    out = G.zeros(T, dtype=torch.int32, device=DEV)
     ds = torch.from_numpy(seeds.view(np.int64)).to(DEV)
     dst = torch.from_numpy(steps.view(np.int64)).to(DEV)
-    lp = torch.zeros(T, dtype=torch.float32, device=DEV)
+    lp = G.zeros(T, dtype=torch.float32, device=DEV)
     check(lib().dis_k_sample(ptr(dev_f32(lg)), V, T, V, ptr(dev_f32(temps)), ptr(dev_f32(tps)), ptr(ds), ptr(dst), ptr(out), ptr(lp), None))
     sync()
     got = out.cpu().tolist()

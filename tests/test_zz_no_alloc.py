@@ -10,6 +10,7 @@ import torch
 
 from distributed_inference_server_b200 import binding as B
 from oracle import oracle as O
+from tests import _gpu_util as G
 from tests._gpu_util import DEV, check, dev_bf16, dev_i32, host, lib, ptr, rand_bf16, sync
 
 pytestmark = pytest.mark.gpu
@@ -50,10 +51,11 @@ def _oracle_attention(a):
 
 
 def _run_both(a):
-    want = torch.empty((a["T"], a["nh"] * a["d"]), dtype=torch.bfloat16, device=DEV)
-    got = torch.full_like(want, float("nan"))
+    want = G.empty((a["T"], a["nh"] * a["d"]), dtype=torch.bfloat16, device=DEV)
+    got = G.empty(want.shape, dtype=torch.bfloat16, device=DEV)
+    got.fill_(float("nan"))
     n = lib().dis_k_attn_scratch_elems(a["T"], a["nh"], a["d"], a["splits"])
-    scr = torch.empty(max(n, 1), dtype=torch.float32, device=DEV)
+    scr = G.empty(max(n, 1), dtype=torch.float32, device=DEV)
     check(lib().dis_k_attn_paged(ptr(a["q"]), ptr(a["pool"]), a["n_pages"], ptr(a["pt"]), a["max_pages"], ptr(a["row"]),
                                  ptr(a["ctx"]), ptr(want), ptr(scr), a["splits"], a["T"], a["nh"], a["nkv"], a["d"], a["ps"], None))
     check(lib().dis_k_attn_paged_static(ptr(a["q"]), ptr(a["pool"]), a["n_pages"], ptr(a["pt"]), a["max_pages"], ptr(a["row"]),
@@ -80,7 +82,7 @@ def test_static_scratch_matches_caller_scratch_twice_in_a_row():
 def test_static_scratch_allocates_nothing_and_refuses_oversize():
     a = _case(3, 128, 8, 2, 16, [90, 300], splits=3)
     _run_both(a)                                                   # first call on the device: symbol lookup done
-    out = torch.empty((a["T"], a["nh"] * a["d"]), dtype=torch.bfloat16, device=DEV)
+    out = G.empty((a["T"], a["nh"] * a["d"]), dtype=torch.bfloat16, device=DEV)
     sync()
     free_before, _ = torch.cuda.mem_get_info()
     check(lib().dis_k_attn_paged_static(ptr(a["q"]), ptr(a["pool"]), a["n_pages"], ptr(a["pt"]), a["max_pages"], ptr(a["row"]),
