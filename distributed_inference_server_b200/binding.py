@@ -138,6 +138,8 @@ PROTOTYPES = {
     "dis_k_attn_prefill": (C.c_int, [vp, vp, C.c_int64, vp, C.c_int32, vp, vp, vp, vp, vp, C.c_int32, C.c_int32, C.c_int32,
                                      C.c_int32, C.c_int32, vp]),
     "dis_k_attn_prefill_block_tokens": (C.c_int, [C.c_int32, C.c_int32, C.c_int32]),
+    "dis_k_sample_vocab_parallel_area_bytes": (C.c_size_t, [C.c_int32, C.c_int32]),
+    "dis_k_sample_vocab_parallel": (C.c_int, [vp, C.c_int32, C.c_int32, C.c_int32, vp, vp, vp, vp, C.c_uint32, vp, C.c_int32, vp, vp, vp]),
     "dis_k_sample": (C.c_int, [vp, C.c_int64, C.c_int32, C.c_int32, vp, vp, vp, vp, vp, vp, vp]),
     "dis_k_synth_bf16": (C.c_int, [vp, C.c_size_t, C.c_uint64, C.c_int32, C.c_int32, C.c_float, C.c_float, vp]),
 }

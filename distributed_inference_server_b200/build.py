@@ -11,7 +11,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OBJ = os.path.join(CSRC, "_build")
 LIB = os.path.join(HERE, "libdis_engine.so")
-SOURCES = ["k_elementwise.cu", "k_gemv.cu", "k_attn_paged.cu", "k_attn_prefill_tc.cu", "k_gemm_tcgen05.cu", "k_gemm_persist.cu", "k_tp.cu", "engine.cu", "api.cpp",
+SOURCES = ["k_elementwise.cu", "k_gemv.cu", "k_attn_paged.cu", "k_attn_prefill_tc.cu", "k_gemm_tcgen05.cu", "k_gemm_persist.cu", "k_tp.cu", "k_tp_sample.cu", "engine.cu", "api.cpp",
            "tp.cpp", "worker.cpp", "serving.cpp", "prefix.cpp"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-Xcompiler", "-fPIC",

@@ -242,6 +242,26 @@ int dis_k_sample(const float *logits, int64_t ld, int32_t T, int32_t V, const fl
                                   reinterpret_cast<const unsigned long long *>(steps), out_tokens, 0, nullptr, nullptr,
                                   out_logprob, (cudaStream_t)stream));
 }
+size_t dis_k_sample_vocab_parallel_area_bytes(int32_t tp, int32_t rows) {
+  return tp > 0 && rows > 0 ? dis::tp_sample_area_bytes(tp, rows) : 0;
+}
+int dis_k_sample_vocab_parallel(const float *logits, int32_t T, int32_t V, int32_t tp, const float *temperature,
+                                const float *top_p, const uint64_t *seeds, const uint64_t *steps, uint32_t call_no,
+                                void *area, int32_t area_rows, uint32_t *out_tokens, float *out_logprob, void *stream) {
+  if (int rc = need_gpu()) return rc;
+  if (!logits || !area || !out_tokens || tp < 1 || tp > dis::kTpMaxRanks || V <= 0 || V % tp != 0) {
+    dis::set_last_error("sample_vocab_parallel: 1 <= tp <= 8, the vocabulary a multiple of tp, logits / area / out_tokens set");
+    return DIS_ERR_INVALID_ARGUMENT;
+  }
+  dis::TpSampPeers sp{};
+  for (int r = 0; r < tp; r++) sp.buf[r] = static_cast<uint32_t *>(area) + (size_t)r * (dis::tp_sample_area_bytes(tp, area_rows) / 4);
+  sp.rank = -1;  // every rank is a slice of this grid
+  sp.tp = tp;
+  sp.cap_rows = area_rows;
+  return k_ret(dis::launch_tp_sample(sp, logits, V, T, V / tp, temperature, top_p, reinterpret_cast<const unsigned long long *>(seeds),
+                                     reinterpret_cast<const unsigned long long *>(steps), nullptr, call_no, out_tokens, out_logprob,
+                                     (cudaStream_t)stream));
+}
 int dis_k_synth_bf16(uint16_t *dst, size_t n, uint64_t seed, int32_t kind, int32_t layer, float amp, float offset,
                      void *stream) {
   if (int rc = need_gpu()) return rc;

@@ -241,7 +241,9 @@ int Engine::init(const dis_engine_config *c) {
     const size_t data_b = (size_t)std::max(2 * tp_size, 8) * ar_cap_rows * m.hidden * sizeof(float);  // 8: flag-in-data two-shot areas
     const size_t flags_b = align_up((size_t)2 * 2 * tp_size * ar_cap_rows * 4, 256);  // two hops
     const size_t cand_b = align_up((size_t)2 * tp_size * ar_cap_rows * 4 * 4, 256);
-    sym_bytes = data_b + flags_b + cand_b + 256;
+    sym_samp_off = align_up(data_b + flags_b + cand_b + 256, 256);
+    sym_bytes = sym_samp_off + tp_sample_area_bytes(tp_size, ar_cap_rows);
+    if (const char *e = getenv("DIS_TP_SAMPLE")) tp_sample_fused = strcmp(e, "gather") != 0;
     // Prefill-sized passes (more rows than the decode region holds) go through ncclAllReduce (reading the projection
     // output in place when it is one slice) + the norm kernel.  DIS_TP_PREFILL_FUSED=1 gives them their own region of the
     // symmetric buffer and a fused peer-memory exchange instead (one kernel, 2 (tp-1)/tp * T*H*4 bytes on the wire),
@@ -295,7 +297,11 @@ int Engine::tp_import(const uint8_t *handles) {
     peers.flags[r] = reinterpret_cast<uint32_t *>(base + data_b);
     peers.cand[r] = reinterpret_cast<uint32_t *>(base + data_b + flags_b);
     peers.cand_flags[r] = reinterpret_cast<uint32_t *>(base + data_b + flags_b + cand_b);
+    samp_peers.buf[r] = reinterpret_cast<uint32_t *>(base + sym_samp_off);
   }
+  samp_peers.rank = tp_rank;
+  samp_peers.tp = tp_size;
+  samp_peers.cap_rows = ar_cap_rows;
   peers.rank = tp_rank;
   peers.tp = tp_size;
   peers.cap_rows = ar_cap_rows;
@@ -778,6 +784,13 @@ cudaError_t Engine::enqueue_head(int R, bool all_greedy) {
     if (r != 0) { set_last_error(std::string("ncclAllGather: ") + nccl->GetErrorString(r)); return cudaErrorUnknown; }
     kernel_launches += 5;
     return launch_argmax_merge(cand_val_all, cand_tok_all, cand_sum_all, tp_size, R, d_out_tokens, d_logprob, stream);
+  }
+  if (tp_custom && tp_sample_fused && R <= ar_cap_rows) {
+    // temperature / nucleus rows (and the greedy rows beside them): the logits stay sharded, the ranks exchange a few
+    // scalars per row over peer memory (k_tp_sample.cu) instead of all-gathering R * V fp32 logits
+    kernel_launches++;
+    return launch_tp_sample(samp_peers, logits, vocab_l, R, vocab_l, temp, topp, seed, step, cur_meta->d<uint32_t>(cur_meta->o_arstep), 0,
+                            d_out_tokens, d_logprob, stream);
   }
   RET_CUDA(gather_full_logits(R));
   kernel_launches++;

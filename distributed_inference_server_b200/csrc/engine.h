@@ -137,9 +137,11 @@ struct Engine {
   void *comm = nullptr;
   // peer-memory exchange (k_tp.cu): one symmetric allocation per rank, mapped into every peer through CUDA IPC
   uint8_t *sym = nullptr;
-  size_t sym_bytes = 0, sym_big_off = 0;
+  size_t sym_bytes = 0, sym_big_off = 0, sym_samp_off = 0;
   void *peer_base[kTpMaxRanks] = {};
   TpPeers peers{};
+  TpSampPeers samp_peers{};  // vocab-parallel sampler's exchange area (k_tp_sample.cu)
+  bool tp_sample_fused = true;  // DIS_TP_SAMPLE=gather: all-gather the logits through NCCL and sample on every rank instead
   TpPeers peers_big{};      // second region of the symmetric buffer: fenced two-shot exchange for prefill-sized passes
   int ar_cap_big = 0;       // rows that region holds (0: absent, such passes go through NCCL)
   bool tp_custom = false;   // peers imported: all-reduce fused into the norm kernels

@@ -52,6 +52,22 @@ cudaError_t launch_tp_add_rmsnorm(const TpPeers &peers, float *x, const float *p
 cudaError_t launch_tp_argmax_merge(const TpPeers &peers, const float *val, const uint32_t *tok, const float *sumexp,
                                    const uint32_t *step_ptr, int T, uint32_t *out, float *out_logprob, cudaStream_t st);
 
+// k_tp_sample.cu : vocab-parallel sampling (greedy, temperature, nucleus) over peer memory.  buf[r] = rank r's exchange area,
+// tp_sample_area_bytes() of zero-initialised memory laid out [round][source rank][cap_rows][kTpSampleVals] x {bits, epoch}.
+// rank < 0: the tp ranks are emulated on one GPU (grid (rows, tp); logits is the full [T][tp * Vl] matrix, out_tokens /
+// out_logprob are [tp][T]).  step_ptr (device) or step_imm numbers the call: it must differ from the previous call's on
+// the same area and be the same on every rank.
+constexpr int kTpSampleRounds = 12, kTpSampleVals = 16;
+struct TpSampPeers {
+  uint32_t *buf[kTpMaxRanks];
+  int rank, tp, cap_rows;
+};
+size_t tp_sample_area_bytes(int tp, int cap_rows);
+cudaError_t launch_tp_sample(const TpSampPeers &sp, const float *logits, long long ld, int T, int Vl,
+                             const float *temperature, const float *top_p, const unsigned long long *seeds,
+                             const unsigned long long *steps, const uint32_t *step_ptr, uint32_t step_imm,
+                             uint32_t *out_tokens, float *out_logprob, cudaStream_t st);
+
 // k_gemv.cu : out[t][n] = sum_k X[t][k] W[n][k]  (T <= kGemvMaxT per launch; launcher loops)
 constexpr int kGemvMaxT = 4;
 cudaError_t launch_gemv(const uint16_t *X, const uint16_t *W, float *out, int T, int N, int K, cudaStream_t st);

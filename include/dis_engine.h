@@ -382,6 +382,19 @@ DIS_API int dis_k_attn_prefill(const uint16_t *q, const uint16_t *kv_pool, int64
 DIS_API int dis_k_sample(const float *logits, int64_t ld, int32_t T, int32_t V, const float *temperature,
                          const float *top_p, const uint64_t *seeds, const uint64_t *steps,
                          uint32_t *out_tokens, float *out_logprob, void *stream);
+/* The vocab-parallel sampler of tensor-parallel engines (csrc/k_tp_sample.cu: each rank keeps its V/tp logit columns
+ * and exchanges a few scalars per row over peer memory -- candidates for greedy rows, 16 partial masses per round of
+ * a 16-ary threshold search for nucleus rows, then the drawn token) with its tp ranks emulated on ONE GPU, so that it
+ * can be checked against the oracle and against dis_k_sample without a second GPU.  logits [T][V] fp32, V a multiple
+ * of tp, T * tp <= 148 (the emulated ranks wait for each other inside one grid).  area: tp *
+ * dis_k_sample_vocab_parallel_area_bytes(tp, area_rows) bytes of device memory, zero-filled once by the caller;
+ * call_no must differ between consecutive calls on the same area.  out_tokens / out_logprob are [tp][T]: what each
+ * emulated rank wrote -- all slices must be equal. */
+DIS_API size_t dis_k_sample_vocab_parallel_area_bytes(int32_t tp, int32_t rows);
+DIS_API int dis_k_sample_vocab_parallel(const float *logits, int32_t T, int32_t V, int32_t tp, const float *temperature,
+                                        const float *top_p, const uint64_t *seeds, const uint64_t *steps,
+                                        uint32_t call_no, void *area, int32_t area_rows, uint32_t *out_tokens,
+                                        float *out_logprob, void *stream);
 /* Synthetic weights: dst[i] = bf16(offset + (2u-1)*amp), u from the counter hash (seed, kind, layer, i). */
 DIS_API int dis_k_synth_bf16(uint16_t *dst, size_t n, uint64_t seed, int32_t kind, int32_t layer, float amp,
                              float offset, void *stream);

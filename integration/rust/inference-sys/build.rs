@@ -8,7 +8,7 @@ fn main() {
     let csrc = src.join("distributed_inference_server_b200/csrc");
     // the same list as distributed_inference_server_b200/build.py
     let files = [
-        "k_elementwise.cu", "k_gemv.cu", "k_attn_paged.cu", "k_attn_prefill_tc.cu", "k_gemm_tcgen05.cu", "k_gemm_persist.cu", "k_tp.cu",
+        "k_elementwise.cu", "k_gemv.cu", "k_attn_paged.cu", "k_attn_prefill_tc.cu", "k_gemm_tcgen05.cu", "k_gemm_persist.cu", "k_tp.cu", "k_tp_sample.cu",
         "engine.cu", "api.cpp", "tp.cpp", "worker.cpp", "serving.cpp", "prefix.cpp",
     ];
     let mut cmd = Command::new(env::var("NVCC").unwrap_or_else(|_| "nvcc".into()));

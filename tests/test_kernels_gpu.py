@@ -438,3 +438,56 @@ def test_sampler_top_p_matches_oracle(T, V):
     for t in range(T):
         if temps[t] == 0:
             assert got[t] == int(np.argmax(lg[t]))
+
+
+@pytest.mark.parametrize("tp,T,V", [(2, 48, 4100), (3, 20, 4098), (4, 24, 128256), (8, 16, 128256)],
+                         ids=["tp2-small-vocab", "tp3-small-vocab", "tp4-llama3-vocab", "tp8-llama3-vocab"])
+def test_vocab_parallel_sampler_matches_the_one_gpu_sampler_and_the_oracle(tp, T, V):
+    """The tensor-parallel engines' sampler (k_tp_sample.cu) with its ranks emulated on one GPU: every rank keeps V/tp
+    logit columns and exchanges scalars (candidates, 16 partial masses per round of the threshold search, the drawn
+    token).  All ranks must write the same token and log-probability; greedy rows are exact; nucleus rows must draw what
+    dis_k_sample and the oracle draw, except where the draw lands within fp32 noise of a bucket edge (the partial sums
+    are associated per rank).  Two calls on the same exchange area: the second must not see the first one's words."""
+    rng = np.random.default_rng(3 + tp)
+    rows = T + 3                                                   # area rows > T: the row stride is the area's, not the call's
+    n_area = tp * lib().dis_k_sample_vocab_parallel_area_bytes(tp, rows) // 4
+    area = G.zeros(n_area, dtype=torch.int32, device=DEV)
+    for call_no in (1, 2):
+        lg = (rng.standard_normal((T, V)) * 2.5).astype(np.float32)
+        lg[0, [V // tp - 1, V // tp]] = 40.0                       # a tie across a slice boundary: the lower id wins
+        temps = rng.choice([0.0, 0.5, 1.0, 1.7], T).astype(np.float32)
+        temps[0] = 0.0
+        tps = rng.choice([0.1, 0.5, 0.9, 0.95, 1.0], T).astype(np.float32)
+        seeds = rng.integers(0, 2 ** 40, T).astype(np.uint64)
+        steps = rng.integers(0, 100, T).astype(np.uint64)
+        dl, dt, dp = dev_f32(lg), dev_f32(temps), dev_f32(tps)
+        ds = torch.from_numpy(seeds.view(np.int64)).to(DEV)
+        dst = torch.from_numpy(steps.view(np.int64)).to(DEV)
+        out = G.zeros((tp, T), dtype=torch.int32, device=DEV)
+        lp = G.zeros((tp, T), dtype=torch.float32, device=DEV)
+        check(lib().dis_k_sample_vocab_parallel(ptr(dl), T, V, tp, ptr(dt), ptr(dp), ptr(ds), ptr(dst), call_no, ptr(area), rows,
+                                                ptr(out), ptr(lp), None))
+        one = G.zeros(T, dtype=torch.int32, device=DEV)
+        one_lp = G.zeros(T, dtype=torch.float32, device=DEV)
+        check(lib().dis_k_sample(ptr(dl), V, T, V, ptr(dt), ptr(dp), ptr(ds), ptr(dst), ptr(one), ptr(one_lp), None))
+        sync()
+        got_all, lp_all = out.cpu().numpy(), lp.cpu().numpy()
+        for r in range(1, tp):                                     # every rank computes the same bits
+            assert np.array_equal(got_all[0], got_all[r]) and np.array_equal(lp_all[0], lp_all[r]), r
+        got, single = got_all[0].tolist(), one.cpu().tolist()
+        assert got[0] == V // tp - 1
+        mism_single = mism_oracle = 0
+        for t in range(T):
+            z = lg[t].astype(np.float64) / (float(temps[t]) if temps[t] > 0 else 1.0)
+            want_lp = z[got[t]] - (np.log(np.exp(z - z.max()).sum()) + z.max())
+            assert abs(float(lp_all[0, t]) - want_lp) <= 1e-3 * max(1.0, abs(want_lp)), (t, float(lp_all[0, t]), want_lp)
+            if temps[t] == 0:
+                assert got[t] == int(np.argmax(lg[t])) == single[t]
+                continue
+            ref, tau, mass = O.sample(lg[t], float(temps[t]), float(tps[t]), int(seeds[t]), int(steps[t]))
+            if got[t] != ref or got[t] != single[t]:
+                mism_oracle += got[t] != ref
+                mism_single += got[t] != single[t]
+                p = np.exp(z - z.max()); p /= p.sum()
+                assert (p >= tau * (1 - 1e-5))[got[t]], (t, got[t], ref, single[t])   # still inside the nucleus
+        assert mism_oracle <= 2 and mism_single <= 2, (mism_oracle, mism_single)
