@@ -222,3 +222,28 @@ def test_tp_prefill_pass_larger_than_the_decode_exchange_region(world):
         if fused[0][0][b] != w["tokens"][b]:
             i = next(k for k in range(n_new) if fused[0][0][b][k] != w["tokens"][b][k])
             assert w["margins"][b, i] <= 5e-3 * np.abs(w["logits"][b, i]).max(), (b, i)
+
+
+@pytest.mark.parametrize("world", WORLDS)
+def test_tp_vocab_parallel_sampler_draws_what_the_gathered_sampler_draws(world):
+    """Temperature / nucleus rows under tensor parallelism: the default keeps the logits sharded and exchanges scalars
+    over peer memory (k_tp_sample.cu); DIS_TP_SAMPLE=gather all-gathers the logits through NCCL and runs the one-GPU
+    sampler on every rank.  Same exchange kernel in front of both, so the logits are bit-identical and the draws must be
+    the same tokens (a draw within fp32 noise of a bucket edge may differ: at most one of the six sequences), with the
+    same log-probabilities, on every rank."""
+    shape = shape_for(world)
+    rng = np.random.default_rng(9)
+    prompts = [rng.integers(0, shape.vocab, n).tolist() for n in (7, 33, 18, 2, 25, 11)]
+    temps = [0.7, 1.1, 0.0, 1.6, 0.3, 0.9]
+    kw = dict(world=world, shape=shape)
+    fused = _run(prompts, 10, temps, "ll", **kw)
+    gathered = _run(prompts, 10, temps, "ll", env={"DIS_TP_SAMPLE": "gather"}, **kw)
+    for r in range(1, world):
+        assert fused[0][0] == fused[r][0] and np.array_equal(fused[0][2], fused[r][2])
+    assert np.array_equal(fused[0][1], gathered[0][1])             # the first pass's logits: same bits
+    same = sum(a == b for a, b in zip(fused[0][0], gathered[0][0]))
+    assert same >= len(prompts) - 1, (fused[0][0], gathered[0][0])
+    assert fused[0][0][2] == gathered[0][0][2]                     # the greedy row among them is exact
+    lp_f, lp_g = np.asarray(fused[0][2]), np.asarray(gathered[0][2])
+    first_same = [fused[0][0][b][0] == gathered[0][0][b][0] for b in range(len(prompts))]
+    assert np.abs(lp_f - lp_g)[first_same].max() <= 1e-4
