@@ -438,7 +438,8 @@ def run_ours(args):
 
     rng = np.random.default_rng(1)
     prompts = [rng.integers(0, shape.vocab, args.prompt_len).tolist() for _ in range(batch)]
-    P = InferenceParams(max_tokens=total_steps + 4, temperature=0.0)
+    # greedy is the headline (BASELINE's metric); --temperature > 0 times sampled decoding (A/B of the samplers)
+    P = InferenceParams(max_tokens=total_steps + 4, temperature=args.temperature, top_p=args.top_p, seed=7)
 
     def barrier():
         if dist is not None:
@@ -461,7 +462,7 @@ def run_ours(args):
     # ---- tensor parallel: parity against a TP=1 engine BEFORE anything is timed, and that engine's own decode time at
     # the same batch (the like-for-like denominator of the scaling curve)
     parity, tp1 = None, None
-    if world > 1 and not args.no_parity and args.model == "8b" and args.shard_of <= 1:
+    if world > 1 and not args.no_parity and args.model == "8b" and args.shard_of <= 1 and args.temperature <= 0:
         parity, one, one_slots = tp_parity_check(eng, make_engine, prompts, P, rank, world, dist, torch, gloo)
         if rank == 0:
             for _ in range(args.settle_steps + args.warmup):
@@ -560,6 +561,8 @@ def run_ours(args):
         step_gbs = step_bytes / (ms_per_step * 1e-3) / 1e9
         cfg = workload_config(world, batch, args.prompt_len, args.model)
         cfg["settle_steps"] = args.settle_steps
+        if args.temperature > 0:
+            cfg["sampling"] = {"temperature": args.temperature, "top_p": args.top_p, "tp_sampler": os.environ.get("DIS_TP_SAMPLE", "fused")}
         line = {"metric": "decode tokens/s Llama-3-" + args.model.upper(), "value": value, "unit": "tokens/s", "n_gpus": world,
                 "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
                 "scaling": "strong" if world > 1 else "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
@@ -765,6 +768,8 @@ def main():
     ap.add_argument("--new-tokens", type=int, default=128)
     ap.add_argument("--settle-steps", type=int, default=48,
                     help="untimed decode steps before the W warm-up steps: lets the board leave the prefill's power state")
+    ap.add_argument("--temperature", type=float, default=0.0, help="> 0: sampled decoding (not the headline; the TP parity gate is greedy-only and is skipped)")
+    ap.add_argument("--top-p", type=float, default=0.9)
     ap.add_argument("--no-parity", action="store_true", help="TP: skip the parity check against a TP=1 engine on rank 0")
     args = ap.parse_args()
     if args.impl == "reference":
