@@ -197,7 +197,9 @@ DIS_API int dis_tp_unique_id(uint8_t out[128]);
 /* Peer-memory exchange: every rank exports a 64-byte CUDA IPC handle of its symmetric buffer, the host
  * all-gathers them (rank order) and hands all tp_size handles to every rank.  After the import the all-reduce
  * after the O and down projections is fused into the residual + RMSNorm kernel (P2P loads over NVLink, flag
- * signalling) and the greedy candidates are merged the same way; without it the engine uses NCCL. */
+ * signalling), the greedy candidates are merged the same way, and temperature / nucleus rows are sampled with the
+ * logits left sharded (a few scalars per row exchanged over peer memory, csrc/k_tp_sample.cu); without it the engine
+ * uses NCCL (all-reduce, and an all-gather of the logits for sampled rows). */
 DIS_API int dis_engine_tp_export(dis_engine *e, uint8_t out[64]);
 DIS_API int dis_engine_tp_import(dis_engine *e, const uint8_t *handles /* [tp_size][64] */);
 
