@@ -7,10 +7,11 @@
 // the logits where they are and exchanges a handful of scalars per row instead:
 //
 //   round 0      local (max, argmax id, sum exp(z - local max))            -> global max m, normaliser Z, greedy rows done
-//   rounds 1..   16-ary search for the nucleus threshold tau: every rank sums its own p_i >= thr_j for 16 thresholds
-//                between lo and hi, the 16 x tp partial masses are exchanged and added IN RANK ORDER (every rank
-//                computes the same bits and narrows [lo, hi) identically); 2^30 bit patterns -> 8 rounds.  Same
-//                definition as sample_kernel (k_elementwise.cu): the largest threshold whose kept mass reaches top_p.
+//   rounds 1..   16-ary search for the nucleus threshold tau: every rank sums its own p_i >= thr_j for 16 equally spaced
+//                thresholds in [lo, hi) (one pass: a bucket per element, masses = suffix sums of the buckets), the
+//                16 x tp partial masses are exchanged and added IN RANK ORDER (every rank computes the same bits and
+//                narrows [lo, hi) identically); 2^30 bit patterns -> 8 rounds.  Same definition as sample_kernel
+//                (k_elementwise.cu): the largest threshold whose kept mass reaches top_p.
 //   draw         the ranks' kept masses are known from the last round: u * kept falls into exactly one rank's
 //                slice (slices are in vocabulary order); that rank walks its kept tokens as sample_kernel does and
 //   last round   broadcasts (token id, z of the token); every rank writes the same token and log-probability.
@@ -54,6 +55,7 @@ __device__ __forceinline__ uint32_t ld_word(const uint32_t *p, uint32_t epoch) {
 struct Shared {
   float red[32][kVals];
   uint32_t mine[kVals];
+  float bucket[kVals];
   uint32_t all[kTpMaxRanks][kVals];
   float scan[32];
   Cand am[32];
@@ -88,6 +90,7 @@ tp_sample_kernel(TpSampPeers sp, const float *__restrict__ logits, long long ld,
                  const uint32_t *__restrict__ step_ptr, uint32_t step_imm, uint32_t *__restrict__ out,
                  float *__restrict__ out_logprob) {
   __shared__ Shared s;
+  extern __shared__ float bins[];  // [kVals][kThreads]: a column per thread
   const int t = blockIdx.x, T = gridDim.x, tp = sp.tp;
   const bool emulated = sp.rank < 0;
   const int me = emulated ? (int)blockIdx.y : sp.rank;
@@ -161,50 +164,61 @@ tp_sample_kernel(TpSampPeers sp, const float *__restrict__ logits, long long ld,
     return;
   }
 
-  // ---- nucleus threshold: 16-ary search over the bit patterns of positive floats (they are ordered)
+  // ---- nucleus threshold: 16-ary search over the bit patterns of positive floats (they are ordered).
+  // A round's thresholds are thr_j = lo + j * 2^k with 16 * 2^k >= hi - lo, so an element's bucket is a shift:
+  // b = min((bits - lo) >> k, 15).  Every thread adds its elements into its own column of bins[16][1024] in shared
+  // memory (one add per element instead of sixteen compare-adds: the pass is then bound by the L2 read of the slice),
+  // the columns are reduced in a fixed order, and mass(thr_j) = sum of buckets j..15 -- buckets are summed from the
+  // top, so the masses cannot increase with j.  Bucket 15 also takes everything at or above lo + 15 * 2^k.
   const float inv_z = 1.0f / Z;
   const float tpv = top_p ? top_p[t] : 1.0f;
-  uint32_t lo = 0u, hi = tpv < 1.0f ? 0x3f800001u : 1u;  // invariant: mass(lo) >= top_p > mass(hi)
+  const bool cut = tpv < 1.0f;  // top_p >= 1: no threshold, the one round only exchanges the slices' total masses
+  uint32_t lo = 0u, hi = cut ? 0x3f800001u : 1u;  // invariant (cut): mass(lo) >= top_p > mass(hi), lo < hi
   int round = 1, jsel = 0;
   do {
-    const uint32_t width = hi - lo;
-    const uint32_t stepw = (width + kVals - 1) / kVals > 0u ? (width + kVals - 1) / kVals : 1u;
-    uint32_t thr[kVals];
-    float acc[kVals];
+    const uint32_t per = (hi - lo + kVals - 1) / kVals;  // >= 1
+    const int k = per > 1u ? 32 - __clz(per - 1u) : 0;   // 2^k >= per
 #pragma unroll
-    for (int j = 0; j < kVals; j++) {
-      const uint32_t c = lo + (uint32_t)j * stepw;
-      thr[j] = c < hi - 1u ? c : hi - 1u;
-      acc[j] = 0.f;
-    }
+    for (int j = 0; j < kVals; j++) bins[j * kThreads + threadIdx.x] = 0.f;
     for (int i = threadIdx.x; i < Vl; i += kThreads) {
       const float p = expf(fmaf(row[i], inv_t, -m)) * inv_z;
       const uint32_t b = __float_as_uint(p);
-#pragma unroll
-      for (int j = 0; j < kVals; j++) acc[j] += b >= thr[j] ? p : 0.f;
+      if (b >= lo) {
+        const uint32_t q = (b - lo) >> k;
+        bins[(q < (uint32_t)(kVals - 1) ? q : (uint32_t)(kVals - 1)) * kThreads + threadIdx.x] += p;  // own column: no race
+      }
     }
 #pragma unroll
     for (int j = 0; j < kVals; j++) {
-      const float v = warp_sum(acc[j]);
+      const float v = warp_sum(bins[j * kThreads + threadIdx.x]);
       if (lane == 0) s.red[warp][j] = v;
     }
     __syncthreads();
     if (threadIdx.x < kVals) {
       float tot = 0.f;
-      for (int w = 0; w < kThreads / 32; w++) tot += s.red[w][threadIdx.x];
-      s.mine[threadIdx.x] = __float_as_uint(tot);
+      for (int w = 0; w < kThreads / 32; w++) tot += s.red[w][threadIdx.x];  // warp order: deterministic
+      s.bucket[threadIdx.x] = tot;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      float run = 0.f;
+      for (int j = kVals - 1; j >= 0; j--) { run += s.bucket[j]; s.mine[j] = __float_as_uint(run); }
     }
     exchange(sp, s, me, t, round, kVals, epoch(round));
     jsel = 0;
-    for (int j = 1; j < kVals; j++) {
-      float mass = 0.f;
-      for (int r = 0; r < tp; r++) mass += __uint_as_float(s.all[r][j]);  // rank order: the same bits on every rank
-      if (mass >= tpv) jsel = j;  // masses do not increase with j: the last hit is the largest threshold that still reaches top_p
+    if (cut) {
+      for (int j = 1; j < kVals; j++) {
+        float mass = 0.f;
+        for (int r = 0; r < tp; r++) mass += __uint_as_float(s.all[r][j]);  // rank order: the same bits on every rank
+        // the last hit is the largest threshold that still reaches top_p; thresholds at or above hi are known to fall short
+        if (mass >= tpv && (((uint32_t)j << k) >> k) == (uint32_t)j && lo + ((uint32_t)j << k) < hi) jsel = j;
+      }
+      const uint32_t next = lo + ((uint32_t)(jsel + 1) << k);
+      if (jsel < kVals - 1 && next < hi) hi = next;
+      lo += (uint32_t)jsel << k;
     }
-    if (jsel < kVals - 1 && thr[jsel + 1] > thr[jsel]) hi = thr[jsel + 1];
-    lo = thr[jsel];
     round++;
-  } while (hi - lo > 1u && round <= kSearchRounds);
+  } while (cut && hi - lo > 1u && round <= kSearchRounds);
   const uint32_t tau = lo;
 
   // ---- which rank's slice holds the draw
@@ -306,7 +320,11 @@ cudaError_t launch_tp_sample(const TpSampPeers &sp, const float *logits, long lo
     set_last_error("tp_sample (one-GPU emulation): rows * tp must not exceed the SM count");
     return cudaErrorInvalidValue;
   }
-  return launch_k(tp_sample_kernel, dim3(T, emulated ? sp.tp : 1), dim3(kThreads), 0, st, sp, logits, ld, Vl, temperature, top_p,
+  constexpr size_t kBinBytes = (size_t)kVals * kThreads * sizeof(float);  // 64 KB of dynamic shared memory
+  static DeviceOnce once;
+  const cudaError_t e = once.run([] { return cudaFuncSetAttribute(tp_sample_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kBinBytes); });
+  if (e != cudaSuccess) { set_last_error("tp_sample: cannot reserve 64 KB of shared memory"); return e; }
+  return launch_k(tp_sample_kernel, dim3(T, emulated ? sp.tp : 1), dim3(kThreads), kBinBytes, st, sp, logits, ld, Vl, temperature, top_p,
                   seeds, steps, step_ptr, step_imm, out_tokens, out_logprob);
 }
 
