@@ -5,7 +5,7 @@ set -u
 mkdir -p gpurun_out
 O=gpurun_out
 N=$(python -c "import torch; print(torch.cuda.device_count())")
-for mode in fused gather fused; do
+for mode in fused gather; do
   i=$(ls $O/r2_tpsample_bench_${mode}_*.json 2>/dev/null | wc -l)
   DIS_TP_SAMPLE=$mode timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29513 \
     bench.py --gpus $N --steps 40 --warmup 5 --temperature 0.8 --top-p 0.9 --no-cpu --ttft-runs 1 --profile-steps 1 \
