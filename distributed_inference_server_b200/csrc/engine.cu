@@ -218,6 +218,7 @@ int Engine::init(const dis_engine_config *c) {
   if (const char *g = getenv("DIS_GEMM_PERSIST")) use_persist = atoi(g) != 0;
   if (const char *g = getenv("DIS_GEMV_MAX_T")) gemv_max_t = std::max(0, std::min(kGemvMaxT, atoi(g)));
   if (const char *g = getenv("DIS_ATTN_MAX_SPLITS")) max_attn_splits = atoi(g);
+  if (const char *g = getenv("DIS_SAMPLER")) sampler_buckets = strcmp(g, "bisect") != 0;
   // Measurement aid, never set in production: DIS_DEBUG_SKIP=norm,attn,... leaves those kernel classes out of the
   // decode step (its results are then garbage) so that step time with and without a class gives the class's marginal
   // cost INSIDE the graph, where programmatic dependent launch overlaps neighbours and ncu's isolated times mislead.
@@ -766,6 +767,13 @@ cudaError_t Engine::enqueue_head(int R, bool all_greedy) {
   float *d_logprob = reinterpret_cast<float *>(d_out_tokens + max_batch);  // TokenEvent.logprob, models.rs:276
   if (tp_size == 1) {
     kernel_launches++;
+    if (!all_greedy && sampler_buckets) {
+      // temperature / nucleus rows: the 16-ary bucket search of k_tp_sample.cu as a single rank (8 passes over the row
+      // instead of the 31 of sample_kernel's bisection; nothing is exchanged).  DIS_SAMPLER=bisect keeps sample_kernel.
+      TpSampPeers solo{};
+      solo.rank = 0; solo.tp = 1; solo.cap_rows = max_batch;
+      return launch_tp_sample(solo, logits, vocab_l, R, vocab_l, temp, topp, seed, step, nullptr, 0, d_out_tokens, d_logprob, stream);
+    }
     return launch_sample(logits, vocab_l, R, vocab_l, temp, topp, seed, step, d_out_tokens, 0, nullptr, nullptr, d_logprob, stream);
   }
   if (all_greedy && tp_custom) {

@@ -141,6 +141,7 @@ struct Engine {
   void *peer_base[kTpMaxRanks] = {};
   TpPeers peers{};
   TpSampPeers samp_peers{};  // vocab-parallel sampler's exchange area (k_tp_sample.cu)
+  bool sampler_buckets = true;  // one GPU, sampled rows: bucket search (k_tp_sample.cu as a single rank); DIS_SAMPLER=bisect: sample_kernel
   bool tp_sample_fused = true;  // DIS_TP_SAMPLE=gather: all-gather the logits through NCCL and sample on every rank instead
   TpPeers peers_big{};      // second region of the symmetric buffer: fenced two-shot exchange for prefill-sized passes
   int ar_cap_big = 0;       // rows that region holds (0: absent, such passes go through NCCL)

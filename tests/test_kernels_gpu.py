@@ -440,8 +440,9 @@ def test_sampler_top_p_matches_oracle(T, V):
             assert got[t] == int(np.argmax(lg[t]))
 
 
-@pytest.mark.parametrize("tp,T,V", [(2, 48, 4100), (3, 20, 4098), (4, 24, 128256), (8, 16, 128256)],
-                         ids=["tp2-small-vocab", "tp3-small-vocab", "tp4-llama3-vocab", "tp8-llama3-vocab"])
+@pytest.mark.parametrize("tp,T,V", [(1, 48, 4099), (1, 32, 128256), (2, 48, 4100), (3, 20, 4098), (4, 24, 128256), (8, 16, 128256)],
+                         ids=["single-rank-ragged-vocab", "single-rank-llama3-vocab", "tp2-small-vocab", "tp3-small-vocab",
+                              "tp4-llama3-vocab", "tp8-llama3-vocab"])
 def test_vocab_parallel_sampler_matches_the_one_gpu_sampler_and_the_oracle(tp, T, V):
     """The tensor-parallel engines' sampler (k_tp_sample.cu) with its ranks emulated on one GPU: every rank keeps V/tp
     logit columns and exchanges scalars (candidates, 16 partial masses per round of the threshold search, the drawn
@@ -454,7 +455,7 @@ def test_vocab_parallel_sampler_matches_the_one_gpu_sampler_and_the_oracle(tp, T
     area = G.zeros(n_area, dtype=torch.int32, device=DEV)
     for call_no in (1, 2):
         lg = (rng.standard_normal((T, V)) * 2.5).astype(np.float32)
-        lg[0, [V // tp - 1, V // tp]] = 40.0                       # a tie across a slice boundary: the lower id wins
+        lg[0, [V // tp - 1, (V // tp) % V]] = 40.0                 # a tie across a slice boundary: the lower id wins
         temps = rng.choice([0.0, 0.5, 1.0, 1.7], T).astype(np.float32)
         temps[0] = 0.0
         tps = rng.choice([0.1, 0.5, 0.9, 0.95, 1.0], T).astype(np.float32)
@@ -475,7 +476,7 @@ def test_vocab_parallel_sampler_matches_the_one_gpu_sampler_and_the_oracle(tp, T
         for r in range(1, tp):                                     # every rank computes the same bits
             assert np.array_equal(got_all[0], got_all[r]) and np.array_equal(lp_all[0], lp_all[r]), r
         got, single = got_all[0].tolist(), one.cpu().tolist()
-        assert got[0] == V // tp - 1
+        assert got[0] == (V // tp - 1 if tp > 1 else 0)
         mism_single = mism_oracle = 0
         for t in range(T):
             z = lg[t].astype(np.float64) / (float(temps[t]) if temps[t] > 0 else 1.0)
