@@ -42,6 +42,32 @@ pub struct dis_prefix_stats {
 }
 
 pub enum dis_engine {}
+pub enum dis_serving {}
+
+/// Admission queue of the continuous batcher: the watermarks and timeout of `PriorityQueueManager`
+/// (crates/core/src/queue.rs:103-158).
+#[repr(C)]
+#[derive(Clone, Copy)]
+pub struct dis_queue_config {
+    pub high_watermark: i32, pub low_watermark: i32, pub max_queue_size: i32, pub request_timeout_s: f64,
+}
+
+#[repr(C)]
+#[derive(Clone, Copy, Default)]
+pub struct dis_queue_depth { pub high: i32, pub normal: i32, pub low: i32, pub total: i32, pub accepting: i32, pub active: i32 }
+
+pub const DIS_EVENT_TOKEN: i32 = 0;
+pub const DIS_EVENT_DONE: i32 = 1;
+pub const DIS_EVENT_EXPIRED: i32 = 2;
+
+/// One streamed item: `TokenEvent::Token { index, logprob }` / `TokenEvent::Done` (crates/core/src/models.rs:268-288)
+/// for the request whose `Uuid` bytes (`RequestID`, crates/core/src/types.rs:7) are in `request_id`.
+#[repr(C)]
+#[derive(Clone, Copy)]
+pub struct dis_serving_event {
+    pub request_id: [u8; 16], pub kind: i32, pub token: u32, pub index: i32, pub finish_reason: i32,
+    pub prompt_tokens: i32, pub waited_ms: f64, pub logprob: f32,
+}
 
 extern "C" {
     pub fn dis_abi_version() -> c_int;
@@ -67,4 +93,19 @@ extern "C" {
     pub fn dis_tp_unique_id(out: *mut u8) -> c_int;
     pub fn dis_engine_tp_export(e: *mut dis_engine, out: *mut u8) -> c_int;
     pub fn dis_engine_tp_import(e: *mut dis_engine, handles: *const u8) -> c_int;
+
+    // ---- continuous batching above the engine (optional: a host that keeps its own PriorityQueueManager drives
+    // dis_engine_step itself; one that does not gets admission by priority, chunked prefill and streaming from these)
+    pub fn dis_serving_create(engine: *mut dis_engine, cfg: *const dis_queue_config, max_active: i32, out: *mut *mut dis_serving) -> c_int;
+    pub fn dis_serving_destroy(s: *mut dis_serving) -> c_int;
+    pub fn dis_serving_last_error(s: *mut dis_serving) -> *const c_char;
+    /// request_id: `Uuid::as_bytes()`; priority 0 = High, 1 = Normal, 2 = Low (crates/core/src/queue.rs).
+    pub fn dis_serving_submit(s: *mut dis_serving, request_id: *const u8, prompt: *const u32, n_prompt: i32,
+                              params: *const dis_sampling_params, priority: i32) -> c_int;
+    /// Client went away (requirements.md:85): the request leaves the queue or frees its slot and KV pages.
+    pub fn dis_serving_cancel(s: *mut dis_serving, request_id: *const u8) -> c_int;
+    /// One scheduler step = one forward pass; fills up to `cap` events.
+    pub fn dis_serving_step(s: *mut dis_serving, events: *mut dis_serving_event, cap: i32, n_events: *mut i32) -> c_int;
+    pub fn dis_serving_depth(s: *mut dis_serving, out: *mut dis_queue_depth) -> c_int;
+    pub fn dis_serving_set_prefill_budget(s: *mut dis_serving, tokens: i32) -> c_int;
 }
