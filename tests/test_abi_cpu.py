@@ -89,3 +89,42 @@ def test_library_was_built_from_the_current_sources():
     from -- dis_build_id() is the hash of every source, header and compiler flag, and has to match the tree."""
     from distributed_inference_server_b200 import build as b
     assert B.load().dis_build_id().decode() == b.source_id()
+
+
+def test_rust_sys_shim_mirrors_the_header_field_for_field():
+    """integration/rust cannot be compiled here (no cargo), so the one thing that can drift silently -- a #[repr(C)]
+    struct whose fields no longer match the header's, or an extern fn the header does not declare -- is checked as text:
+    every struct of the shim has the header's field names in the header's order, and every `pub fn dis_*` exists in
+    the header with the same number of parameters."""
+    import re
+    hdr = open(os.path.join(ROOT, "include", "dis_engine.h")).read()
+    hdr = re.sub(r"/\*.*?\*/", " ", hdr, flags=re.S)
+    rs = open(os.path.join(ROOT, "integration", "rust", "inference-sys", "src", "lib.rs")).read()
+    rs = re.sub(r"//[^\n]*", " ", rs)
+    h_structs = {}
+    for body, name in re.findall(r"typedef struct \w*\s*\{(.*?)\}\s*(\w+)\s*;", hdr, flags=re.S):
+        fields = []
+        for decl in body.split(";"):
+            decl = decl.strip()
+            if not decl:
+                continue
+            first, *rest = decl.split(",")
+            names = [re.sub(r"\[.*?\]", "", first).split()[-1].lstrip("*")] + [re.sub(r"\[.*?\]", "", r).strip().lstrip("*") for r in rest]
+            fields += names
+        h_structs[name] = fields
+    aliases = {"dis_worker_status": "dis_engine_status"}
+    n = 0
+    for name, body in re.findall(r"pub struct (\w+)\s*\{(.*?)\}", rs, flags=re.S):
+        fields = re.findall(r"pub (\w+)\s*:", body)
+        want = h_structs.get(name) or h_structs.get(aliases.get(name, ""))
+        assert want is not None, f"{name}: no such struct in the header"
+        assert fields == want, (name, fields, want)
+        n += 1
+    assert n >= 7
+    h_fns = {m[0]: m[1] for m in re.findall(r"DIS_API [^;(]*?(dis_\w+)\s*\(([^;]*?)\)\s*;", hdr, flags=re.S)}
+    def count(params):
+        params = params.strip()
+        return 0 if params in ("", "void") else len(params.split(","))
+    for fn, params in re.findall(r"pub fn (dis_\w+)\s*\((.*?)\)\s*(?:->|;)", rs, flags=re.S):
+        assert fn in h_fns, f"{fn} is not declared in include/dis_engine.h"
+        assert count(params) == count(h_fns[fn]), (fn, params, h_fns[fn])
