@@ -112,6 +112,8 @@ PROTOTYPES = {
     "dis_serving_step_at": (C.c_int, [vp, C.c_double, C.POINTER(ServingEvent), C.c_int32, i32p]),
     "dis_serving_depth": (C.c_int, [vp, C.POINTER(QueueDepth)]),
     "dis_serving_set_prefill_budget": (C.c_int, [vp, C.c_int32]),
+    "dis_serving_set_prefill_order": (C.c_int, [vp, C.c_int32, C.c_double]),
+    "dis_serving_order_prompts": (C.c_int, [C.c_int32, vp, vp, vp, C.c_double, vp]),
     "dis_serving_plan_step": (C.c_int, [C.c_int32, vp, C.c_int32, C.c_int32, vp]),
     "dis_serving_debug_pop": (C.c_int, [vp, C.c_int32, vp, i32p]),
     "dis_engine_prefix_stats": (C.c_int, [vp, C.POINTER(PrefixStats)]),

@@ -919,8 +919,8 @@ int Engine::prefill(int n, const int *slots, uint32_t *out_tokens, int *out_fini
 // ------------------------------------------------------------------------------------ mixed step
 // How one forward pass is shared between running sequences and prompts that are still being read (chunked prefill,
 // SURVEY.md §8 row f1): every decode row gets its one token; the remaining room -- at most `budget` prompt tokens and
-// never more than `cap` tokens in the pass -- goes to the unfinished prompts IN LIST ORDER, so an earlier request
-// (the admission queue's order: priority lane, then arrival) is never overtaken by a later one.  Pure function:
+// never more than `cap` tokens in the pass -- goes to the unfinished prompts IN LIST ORDER: the caller's list is the
+// schedule (the batcher lists them by priority class, then shortest prompt first with aging, serving.cpp).  Pure function:
 // exported as dis_serving_plan_step so that the rule is property-tested without a GPU.
 void plan_mixed_step(int n, const int *remaining_prompt, int budget, int cap, int *take) {
   int decode_rows = 0;

@@ -9,7 +9,8 @@
 //   ContinuousBatcher  the scheduler the reference only has as a window batcher in its spec (design.md:227-267,
 //                      requirements.md:45-48): every step admits queued requests into free engine slots (KV pages
 //                      permitting) and runs ONE forward pass in which every running sequence decodes a token and
-//                      the admitted prompts advance by a bounded chunk (dis_engine_step), retires finished
+//                      the admitted prompts advance by a bounded chunk (dis_engine_step; shortest prompt first inside a
+//                      priority class, with aging), retires finished
 //                      sequences and reports one event per token (TokenEvent, models.rs:268-288).
 #include <algorithm>
 #include <chrono>
@@ -106,7 +107,25 @@ struct Active {
   int32_t produced;
   int32_t prompt_tokens;
   double enqueued_at;
+  int32_t priority;
 };
+
+// Which admitted prompt is read first inside a pass.  The admission QUEUE keeps the reference's order (priority lane,
+// then arrival: crates/core/src/queue.rs:130-158); this is the order among requests that already hold a slot, which the
+// reference does not define.  Shortest prompt first inside a priority class minimises the mean time to first token (a
+// 128-token prompt does not wait behind an 8192-token one that arrived a moment earlier), and `aging` tokens of
+// precedence per second of waiting bound how long a long prompt can be overtaken.  Ties keep arrival order.
+void order_prompts(int n, const int32_t *priority, const int32_t *prompt_tokens, const double *waited_s, double aging,
+                   int32_t *order) {
+  std::vector<int32_t> idx((size_t)std::max(n, 0));
+  for (int i = 0; i < n; i++) idx[(size_t)i] = i;
+  std::stable_sort(idx.begin(), idx.end(), [&](int32_t a, int32_t b) {
+    if (priority[a] != priority[b]) return priority[a] > priority[b];  // High = 2 first
+    const double ka = (double)prompt_tokens[a] - aging * waited_s[a], kb = (double)prompt_tokens[b] - aging * waited_s[b];
+    return ka < kb;
+  });
+  for (int i = 0; i < n; i++) order[i] = idx[(size_t)i];
+}
 
 }  // namespace
 
@@ -119,6 +138,8 @@ struct dis_serving {
   std::mutex mu;
   int32_t max_active = 0;
   int32_t prefill_budget = 4096;  // prompt tokens read per scheduler step (beside one token for every running sequence)
+  int32_t prefill_order = 1;      // 0: admission order, 1: shortest prompt first inside a priority class, with aging
+  double aging_tokens_per_s = 4096.0;
   std::string last_error;
   explicit dis_serving(const dis_queue_config &c) : cfg(c), queue(c) {}
 };
@@ -185,6 +206,21 @@ int dis_serving_set_prefill_budget(dis_serving *s, int32_t tokens) {
   if (!s || tokens < 1) return DIS_ERR_INVALID_ARGUMENT;
   std::lock_guard<std::mutex> lk(s->mu);
   s->prefill_budget = tokens;
+  return DIS_OK;
+}
+
+int dis_serving_set_prefill_order(dis_serving *s, int32_t mode, double aging_tokens_per_s) {
+  if (!s || (mode != 0 && mode != 1) || !(aging_tokens_per_s >= 0.0)) return DIS_ERR_INVALID_ARGUMENT;
+  std::lock_guard<std::mutex> lk(s->mu);
+  s->prefill_order = mode;
+  s->aging_tokens_per_s = aging_tokens_per_s;
+  return DIS_OK;
+}
+
+int dis_serving_order_prompts(int32_t n, const int32_t *priority, const int32_t *prompt_tokens, const double *waited_s,
+                              double aging_tokens_per_s, int32_t *order) {
+  if (n < 0 || (n > 0 && (!priority || !prompt_tokens || !waited_s || !order)) || !(aging_tokens_per_s >= 0.0)) return DIS_ERR_INVALID_ARGUMENT;
+  order_prompts(n, priority, prompt_tokens, waited_s, aging_tokens_per_s, order);
   return DIS_OK;
 }
 
@@ -268,12 +304,28 @@ static int step_impl(dis_serving *s, double now_s, bool clock_injected, dis_serv
       emit(s, q.id, DIS_EVENT_DONE, 0, 0, DIS_FINISH_FAILED, (int32_t)q.prompt.size(), (now_s - q.enqueued_at) * 1e3);
       continue;
     }
-    s->active.push_back(Active{q.id, slot, 0, (int32_t)q.prompt.size(), q.enqueued_at});
+    s->active.push_back(Active{q.id, slot, 0, (int32_t)q.prompt.size(), q.enqueued_at, q.priority});
   }
   if (s->active.empty()) return drain(s, events, cap, n_events);
   // 3. ONE forward pass for everybody: each running sequence decodes a token and, in the same pass, the prompts still
   // being read advance by up to prefill_budget tokens in admission order (chunked prefill).  Running sequences are
   // never stalled behind a long prompt, and a prompt is never starved by the running ones.
+  if (s->prefill_order == 1) {
+    // running sequences first (a decode row each, order immaterial), then the prompts still being read in the order
+    // order_prompts gives them; dis_engine_step hands out the pass's prompt budget in list order
+    std::vector<Active> running, reading;
+    for (auto &a : s->active) (a.produced > 0 ? running : reading).push_back(a);
+    if (reading.size() > 1) {
+      std::vector<int32_t> pr, pt, ord(reading.size());
+      std::vector<double> wt;
+      for (auto &a : reading) { pr.push_back(a.priority); pt.push_back(a.prompt_tokens); wt.push_back(std::max(0.0, now_s - a.enqueued_at)); }
+      order_prompts((int)reading.size(), pr.data(), pt.data(), wt.data(), s->aging_tokens_per_s, ord.data());
+      for (int32_t i : ord) running.push_back(reading[(size_t)i]);
+    } else {
+      for (auto &a : reading) running.push_back(a);
+    }
+    s->active.swap(running);
+  }
   std::vector<int32_t> slots, fin(s->active.size()), produced(s->active.size());
   std::vector<uint32_t> toks(s->active.size());
   for (auto &a : s->active) slots.push_back(a.slot);

@@ -478,6 +478,11 @@ class ContinuousBatcher:
         if self.lib.dis_serving_set_prefill_budget(self.h, int(tokens)) != B.OK:
             raise ValueError("prefill budget must be >= 1")
 
+    def set_prefill_order(self, shortest_first: bool = True, aging_tokens_per_s: float = 4096.0) -> None:
+        """Order in which admitted prompts are read inside a pass (dis_serving_set_prefill_order)."""
+        if self.lib.dis_serving_set_prefill_order(self.h, 1 if shortest_first else 0, float(aging_tokens_per_s)) != B.OK:
+            raise ValueError("aging must be >= 0")
+
     def cancel(self, request_id) -> bool:
         """Client disconnect (requirements.md:85); False if the request is neither queued nor running."""
         return self.lib.dis_serving_cancel(self.h, self._wire_id(request_id)) == B.OK

@@ -267,6 +267,15 @@ DIS_API int dis_serving_depth(dis_serving *s, dis_queue_depth *out);
 /* Prompt tokens read per scheduler step beside the running sequences' decode rows (default 4096): the knob between
  * time-to-first-token of waiting requests and inter-token latency of running ones. */
 DIS_API int dis_serving_set_prefill_budget(dis_serving *s, int32_t tokens);
+/* Which admitted prompt is read first inside a pass.  The admission queue keeps the reference's order (priority lane,
+ * then arrival: crates/core/src/queue.rs:130-158); among requests that already hold a slot -- an order the reference
+ * does not define -- mode 1 (default) reads the shortest prompt first inside a priority class, a waiting request
+ * gaining aging_tokens_per_s (default 4096) tokens of precedence per second, ties in arrival order; mode 0 keeps
+ * admission order.  dis_serving_order_prompts is that rule as a pure function (no engine, no GPU): order[] receives the
+ * indices 0..n-1 in reading order. */
+DIS_API int dis_serving_set_prefill_order(dis_serving *s, int32_t mode, double aging_tokens_per_s);
+DIS_API int dis_serving_order_prompts(int32_t n, const int32_t *priority, const int32_t *prompt_tokens,
+                                      const double *waited_s, double aging_tokens_per_s, int32_t *order);
 /* The rule dis_engine_step uses to share a pass, as a pure function (no engine, no GPU) so that it can be property-
  * tested: remaining_prompt[i] <= 0 marks a decode row (take[i] = 1); the other entries receive, in list order, as
  * much of their remaining prompt as still fits into min(budget, cap - decode rows) tokens. */

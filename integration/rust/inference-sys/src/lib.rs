@@ -99,7 +99,7 @@ extern "C" {
     pub fn dis_serving_create(engine: *mut dis_engine, cfg: *const dis_queue_config, max_active: i32, out: *mut *mut dis_serving) -> c_int;
     pub fn dis_serving_destroy(s: *mut dis_serving) -> c_int;
     pub fn dis_serving_last_error(s: *mut dis_serving) -> *const c_char;
-    /// request_id: `Uuid::as_bytes()`; priority 0 = High, 1 = Normal, 2 = Low (crates/core/src/queue.rs).
+    /// request_id: `Uuid::as_bytes()`; priority: DIS_PRIORITY_LOW = 0, NORMAL = 1, HIGH = 2 (the lanes of crates/core/src/queue.rs).
     pub fn dis_serving_submit(s: *mut dis_serving, request_id: *const u8, prompt: *const u32, n_prompt: i32,
                               params: *const dis_sampling_params, priority: i32) -> c_int;
     /// Client went away (requirements.md:85): the request leaves the queue or frees its slot and KV pages.
@@ -108,4 +108,7 @@ extern "C" {
     pub fn dis_serving_step(s: *mut dis_serving, events: *mut dis_serving_event, cap: i32, n_events: *mut i32) -> c_int;
     pub fn dis_serving_depth(s: *mut dis_serving, out: *mut dis_queue_depth) -> c_int;
     pub fn dis_serving_set_prefill_budget(s: *mut dis_serving, tokens: i32) -> c_int;
+    /// mode 0: prompts advance in admission order; 1 (default): shortest prompt first inside a priority class, a waiting
+    /// request gaining `aging_tokens_per_s` tokens of precedence per second.
+    pub fn dis_serving_set_prefill_order(s: *mut dis_serving, mode: i32, aging_tokens_per_s: f64) -> c_int;
 }

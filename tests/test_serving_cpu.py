@@ -131,3 +131,46 @@ def test_mixed_step_plan_is_fair_and_bounded(remaining, budget, cap):
     if len(short):
         assert (pre[short[0] + 1:] == 0).all()          # nobody behind a partly served prompt reads anything
         assert int(pre.sum()) == room                   # and the room was used up
+
+
+@settings(max_examples=200, deadline=None)
+@given(st.lists(st.tuples(st.integers(0, 2), st.integers(1, 8192), st.floats(0.0, 30.0)), min_size=0, max_size=60),
+       st.floats(0.0, 10000.0))
+def test_prompt_reading_order_is_shortest_first_within_priority_with_aging(reqs, aging):
+    """dis_serving_order_prompts, the order in which the batcher reads the prompts of requests that already hold a slot:
+    a permutation; a higher priority class is never behind a lower one; inside a class the effective length
+    prompt_tokens - aging * waited never decreases; equal keys keep arrival (= list) order."""
+    import numpy as np
+    lib = B.load()
+    n = len(reqs)
+    pr = np.array([r[0] for r in reqs], np.int32)
+    pt = np.array([r[1] for r in reqs], np.int32)
+    wt = np.array([r[2] for r in reqs], np.float64)
+    order = np.full(n, -1, np.int32)
+    assert lib.dis_serving_order_prompts(n, pr.ctypes.data, pt.ctypes.data, wt.ctypes.data, float(aging), order.ctypes.data) == B.OK
+    assert sorted(order.tolist()) == list(range(n))
+    key = pt.astype(np.float64) - aging * wt
+    for a, b in zip(order[:-1], order[1:]):
+        assert pr[a] >= pr[b]
+        if pr[a] == pr[b]:
+            assert key[a] <= key[b]
+            if key[a] == key[b]:
+                assert a < b
+
+
+def test_prompt_reading_order_examples():
+    import numpy as np
+    lib = B.load()
+
+    def order(pr, pt, wt, aging):
+        pr, pt, wt = np.array(pr, np.int32), np.array(pt, np.int32), np.array(wt, np.float64)
+        out = np.zeros(len(pr), np.int32)
+        assert lib.dis_serving_order_prompts(len(pr), pr.ctypes.data, pt.ctypes.data, wt.ctypes.data, aging, out.ctypes.data) == B.OK
+        return out.tolist()
+    N, H, L = B.PRIORITY_NORMAL, B.PRIORITY_HIGH, B.PRIORITY_LOW
+    assert order([N, N, N], [8000, 128, 2000], [0, 0, 0], 4096.0) == [1, 2, 0]          # shortest first
+    assert order([N, H, L], [100, 8000, 10], [0, 0, 0], 4096.0) == [1, 0, 2]            # priority before length
+    assert order([N, N], [8000, 128], [2.0, 0.0], 4096.0) == [0, 1]                     # 2 s of waiting outweigh 7872 tokens
+    assert order([N, N], [8000, 128], [1.0, 0.0], 4096.0) == [1, 0]                     # 1 s does not
+    assert order([N, N, N], [500, 500, 500], [0, 0, 0], 0.0) == [0, 1, 2]               # ties: arrival order
+    assert lib.dis_serving_order_prompts(2, None, None, None, 1.0, None) == B.ERR_INVALID_ARGUMENT

@@ -161,3 +161,42 @@ def test_chunked_prefill_in_the_batcher_never_stalls_running_requests():
     _matches_oracle(mimic, late, got["late"])
     assert e.status().kv_pages_free == e.status().kv_pages_total
     cb.close(); e.close()
+
+
+def test_short_prompts_are_read_before_a_long_one_that_arrived_first():
+    """The order among requests that hold a slot (dis_serving_set_prefill_order): by default the shortest prompt is read
+    first, so three 10-token requests submitted AFTER a 230-token one get their first token before it; in admission
+    order (mode 0) the long prompt is read first.  Either way every request gets the tokens it gets alone."""
+    rng = np.random.default_rng(21)
+    long_p = rng.integers(0, SHAPE.vocab, 230).tolist()
+    shorts = [rng.integers(0, SHAPE.vocab, 10).tolist() for _ in range(3)]
+    mimic = O.Oracle(SHAPE, act_round=True); mimic.fill_synthetic(31, True)
+    for shortest_first in (True, False):
+        e = Engine(WorkerConfig(to_engine_shape(SHAPE), max_batch=4, kv_pages=128, page_size=16, max_step_tokens=256))
+        e.load_synthetic(31); e.finalize()
+        cb = ContinuousBatcher(e, max_active=4)
+        cb.set_prefill_budget(64)
+        cb.set_prefill_order(shortest_first)
+        cb.submit("long", long_p, InferenceParams(4, 0.0))
+        for i, p in enumerate(shorts):
+            cb.submit(f"s{i}", p, InferenceParams(4, 0.0))
+        first, toks = [], {}
+        for _ in range(200):
+            for ev in cb.step():
+                if ev[1] == B.EVENT_TOKEN:
+                    if ev[3] == 0:
+                        first.append(ev[0])
+                    toks.setdefault(ev[0], []).append(ev[2])
+            d = cb.depth()
+            if d.total == 0 and d.active == 0:
+                break
+        assert sorted(first) == ["long", "s0", "s1", "s2"]
+        if shortest_first:
+            assert first.index("long") == 3, first
+        else:
+            assert first.index("long") == 0, first
+        _matches_oracle(mimic, long_p, toks["long"])
+        for i, p in enumerate(shorts):
+            _matches_oracle(mimic, p, toks[f"s{i}"])
+        assert e.status().kv_pages_free == e.status().kv_pages_total
+        cb.close(); e.close()
